@@ -1,0 +1,106 @@
+"""Generates tests/golden/*.npz by running the REFERENCE's own OMP build (oracle/_ref/libgsdf_ref.so, compiled
+from /root/reference by oracle/Makefile) single-threaded (OMP_THREAD_LIMIT=1 = its bit-reproducible mode) on
+small seeded synthetic sequences.  Run here (where /root/reference exists):
+
+    python tests/golden/make_golden.py
+
+The fixtures travel to the GPU box, where /root/reference does not exist; tests compare both the C restatement
+(oracle/gsdf_oracle.c) and the CUDA path against them.
+"""
+import os
+import sys
+from pathlib import Path
+
+os.environ["OMP_THREAD_LIMIT"] = "1"
+ROOT = Path(__file__).resolve().parents[2]
+sys.path.insert(0, str(ROOT / "oracle"))
+sys.path.insert(0, str(ROOT / "gradient-sdf_b200"))
+
+import numpy as np  # noqa: E402
+import pyoracle as po  # noqa: E402
+import synth  # noqa: E402
+
+W, H = 160, 120
+N_FRAMES = 7
+N_INJECT = 3  # frames fused at ground-truth poses for the kernel-level dumps
+
+
+def to_mm(frames):
+    depth_mm = np.round(frames / np.float32(0.001)).astype(np.uint16)
+    assert np.array_equal(depth_mm.astype(np.float32) * np.float32(0.001), frames)
+    return depth_mm
+
+
+def run(variant: int, voxel_size: float, trunc: float, name: str, free_run: bool = True) -> None:
+    # kernel-level frames: the reference's own orbit step (100 frames per turn ~ matlab/poses.txt's 90)
+    frames, poses, K, _ = synth.make_sequence(100, W, H)
+    frames, poses = frames[:N_INJECT + 1], poses[:N_INJECT + 1]
+    out = dict(depth_mm=to_mm(frames), poses=poses, K=K, variant=variant, voxel_size=np.float32(voxel_size),
+               trunc=np.float32(trunc), width=W, height=H)
+
+    # ---- L1: kernel-level, pose-injected
+    r = po.RefScan(variant, voxel_size, trunc, W, H, K)
+    out["normals0"] = r.normals(frames[0])
+    out["normal_cache"] = r.normal_cache()
+    Rs, ts = [], []
+    for i in range(N_INJECT):
+        R, t, _, _ = r.update(frames[i], poses[i])
+        Rs.append(R)
+        ts.append(t)
+        if i == 0:
+            k, d, w, g = r.download()
+            out.update(f0_keys=k, f0_dist=d, f0_weight=w, f0_grad=g)
+    out["inject_R"], out["inject_t"] = np.stack(Rs), np.stack(ts)
+    k, d, w, g = r.download()
+    out.update(keys=k, dist=d, weight=w, grad=g)
+    rng = np.random.default_rng(7)
+    idx = rng.integers(0, len(k), 4000)
+    pts = (k[idx].astype(np.float32) + rng.uniform(-0.7, 0.7, (4000, 3)).astype(np.float32)) * np.float32(voxel_size)
+    phi, grad, wq = r.query(pts)
+    out.update(q_pts=pts, q_phi=phi, q_grad=grad, q_w=wq)
+    # one tracker iteration from the ground-truth pose of frame 2 against frame 3 (gives xi through the pose)
+    r.set_opt(1, 1e-3, 1.0)
+    r.set_pose(poses[N_INJECT - 1])
+    out["one_iter_start"] = r.get_pose()
+    conv, _ = r.optimize(frames[N_INJECT])
+    out["one_iter_pose"], out["one_iter_conv"] = r.get_pose(), conv
+    r.close()
+
+    if not free_run:
+        path = Path(__file__).resolve().parent / f"{name}.npz"
+        np.savez_compressed(path, **out)
+        print(name, "voxels", len(out["keys"]), "size %.0f KB" % (path.stat().st_size / 1024))
+        return
+
+    # ---- L3: free-running, as main_scan_3d.cpp:208-266 without a pose file (frame 0 fused at identity);
+    # gentler camera motion (400 frames per turn: ~3 cm, 0.9 degrees per frame) so that the tracker converges
+    frames = synth.make_sequence(400, W, H)[0][:N_FRAMES]
+    out["free_depth_mm"] = to_mm(frames)
+    r = po.RefScan(variant, voxel_size, trunc, W, H, K)
+    ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+    r.update(frames[0], ident)
+    r.set_pose(ident)
+    traj, convs, iters = [ident.copy()], [True], [0]
+    for i in range(1, N_FRAMES):
+        conv, it = r.optimize(frames[i])
+        p = r.get_pose()
+        if conv:
+            r.update(frames[i], p)
+        traj.append(p)
+        convs.append(conv)
+        iters.append(it)
+    k, d, w, g = r.download()
+    out.update(free_traj=np.stack(traj), free_conv=np.array(convs), free_iters=np.array(iters), free_keys=k,
+               free_dist=d, free_weight=w, free_grad=g)
+    r.close()
+    path = Path(__file__).resolve().parent / f"{name}.npz"
+    np.savez_compressed(path, **out)
+    print(name, "voxels", len(out["keys"]), "free voxels", len(k), "conv", convs, "iters", iters,
+          "size %.0f KB" % (path.stat().st_size / 1024))
+
+
+if __name__ == "__main__":
+    assert po.have_ref(), "build oracle/_ref first (make -C oracle ref)"
+    run(0, 0.02, 5.0, "grad_160x120_2cm_t5")
+    run(1, 0.02, 5.0, "base_160x120_2cm_t5")
+    run(0, 0.01, 10.0, "grad_160x120_1cm_t10", free_run=False)
