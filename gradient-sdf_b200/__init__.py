@@ -1,0 +1,330 @@
+"""gradient-sdf_b200 — B200-native Scan3D track+fuse hot path (ctypes host binding over include/gsdf_b200.h).
+
+The directory name is not a Python identifier; load it with `gsdf_loader.load()` at the repo root (tests,
+bench.py and __graft_entry__.py do) — it registers this package as `gradient_sdf_b200`.
+
+The classes mirror the reference's C++ surface for this path:
+    MapGradPixelSdf / MapPixelSdf   sdf_tracker/MapGradPixelSdf.h, MapPixelSdf.h  (update, setup, tsdf, weights)
+    RigidPointOptimizer             sdf_tracker/RigidOptimizer.h:90-110           (optimize, pose, set_pose, setters)
+    NormalEstimator                 normals/NormalEstimator.h:158-210             (compute, x0/y0/n_sq_inv planes)
+The C++ forwarding shells with the same names are in host/.  Everything computes on the GPU through
+libgsdf_b200.so; if the library or a CUDA device is missing the constructors raise (no CPU fallback).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "libgsdf_b200.so"
+
+GSDF_GRAD_SDF, GSDF_BASE_SDF = 0, 1
+_f32p = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int32)
+
+STATUS = {0: "GSDF_OK", 1: "GSDF_ERR_INVALID", 2: "GSDF_ERR_CUDA", 3: "GSDF_ERR_CAPACITY", 4: "GSDF_ERR_NCCL",
+          5: "GSDF_ERR_NO_FRAME"}
+
+# every symbol include/gsdf_b200.h declares (tests check the library exports them all)
+EXPORTS = [
+    "gsdf_create", "gsdf_destroy", "gsdf_last_error", "gsdf_reset", "gsdf_get_normal_cache", "gsdf_compute_normals",
+    "gsdf_upload_frame", "gsdf_set_frame_device", "gsdf_integrate", "gsdf_integrate_pose", "gsdf_accumulate",
+    "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
+    "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_version",
+]
+
+
+class GsdfError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"{STATUS.get(status, status)}: {msg}")
+        self.status = status
+
+
+class Config(C.Structure):
+    _fields_ = [("variant", C.c_int32), ("voxel_size", C.c_float), ("truncation", C.c_float), ("z_min", C.c_float),
+                ("z_max", C.c_float), ("width", C.c_int32), ("height", C.c_int32), ("K", C.c_float * 9),
+                ("normal_window", C.c_int32), ("log2_capacity", C.c_int32), ("device", C.c_int32),
+                ("world_size", C.c_int32), ("rank", C.c_int32)]
+
+
+class IntegrateStats(C.Structure):
+    _fields_ = [("points", C.c_int64), ("updates", C.c_int64), ("blocks", C.c_int64)]
+
+
+def build(verbose: bool = False) -> None:
+    """Compile libgsdf_b200.so for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    subprocess.run(["make", "-C", str(HERE), "all"], check=True, stdout=None if verbose else subprocess.DEVNULL)
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """The C-ABI library.  Raises if it has not been built: the product never falls back to a CPU path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise FileNotFoundError(f"{LIB_PATH} is missing: run __graft_entry__.build() (make -C gradient-sdf_b200)")
+    L = C.CDLL(str(LIB_PATH))
+    H = C.c_void_p
+    L.gsdf_create.argtypes = [C.POINTER(Config), C.POINTER(H)]
+    L.gsdf_destroy.argtypes = [H]
+    L.gsdf_last_error.restype = C.c_char_p
+    L.gsdf_last_error.argtypes = [H]
+    L.gsdf_reset.argtypes = [H]
+    L.gsdf_get_normal_cache.argtypes = [H, _f32p]
+    L.gsdf_compute_normals.argtypes = [H, _f32p, _f32p, _f32p]
+    L.gsdf_upload_frame.argtypes = [H, C.c_void_p]
+    L.gsdf_set_frame_device.argtypes = [H, C.c_void_p]
+    L.gsdf_integrate.argtypes = [H, _f32p, _f32p, C.POINTER(IntegrateStats)]
+    L.gsdf_integrate_pose.argtypes = [H, _f32p, C.POINTER(IntegrateStats)]
+    L.gsdf_accumulate.argtypes = [H, _f32p, _f32p, C.c_int32, _f32p]
+    L.gsdf_track.argtypes = [H, _f32p, C.c_int32, C.c_float, C.c_float, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.gsdf_query.argtypes = [H, _f32p, C.c_int64, _f32p, _f32p, _f32p]
+    L.gsdf_voxel_count.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    L.gsdf_download.argtypes = [H, C.c_int64, _i32p, _f32p, _f32p, _f32p, C.POINTER(C.c_int64)]
+    L.gsdf_pose_matrix.restype = None
+    L.gsdf_pose_matrix.argtypes = [_f32p, _f32p, _f32p]
+    L.gsdf_pose_apply_increment.restype = None
+    L.gsdf_pose_apply_increment.argtypes = [_f32p, _f32p, _f32p]
+    L.gsdf_llt_solve6.restype = None
+    L.gsdf_llt_solve6.argtypes = [_f32p, _f32p, _f32p]
+    L.gsdf_synchronize.argtypes = [H]
+    L.gsdf_stream.restype = C.c_void_p
+    L.gsdf_stream.argtypes = [H]
+    L.gsdf_launch_count.restype = C.c_int64
+    L.gsdf_launch_count.argtypes = [H]
+    L.gsdf_comm_unique_id.argtypes = [C.POINTER(C.c_uint8)]
+    L.gsdf_comm_init.argtypes = [H, C.POINTER(C.c_uint8)]
+    L.gsdf_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def _fp(a):
+    return a.ctypes.data_as(_f32p)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+# ---- pose algebra (no GPU needed) -------------------------------------------------------------------------
+def pose_matrix(pose7):
+    """(R 3x3, normalised pose7) as Sophus::SE3f(quaternion, t).rotationMatrix() gives them."""
+    p = _f32(pose7)
+    R, pn = np.zeros(9, np.float32), np.zeros(7, np.float32)
+    lib().gsdf_pose_matrix(_fp(p), _fp(R), _fp(pn))
+    return R.reshape(3, 3), pn
+
+
+def pose_apply_increment(pose7, xi):
+    p, x, out = _f32(pose7), _f32(xi), np.zeros(7, np.float32)
+    lib().gsdf_pose_apply_increment(_fp(p), _fp(x), _fp(out))
+    return out
+
+
+def llt_solve6(H, g):
+    H, g, xi = _f32(H).reshape(36), _f32(g), np.zeros(6, np.float32)
+    lib().gsdf_llt_solve6(_fp(H), _fp(g), _fp(xi))
+    return xi
+
+
+class NormalEstimator:
+    """cv::NormalEstimator<float>(width, height, K, Size(win, win)) — parameters only; the device cache lives in
+    the volume the estimator is handed to (as the reference hands NEst to Sdf::update)."""
+
+    def __init__(self, width: int, height: int, K, window: int = 11):
+        self.width, self.height, self.window = int(width), int(height), int(window)
+        self.K = _f32(K).reshape(3, 3)
+
+
+class Sdf:
+    """Abstract volume (sdf_tracker/Sdf.h).  One instance = one gsdf_handle = one GPU shard."""
+
+    variant = GSDF_GRAD_SDF
+
+    def __init__(self, voxel_size: float, T: float, NEst: NormalEstimator, log2_capacity: int = 17, device: int = 0,
+                 world_size: int = 1, rank: int = 0, z_min: float = 0.5, z_max: float = 3.5):
+        cfg = Config()
+        cfg.variant = self.variant
+        cfg.voxel_size = float(np.float32(voxel_size))
+        cfg.truncation = float(np.float32(T))
+        cfg.z_min, cfg.z_max = z_min, z_max
+        cfg.width, cfg.height = NEst.width, NEst.height
+        for i, v in enumerate(NEst.K.reshape(9)):
+            cfg.K[i] = float(v)
+        cfg.normal_window = NEst.window
+        cfg.log2_capacity = log2_capacity
+        cfg.device, cfg.world_size, cfg.rank = device, world_size, rank
+        self.cfg = cfg
+        self.width, self.height = NEst.width, NEst.height
+        self.voxel_size = cfg.voxel_size
+        self.L = lib()
+        self.h = C.c_void_p()
+        st = self.L.gsdf_create(C.byref(cfg), C.byref(self.h))
+        if st != 0:
+            raise GsdfError(st, (self.L.gsdf_last_error(None) or b"").decode())
+
+    # -- plumbing
+    def _check(self, st: int):
+        if st != 0:
+            raise GsdfError(st, (self.L.gsdf_last_error(self.h) or b"").decode())
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.gsdf_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        self._check(self.L.gsdf_reset(self.h))
+
+    def synchronize(self):
+        self._check(self.L.gsdf_synchronize(self.h))
+
+    @property
+    def stream(self) -> int:
+        return int(self.L.gsdf_stream(self.h) or 0)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.L.gsdf_launch_count(self.h))
+
+    def comm_init(self, id128: bytes):
+        buf = (C.c_uint8 * 128).from_buffer_copy(id128)
+        self._check(self.L.gsdf_comm_init(self.h, buf))
+
+    # -- frames
+    def upload_frame(self, depth):
+        """depth: host float32 array (height, width), metres; a pinned torch tensor's numpy view works too."""
+        d = _f32(depth)
+        assert d.size == self.width * self.height
+        self._keep = d
+        self._check(self.L.gsdf_upload_frame(self.h, d.ctypes.data))
+
+    def set_frame_device(self, dev_ptr: int):
+        self._check(self.L.gsdf_set_frame_device(self.h, C.c_void_p(dev_ptr)))
+
+    # -- NormalEstimator
+    def normal_cache(self):
+        out = np.zeros((11, self.height, self.width), np.float32)
+        self._check(self.L.gsdf_get_normal_cache(self.h, _fp(out)))
+        return out
+
+    def compute_normals(self):
+        n = np.zeros((3, self.height, self.width), np.float32)
+        self._check(self.L.gsdf_compute_normals(self.h, _fp(n[0]), _fp(n[1]), _fp(n[2])))
+        return n
+
+    # -- Sdf::update / setup
+    def update(self, depth, pose7, stats: bool = True):
+        """Sdf::update(color, depth, K, pose, NEst): depth=None fuses the frame already set."""
+        if depth is not None:
+            self.upload_frame(depth)
+        p = _f32(pose7)
+        st = IntegrateStats()
+        self._check(self.L.gsdf_integrate_pose(self.h, _fp(p), C.byref(st) if stats else None))
+        return (st.points, st.updates, st.blocks) if stats else None
+
+    def update_Rt(self, depth, R, t, stats: bool = True):
+        if depth is not None:
+            self.upload_frame(depth)
+        R, t = _f32(R).reshape(9), _f32(t)
+        st = IntegrateStats()
+        self._check(self.L.gsdf_integrate(self.h, _fp(R), _fp(t), C.byref(st) if stats else None))
+        return (st.points, st.updates, st.blocks) if stats else None
+
+    def setup(self, depth):
+        """Sdf::setup = update at the identity pose (Sdf.h:119-121)."""
+        return self.update(depth, np.array([0, 0, 0, 0, 0, 0, 1], np.float32))
+
+    # -- Sdf::tsdf / weights (batched)
+    def query(self, pts):
+        p = _f32(pts).reshape(-1, 3)
+        n = p.shape[0]
+        phi, grad, w = np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros(n, np.float32)
+        self._check(self.L.gsdf_query(self.h, _fp(p), n, _fp(phi), _fp(grad), _fp(w)))
+        return phi, grad, w
+
+    def accumulate(self, R, t, sampling: int = 1):
+        R, t, out = _f32(R).reshape(9), _f32(t), np.zeros(29, np.float32)
+        self._check(self.L.gsdf_accumulate(self.h, _fp(R), _fp(t), sampling, _fp(out)))
+        return out
+
+    # -- map access
+    def voxel_count(self):
+        n, b = C.c_int64(0), C.c_int64(0)
+        self._check(self.L.gsdf_voxel_count(self.h, C.byref(n), C.byref(b)))
+        return int(n.value), int(b.value)
+
+    def download(self, sort: bool = True):
+        n, _ = self.voxel_count()
+        keys, dist = np.zeros((n, 3), np.int32), np.zeros(n, np.float32)
+        weight, grad = np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+        got = C.c_int64(0)
+        if n:
+            self._check(self.L.gsdf_download(self.h, n, keys.ctypes.data_as(_i32p), _fp(dist), _fp(weight), _fp(grad),
+                                             C.byref(got)))
+            assert got.value == n
+        if sort and n:
+            order = np.lexsort((keys[:, 2], keys[:, 1], keys[:, 0]))
+            keys, dist, weight, grad = keys[order], dist[order], weight[order], grad[order]
+        return keys, dist, weight, grad
+
+
+class MapGradPixelSdf(Sdf):
+    """MapGradPixelSdf(voxel_size, T) — Gradient-SDF volume (sdf_tracker/MapGradPixelSdf.h:99-103)."""
+    variant = GSDF_GRAD_SDF
+
+
+class MapPixelSdf(Sdf):
+    """MapPixelSdf(voxel_size, T) — plain SDF volume (sdf_tracker/MapPixelSdf.h:97-101)."""
+    variant = GSDF_BASE_SDF
+
+
+class RigidPointOptimizer:
+    """RigidPointOptimizer(tSDF) / (num_iterations, conv_threshold, damping, tSDF)
+    (sdf_tracker/RigidPointOptimizer.h:55-61, RigidOptimizer.h:68-83)."""
+
+    def __init__(self, tSDF: Sdf, num_iterations: int = 25, conv_threshold: float = 1e-3, damping: float = 1.0):
+        self.tSDF = tSDF
+        self.num_iterations, self.conv_threshold, self.damping = num_iterations, conv_threshold, damping
+        self._pose = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+        self.last_iterations = 0
+
+    def set_num_iterations(self, n):
+        self.num_iterations = int(n)
+
+    def set_conv_threshold(self, t):
+        self.conv_threshold = float(t)
+
+    def set_damping(self, d):
+        self.damping = float(d)
+
+    def set_pose(self, pose7):
+        self._pose = pose_matrix(pose7)[1]  # SE3(q, t) normalises the quaternion
+
+    def pose(self):
+        return self._pose.copy()
+
+    def optimize(self, depth) -> bool:
+        """optimize(depth, K): depth=None tracks against the frame already set on the volume."""
+        s = self.tSDF
+        if depth is not None:
+            s.upload_frame(depth)
+        conv, it = C.c_int32(0), C.c_int32(0)
+        s._check(s.L.gsdf_track(s.h, _fp(self._pose), self.num_iterations, self.conv_threshold, self.damping,
+                                C.byref(conv), C.byref(it)))
+        self.last_iterations = int(it.value)
+        return bool(conv.value)

@@ -1,0 +1,123 @@
+// Device-side building blocks of the Scan3D hot path: voxel-block hash, key arithmetic, voxel accumulators.
+//
+// HBM layout (one shard per GPU):
+//   keys  : u64[cap]                    open-addressing table of packed 8^3-block keys, EMPTY = ~0
+//   grad-sdf  acc4 : float4[cap*512]    per voxel {S = sum w*trunc(sdf), Gx, Gy, Gz = sum w*R*n}
+//             accW : float [cap*512]    per voxel  W = sum w
+//   base-sdf  acc2 : float2[cap*512]    per voxel {W, S}
+// The hash slot IS the block's storage index (no second indirection, no allocator race): a block exists as
+// soon as its key is CAS-ed into the table, and its voxels are zero from gsdf_create/gsdf_reset, so fusion
+// is a single pass of fire-and-forget vector reductions (red.global.add.v4.f32 / .v2.f32 / .f32).
+// dist = S / W is derived on read, which is algebraically the reference's running weighted mean
+// (MapGradPixelSdfOmp.cpp:115-116) and order-independent up to fp32 rounding.
+//
+// Key-determining arithmetic (everything that feeds a branch or a round()) keeps the reference's fp32
+// association order with every product and sum rounded separately.  The library is
+// compiled with -fmad=false; the *_rn intrinsics below make that explicit where it matters.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gsdf {
+
+constexpr int kBlockLog2 = 3;                 // 8^3 voxels per block
+constexpr int kBlockVoxels = 512;
+constexpr unsigned long long kEmptyKey = ~0ull;
+constexpr int kMaxProbe = 512;
+constexpr int kKeyBias = 1 << 20;             // block coordinates in [-2^20, 2^20)
+
+struct MapView {
+    unsigned long long* keys;
+    float4* acc4;
+    float* accW;
+    float2* acc2;
+    uint32_t cap_mask;
+    int32_t world, rank;
+};
+
+struct Counters {
+    unsigned long long points;    // pixels that passed every validity test
+    unsigned long long updates;   // committed (pixel,k) samples
+    unsigned int blocks;          // allocated blocks
+    unsigned int overflow;        // find-or-insert gave up: GSDF_ERR_CAPACITY
+    unsigned int ticket;          // last-block-done ticket of the reduction
+    unsigned int pad;
+};
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+    return x;
+}
+
+__device__ __forceinline__ unsigned long long pack_block(int bx, int by, int bz) {
+    return ((unsigned long long)(unsigned)(bx + kKeyBias) & 0x1FFFFFull) |
+           (((unsigned long long)(unsigned)(by + kKeyBias) & 0x1FFFFFull) << 21) |
+           (((unsigned long long)(unsigned)(bz + kKeyBias) & 0x1FFFFFull) << 42);
+}
+__device__ __forceinline__ void unpack_block(unsigned long long k, int& bx, int& by, int& bz) {
+    bx = (int)(k & 0x1FFFFFull) - kKeyBias;
+    by = (int)((k >> 21) & 0x1FFFFFull) - kKeyBias;
+    bz = (int)((k >> 42) & 0x1FFFFFull) - kKeyBias;
+}
+__device__ __forceinline__ unsigned long long block_key_of(int vx, int vy, int vz) {
+    return pack_block(vx >> kBlockLog2, vy >> kBlockLog2, vz >> kBlockLog2);  // arithmetic shift = floor
+}
+__device__ __forceinline__ int local_index(int vx, int vy, int vz) {
+    return (vx & 7) | ((vy & 7) << 3) | ((vz & 7) << 6);
+}
+// Shard owner of a block (uses hash bits disjoint from the slot bits).
+__device__ __forceinline__ int block_owner(unsigned long long key, int world) {
+    return (int)((mix64(key) >> 40) % (unsigned long long)world);
+}
+
+// Read-only probe.  Returns the slot or -1.
+__device__ __forceinline__ int map_find(const MapView& m, unsigned long long key) {
+    uint32_t slot = (uint32_t)mix64(key) & m.cap_mask;
+#pragma unroll 1
+    for (int probe = 0; probe < kMaxProbe; ++probe) {
+        const unsigned long long k = __ldcg(m.keys + slot);
+        if (k == key) return (int)slot;
+        if (k == kEmptyKey) return -1;
+        slot = (slot + 1) & m.cap_mask;
+    }
+    return -1;
+}
+
+// Find-or-insert (the reference's tsdf_[vi], MapGradPixelSdfOmp.cpp:114, at block granularity).
+// Returns the slot, or -1 if kMaxProbe slots were all taken by other keys (caller raises overflow).
+__device__ __forceinline__ int map_find_or_insert(const MapView& m, unsigned long long key, Counters* ctr) {
+    uint32_t slot = (uint32_t)mix64(key) & m.cap_mask;
+#pragma unroll 1
+    for (int probe = 0; probe < kMaxProbe; ++probe) {
+        unsigned long long k = __ldcg(m.keys + slot);
+        if (k == key) return (int)slot;
+        if (k == kEmptyKey) {
+            k = atomicCAS(m.keys + slot, kEmptyKey, key);
+            if (k == kEmptyKey) { atomicAdd(&ctr->blocks, 1u); return (int)slot; }
+            if (k == key) return (int)slot;
+        }
+        slot = (slot + 1) & m.cap_mask;
+    }
+    return -1;
+}
+
+// Eigen fixed-size 3-term reduction: a0*b0 + (a1*b1 + a2*b2), each product and sum rounded, no FMA.
+__device__ __forceinline__ float dot3_rn(float a0, float a1, float a2, float b0, float b1, float b2) {
+    return __fadd_rn(__fmul_rn(a0, b0), __fadd_rn(__fmul_rn(a1, b1), __fmul_rn(a2, b2)));
+}
+
+// float2vox, MapGradPixelSdf.h:74-77: round-half-away-from-zero of vs_inv * p
+__device__ __forceinline__ int float2vox1(float vs_inv, float p) { return (int)roundf(__fmul_rn(vs_inv, p)); }
+
+// Sdf::weight, Sdf.h:76-85
+__device__ __forceinline__ float sdf_weight(float sdf, float T, float inv_T) {
+    float w = 0.f;
+    if (sdf <= 0.f) w = 1.f;
+    else if (sdf <= T) w = __fsub_rn(1.f, __fmul_rn(sdf, inv_T));
+    return w;
+}
+// Sdf::truncate, Sdf.h:72-74
+__device__ __forceinline__ float sdf_truncate(float sdf, float T) { return fmaxf(-T, fminf(T, sdf)); }
+
+}  // namespace gsdf

@@ -1,0 +1,418 @@
+// Hand-written sm_100a kernels of the Scan3D hot path.  Included by gsdf_api.cu only.
+//   normals_kernel      cv::NormalEstimator<float>::compute          (normals/NormalEstimator.h:179-204)
+//   fuse_kernel<V>      Map{Grad,}PixelSdf::update                   (MapGradPixelSdfOmp.cpp:82-126,
+//                                                                     MapPixelSdfOmp.cpp:152-192)
+//   accumulate_kernel<V> RigidPointOptimizer per-pixel loop + sums   (RigidPointOptimizerOmp.cpp:69-91)
+//   query_kernel<V>     Sdf::weights / Sdf::tsdf                     (MapGradPixelSdf.h:109-125,
+//                                                                     MapPixelSdf.h:107-143, MapPixelSdfOmp.cpp:44-113)
+//   count/download      map iteration of the writers                 (MapGradPixelSdfOmp.cpp:144-151,189,285)
+#pragma once
+
+#include "gsdf_device.cuh"
+
+namespace gsdf {
+
+struct FrameGeom {
+    int w, h;
+    float vs, vs_inv, T, inv_T, z_min, z_max;
+    int factor;  // floor(T / vs), MapGradPixelSdfOmp.cpp:78
+};
+
+struct Pose {
+    float R[9];
+    float t[3];
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// Normal estimation (FALS).  One CTA computes a NT_W x NT_H tile of normals.  The masked reciprocal depth
+// times the three cached planes is staged through shared memory with an r-pixel REFLECT_101 halo; the window
+// sums follow the oracle's order exactly (double accumulation; rows left->right, then columns top->bottom,
+// one rounding to float), so the normals — and therefore the validity tests that decide the voxel key set —
+// are bit-identical to the reference build.
+constexpr int NT_W = 32, NT_H = 16, N_MAXR = 7;
+
+__device__ __forceinline__ int reflect101(int p, int len) {
+    if (len == 1) return 0;
+    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
+    return p;
+}
+
+__global__ void __launch_bounds__(NT_W* NT_H)
+normals_kernel(const float* __restrict__ depth, const float* __restrict__ x0n, const float* __restrict__ y0n,
+               const float* __restrict__ nsi, const float* __restrict__ Q, /* 6 planes Q11,Q12,Q13,Q22,Q23,Q33 */
+               float* __restrict__ nx, float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int tw = NT_W + 2 * r, th = NT_H + 2 * r;
+    float* a = reinterpret_cast<float*>(smem_raw);                                             // [3][th][tw] products
+    double* rs = reinterpret_cast<double*>(smem_raw + ((sizeof(float) * 3 * tw * th + 7) & ~size_t(7)));  // [3][th][NT_W] row sums
+    const int tid = threadIdx.y * NT_W + threadIdx.x;
+    const int x_base = blockIdx.x * NT_W, y_base = blockIdx.y * NT_H;
+    const size_t n = (size_t)w * h;
+
+    for (int i = tid; i < tw * th; i += NT_W * NT_H) {
+        const int ly = i / tw, lx = i - ly * tw;
+        // rows/columns beyond the image on the far side are clamped first (tiles may overhang), then reflected
+        const int gx = reflect101(min(x_base + lx - r, w - 1 + r), w);
+        const int gy = reflect101(min(y_base + ly - r, h - 1 + r), h);
+        const size_t g = (size_t)gy * w + gx;
+        const float z = depth[g];
+        const float zi = z != 0.f ? __fdiv_rn(1.f, z) : 0.f;          // NormalEstimator.h:181-187
+        a[i] = __fmul_rn(x0n[g], zi);                                  // :191
+        a[tw * th + i] = __fmul_rn(y0n[g], zi);                        // :192
+        a[2 * tw * th + i] = __fmul_rn(nsi[g], zi);                    // :193
+    }
+    __syncthreads();
+    // row sums for the NT_W centre columns of every (halo) row
+    for (int i = tid; i < 3 * th * NT_W; i += NT_W * NT_H) {
+        const int p = i / (th * NT_W), rem = i - p * th * NT_W;
+        const int ly = rem / NT_W, lx = rem - ly * NT_W;
+        const float* row = a + p * tw * th + ly * tw + lx;
+        double s = 0.0;
+        for (int d = 0; d <= 2 * r; ++d) s = __dadd_rn(s, (double)row[d]);
+        rs[i] = s;
+    }
+    __syncthreads();
+    const int x = x_base + threadIdx.x, y = y_base + threadIdx.y;
+    if (x >= w || y >= h) return;
+    double s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    for (int d = 0; d <= 2 * r; ++d) {
+        const int j = (threadIdx.y + d) * NT_W + threadIdx.x;
+        s1 = __dadd_rn(s1, rs[j]);
+        s2 = __dadd_rn(s2, rs[th * NT_W + j]);
+        s3 = __dadd_rn(s3, rs[2 * th * NT_W + j]);
+    }
+    const float b1 = (float)s1, b2 = (float)s2, b3 = (float)s3;
+    const size_t g = (size_t)y * w + x;
+    const float q11 = Q[g], q12 = Q[n + g], q13 = Q[2 * n + g], q22 = Q[3 * n + g], q23 = Q[4 * n + g], q33 = Q[5 * n + g];
+    const float vx = __fadd_rn(__fadd_rn(__fmul_rn(b1, q11), __fmul_rn(b2, q12)), __fmul_rn(b3, q13));  // :195
+    const float vy = __fadd_rn(__fadd_rn(__fmul_rn(b1, q12), __fmul_rn(b2, q22)), __fmul_rn(b3, q23));  // :196
+    const float vz = __fadd_rn(__fadd_rn(__fmul_rn(b1, q13), __fmul_rn(b2, q23)), __fmul_rn(b3, q33));  // :197
+    const float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)), __fmul_rn(vz, vz)));  // :199
+    nx[g] = __fdiv_rn(vx, nn);  // :201-203
+    ny[g] = __fdiv_rn(vy, nn);
+    nz[g] = __fdiv_rn(vz, nn);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Fusion: one thread per pixel walks 2*factor+1 samples along its ray and scatters into the voxel blocks.
+template <int VARIANT>
+__global__ void __launch_bounds__(256)
+fuse_kernel(MapView m, FrameGeom g, Pose pose, const float* __restrict__ depth, const float* __restrict__ nx,
+            const float* __restrict__ ny, const float* __restrict__ nz, const float* __restrict__ x0,
+            const float* __restrict__ y0, const float* __restrict__ hom_inv, Counters* ctr) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = g.w * g.h;
+    bool valid = idx < n;
+    float z = 0.f, Rxy0 = 0.f, Rxy1 = 0.f, Rxy2 = 0.f, Rn0 = 0.f, Rn1 = 0.f, Rn2 = 0.f;
+    const float* R = pose.R;
+    if (valid) {
+        z = depth[idx];
+        valid = !(z <= g.z_min || z >= g.z_max);  // MapGradPixelSdfOmp.cpp:89
+    }
+    if (valid) {
+        const float hx = x0[idx], hy = y0[idx];
+        const float a = nx[idx], b = ny[idx], c = nz[idx];
+        Rxy0 = dot3_rn(R[0], R[1], R[2], hx, hy, 1.f);  // :93
+        Rxy1 = dot3_rn(R[3], R[4], R[5], hx, hy, 1.f);
+        Rxy2 = dot3_rn(R[6], R[7], R[8], hx, hy, 1.f);
+        Rn0 = dot3_rn(R[0], R[1], R[2], a, b, c);       // :95
+        Rn1 = dot3_rn(R[3], R[4], R[5], a, b, c);
+        Rn2 = dot3_rn(R[6], R[7], R[8], a, b, c);
+        const float nsq = dot3_rn(a, b, c, a, b, c);
+        const float d = dot3_rn(a, b, c, hx, hy, 1.f);
+        // the reference compares the float expressions against double literals (:97-100); a NaN compares false
+        // in both tests, exactly as there
+        if ((double)nsq < .1) valid = false;
+        else if ((double)__fmul_rn(__fmul_rn(d, d), hom_inv[idx]) < .25) valid = false;
+    }
+    unsigned int n_upd = 0;
+    if (valid) {
+        unsigned long long last_key = kEmptyKey;
+        int slot = -1;
+        for (int kk = -g.factor; kk <= g.factor; ++kk) {  // float k = -factor .. factor, :103
+            const float s = __fadd_rn(z, __fmul_rn((float)kk, g.vs));
+            const float px = __fadd_rn(__fmul_rn(s, Rxy0), pose.t[0]);  // :105
+            const float py = __fadd_rn(__fmul_rn(s, Rxy1), pose.t[1]);
+            const float pz = __fadd_rn(__fmul_rn(s, Rxy2), pose.t[2]);
+            const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
+            const float qx = __fsub_rn(__fmul_rn(g.vs, (float)vx), pose.t[0]);  // vox2float(vi) - t, :107
+            const float qy = __fsub_rn(__fmul_rn(g.vs, (float)vy), pose.t[1]);
+            const float qz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pose.t[2]);
+            const float sdf = __fsub_rn(dot3_rn(R[2], R[5], R[8], qx, qy, qz), z);  // row 2 of R^T, :107-108
+            const float wgt = sdf_weight(sdf, g.T, g.inv_T);
+            if (wgt > 0.f) {
+                const unsigned long long key = block_key_of(vx, vy, vz);
+                if (key != last_key) {
+                    last_key = key;
+                    if (m.world > 1 && block_owner(key, m.world) != m.rank) slot = -2;  // another rank's block
+                    else {
+                        slot = map_find_or_insert(m, key, ctr);
+                        if (slot < 0) atomicAdd(&ctr->overflow, 1u);
+                    }
+                }
+                if (slot >= 0) {
+                    const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
+                    const float ws = wgt * sdf_truncate(sdf, g.T);
+                    if (VARIANT == 0) {
+                        atomicAdd(m.acc4 + addr, make_float4(ws, wgt * Rn0, wgt * Rn1, wgt * Rn2));  // :115-117
+                        atomicAdd(m.accW + addr, wgt);
+                    } else {
+                        atomicAdd(m.acc2 + addr, make_float2(wgt, ws));  // MapPixelSdfOmp.cpp:183-185
+                    }
+                    ++n_upd;
+                }
+            }
+        }
+    }
+    // counters: warp-reduce, one atomic per warp
+    const unsigned int pts = __popc(__ballot_sync(0xffffffffu, valid));
+    n_upd = __reduce_add_sync(0xffffffffu, n_upd);
+    if ((threadIdx.x & 31) == 0 && (pts | n_upd)) {
+        atomicAdd(&ctr->points, (unsigned long long)pts);
+        atomicAdd(&ctr->updates, (unsigned long long)n_upd);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Point queries shared by the tracker and gsdf_query.
+template <int VARIANT>
+struct Lookup;
+
+template <>
+struct Lookup<0> {  // MapGradPixelSdf.h:109-125
+    // returns weight; if > 0 fills phi and grad
+    __device__ static __forceinline__ float eval(const MapView& m, const FrameGeom& g, float px, float py, float pz,
+                                                 float& phi, float& g0, float& g1, float& g2) {
+        const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
+        const unsigned long long key = block_key_of(vx, vy, vz);
+        if (m.world > 1 && block_owner(key, m.world) != m.rank) return 0.f;
+        const int slot = map_find(m, key);
+        if (slot < 0) return 0.f;
+        const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
+        const float W = m.accW[addr];
+        if (!(W > 0.f)) return 0.f;
+        const float4 a = m.acc4[addr];
+        const float dist = a.x / W;
+        const float sq = dot3_rn(a.y, a.z, a.w, a.y, a.z, a.w);
+        float n0 = a.y, n1 = a.z, n2 = a.w;
+        if (sq > 0.f) { const float l = __fsqrt_rn(sq); n0 = __fdiv_rn(n0, l); n1 = __fdiv_rn(n1, l); n2 = __fdiv_rn(n2, l); }
+        const float dx = __fsub_rn(__fmul_rn(g.vs, (float)vx), px);
+        const float dy = __fsub_rn(__fmul_rn(g.vs, (float)vy), py);
+        const float dz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pz);
+        g0 = 1.2f * n0; g1 = 1.2f * n1; g2 = 1.2f * n2;
+        // `1.2*v.grad.normalized().dot(..)` is a double product in the reference (MapGradPixelSdf.h:114)
+        phi = (float)((double)dist + 1.2 * (double)dot3_rn(n0, n1, n2, dx, dy, dz));
+        return W;
+    }
+};
+
+template <>
+struct Lookup<1> {  // MapPixelSdf.h:107-143 + interp3, MapPixelSdfOmp.cpp:44-113
+    __device__ static __forceinline__ float eval(const MapView& m, const FrameGeom& g, float px, float py, float pz,
+                                                 float& phi, float& g0, float& g1, float& g2) {
+        const float fx = __fmul_rn(g.vs_inv, px), fy = __fmul_rn(g.vs_inv, py), fz = __fmul_rn(g.vs_inv, pz);
+        const int im = (int)floorf(fx), jm = (int)floorf(fy), km = (int)floorf(fz);
+        float d[8];
+        float Wn = 0.f;
+        const int rx = (int)roundf(fx) - im, ry = (int)roundf(fy) - jm, rz = (int)roundf(fz) - km;  // nearest corner
+        unsigned long long last_key = kEmptyKey;
+        int slot = -1;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const int i0 = c & 1, j0 = (c >> 1) & 1, k0 = c >> 2;
+            const int vx = im + i0, vy = jm + j0, vz = km + k0;
+            const unsigned long long key = block_key_of(vx, vy, vz);
+            if (key != last_key) { last_key = key; slot = map_find(m, key); }
+            if (slot < 0) return 0.f;  // weights(): all 8 corners must exist (MapPixelSdf.h:127-136)
+            const float2 v = m.acc2[(size_t)slot * kBlockVoxels + local_index(vx, vy, vz)];
+            if (!(v.x > 0.f)) return 0.f;
+            d[c] = v.y / v.x;
+            if (i0 == rx && j0 == ry && k0 == rz) Wn = v.x;
+        }
+        const float dx = fx - (float)im, dy = fy - (float)jm, dz = fz - (float)km;
+        const float d01 = (1.f - dx) * d[0] + dx * d[1], d23 = (1.f - dx) * d[2] + dx * d[3];
+        const float d45 = (1.f - dx) * d[4] + dx * d[5], d67 = (1.f - dx) * d[6] + dx * d[7];
+        const float d02 = (1.f - dy) * d[0] + dy * d[2], d13 = (1.f - dy) * d[1] + dy * d[3];
+        const float d46 = (1.f - dy) * d[4] + dy * d[6], d57 = (1.f - dy) * d[5] + dy * d[7];
+        g0 = g.vs_inv * ((((1.f - dz) * d13 + dz * d57) - (1.f - dz) * d02) - dz * d46);  // :97
+        g1 = g.vs_inv * ((((1.f - dz) * d23 + dz * d67) - (1.f - dz) * d01) - dz * d45);  // :98
+        g2 = g.vs_inv * ((((1.f - dy) * d45 + dy * d67) - (1.f - dy) * d01) - dy * d23);  // :99
+        const float dy0 = (1.f - dy) * d01 + dy * d23, dy1 = (1.f - dy) * d45 + dy * d67;
+        phi = (1.f - dz) * dy0 + dz * dy1;  // :107
+        return Wn;
+    }
+};
+
+template <int VARIANT>
+__global__ void __launch_bounds__(256)
+query_kernel(MapView m, FrameGeom g, const float* __restrict__ pts, long long n, float* __restrict__ phi,
+             float* __restrict__ grad, float* __restrict__ w) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float f = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f;
+    const float w0 = Lookup<VARIANT>::eval(m, g, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], f, g0, g1, g2);
+    if (!(w0 > 0.f)) { f = 0.f; g0 = g1 = g2 = 0.f; }
+    w[i] = w0; phi[i] = f;
+    grad[3 * i] = g0; grad[3 * i + 1] = g1; grad[3 * i + 2] = g2;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Tracker: per pixel residual + Jacobian, then the 29 sums (g[6], upper H[21], E, counter) by a
+// warp-shuffle -> shared-memory -> grid (last-block-done, fixed order => bit-reproducible) tree reduction.
+constexpr int kAccTerms = 29;
+constexpr int kAccStride = 32;
+constexpr int kAccThreads = 256;
+
+struct TrackIntr {
+    float fx_inv, fy_inv, cx, cy;  // RigidPointOptimizerOmp.cpp:48-52
+    int sampling, ws, hs;          // sampled grid size
+};
+
+template <int VARIANT>
+__global__ void __launch_bounds__(kAccThreads)
+accumulate_kernel(MapView m, FrameGeom g, TrackIntr ti, const Pose* __restrict__ pose_ptr,
+                  const float* __restrict__ depth, float* __restrict__ partials, Counters* ctr,
+                  float* __restrict__ out29) {
+    // pose_ptr: device-resident pose (kept on the device so a Gauss-Newton loop needs no host round trip)
+    float acc[kAccTerms];
+#pragma unroll
+    for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
+    __shared__ Pose pose;
+    if (threadIdx.x < 12) reinterpret_cast<float*>(&pose)[threadIdx.x] = reinterpret_cast<const float*>(pose_ptr)[threadIdx.x];
+    __syncthreads();
+    const float* R = pose.R;
+    const int total = ti.ws * ti.hs;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int ys = i / ti.ws, xs = i - ys * ti.ws;
+        const int x = xs * ti.sampling, y = ys * ti.sampling;
+        const float z = depth[(size_t)y * g.w + x];
+        if (z <= g.z_min || z >= g.z_max) continue;  // :72-73
+        const float x0 = ((float)x - ti.cx) * ti.fx_inv, y0 = ((float)y - ti.cy) * ti.fy_inv;  // :75-76
+        const float cx_ = x0 * z, cy_ = y0 * z;
+        const float px = dot3_rn(R[0], R[1], R[2], cx_, cy_, z) + pose.t[0];  // :78
+        const float py = dot3_rn(R[3], R[4], R[5], cx_, cy_, z) + pose.t[1];
+        const float pz = dot3_rn(R[6], R[7], R[8], cx_, cy_, z) + pose.t[2];
+        float phi, g0, g1, g2;
+        const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2);
+        if (w0 > 0.f) {
+            float J[6];
+            J[0] = g0; J[1] = g1; J[2] = g2;
+            J[3] = py * g2 - pz * g1;  // point.cross(grad), :86
+            J[4] = pz * g0 - px * g2;
+            J[5] = px * g1 - py * g0;
+            int o = 6;
+#pragma unroll
+            for (int a = 0; a < 6; ++a) {
+                acc[a] += phi * J[a];  // :87
+#pragma unroll
+                for (int b = a; b < 6; ++b) acc[o++] += J[a] * J[b];  // :88 (upper triangle)
+            }
+            acc[27] += phi * phi;  // :84
+            acc[28] += 1.f;        // :89
+        }
+    }
+    // warp tree
+#pragma unroll
+    for (int i = 0; i < kAccTerms; ++i) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], off);
+    }
+    __shared__ float sm[kAccThreads / 32][kAccStride];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < kAccTerms; ++i) sm[warp][i] = acc[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < kAccTerms) {
+        float s = 0.f;
+#pragma unroll
+        for (int wq = 0; wq < kAccThreads / 32; ++wq) s += sm[wq][threadIdx.x];
+        partials[(size_t)blockIdx.x * kAccStride + threadIdx.x] = s;
+    }
+    // grid stage: the last block to arrive sums all partials in block order
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int t = atomicInc(&ctr->ticket, gridDim.x - 1);  // wraps back to 0 for the next launch
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    // warp wq reduces terms wq, wq+8, ...; lanes stride over blocks, then a fixed-shape shuffle tree
+    for (int term = warp; term < kAccTerms; term += kAccThreads / 32) {
+        float s = 0.f;
+        for (int b = lane; b < (int)gridDim.x; b += 32) s += __ldcg(partials + (size_t)b * kAccStride + term);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        if (lane == 0) out29[term] = s;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Map iteration: count / compact voxels with weight > 0.
+template <int VARIANT>
+__global__ void __launch_bounds__(256)
+count_kernel(MapView m, unsigned long long* n_voxels, unsigned long long* n_blocks) {
+    // one warp per slot
+    const unsigned int warps_per_block = blockDim.x >> 5;
+    const unsigned int lane = threadIdx.x & 31;
+    unsigned long long cnt = 0, blk = 0;
+    for (unsigned int slot = blockIdx.x * warps_per_block + (threadIdx.x >> 5); slot <= m.cap_mask;
+         slot += gridDim.x * warps_per_block) {
+        if (m.keys[slot] == kEmptyKey) continue;
+        if (lane == 0) ++blk;
+        for (int v = lane; v < kBlockVoxels; v += 32) {
+            const size_t addr = (size_t)slot * kBlockVoxels + v;
+            const float W = VARIANT == 0 ? m.accW[addr] : m.acc2[addr].x;
+            cnt += W > 0.f ? 1 : 0;
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+    if (lane == 0) {
+        if (cnt) atomicAdd(n_voxels, cnt);
+        if (blk) atomicAdd(n_blocks, blk);
+    }
+}
+
+template <int VARIANT>
+__global__ void __launch_bounds__(256)
+download_kernel(MapView m, unsigned long long* cursor, long long max_n, int* __restrict__ keys,
+                float* __restrict__ dist, float* __restrict__ weight, float* __restrict__ grad) {
+    const unsigned int warps_per_block = blockDim.x >> 5;
+    const unsigned int lane = threadIdx.x & 31;
+    for (unsigned int slot = blockIdx.x * warps_per_block + (threadIdx.x >> 5); slot <= m.cap_mask;
+         slot += gridDim.x * warps_per_block) {
+        const unsigned long long key = m.keys[slot];
+        if (key == kEmptyKey) continue;
+        int bx, by, bz;
+        unpack_block(key, bx, by, bz);
+        for (int v = lane; v < kBlockVoxels; v += 32) {
+            const size_t addr = (size_t)slot * kBlockVoxels + v;
+            float W, S, gx = 0.f, gy = 0.f, gz = 0.f;
+            if (VARIANT == 0) { W = m.accW[addr]; const float4 a = m.acc4[addr]; S = a.x; gx = a.y; gy = a.z; gz = a.w; }
+            else { const float2 a = m.acc2[addr]; W = a.x; S = a.y; }
+            const bool live = W > 0.f;
+            const unsigned int mask = __ballot_sync(0xffffffffu, live);
+            if (!mask) continue;
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(cursor, (unsigned long long)__popc(mask));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (live) {
+                const long long o = (long long)base + __popc(mask & ((1u << lane) - 1));
+                if (o < max_n) {
+                    keys[3 * o] = (bx << 3) | (v & 7);
+                    keys[3 * o + 1] = (by << 3) | ((v >> 3) & 7);
+                    keys[3 * o + 2] = (bz << 3) | (v >> 6);
+                    dist[o] = S / W;
+                    weight[o] = W;
+                    grad[3 * o] = gx; grad[3 * o + 1] = gy; grad[3 * o + 2] = gz;
+                }
+            }
+        }
+    }
+}
+
+}  // namespace gsdf

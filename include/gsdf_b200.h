@@ -1,0 +1,134 @@
+/* gsdf_b200.h — C ABI of the B200-native Scan3D track+fuse hot path (libgsdf_b200.so).
+ *
+ * Drop-in boundary for c-sommer/gradient-sdf's depth-scanning path.  The reference has no FFI: its boundary is
+ * the C++ class surface consumed by cpp/depth_scanning/src/main_scan_3d.cpp:208-266.  Each entry point below
+ * names the reference interface it replaces (paths relative to /root/reference/cpp/include).  The host-side
+ * forwarding shells with the reference's class names live in gradient-sdf_b200/host/; INTEGRATION.md shows the
+ * binding a maintainer would add to the reference tree.
+ *
+ * Conventions: plain pointers and sizes only; every call returns a gsdf_status (0 = ok) and never throws;
+ * host buffers are borrowed for the duration of the call; one handle <-> one host thread <-> one device and one
+ * CUDA stream; a handle owns all its device memory.  Rotations are row-major 3x3 float, poses are 7 floats
+ * "tx ty tz qx qy qz qw" (the reference's pose-file order, img_loader/ImageLoader.h:231-259), camera-to-world.
+ * There is no CPU fallback: without a CUDA device gsdf_create fails with GSDF_ERR_CUDA.
+ */
+#ifndef GSDF_B200_H_
+#define GSDF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gsdf_map* gsdf_handle;
+
+typedef enum gsdf_status {
+    GSDF_OK = 0,
+    GSDF_ERR_INVALID = 1,   /* bad argument / null pointer / call order */
+    GSDF_ERR_CUDA = 2,      /* CUDA runtime error, see gsdf_last_error */
+    GSDF_ERR_CAPACITY = 3,  /* block hash full: samples would have been dropped (never silent) */
+    GSDF_ERR_NCCL = 4,
+    GSDF_ERR_NO_FRAME = 5   /* integrate/accumulate/track before a depth frame was set */
+} gsdf_status;
+
+enum { GSDF_GRAD_SDF = 0, GSDF_BASE_SDF = 1 };
+
+/* Replaces the constructor arguments of MapGradPixelSdf(float voxel_size, float T) / MapPixelSdf(float, float)
+ * (sdf_tracker/MapGradPixelSdf.h:99-103, MapPixelSdf.h:97-101), cv::NormalEstimator<float>(w, h, K, Size)
+ * (normals/NormalEstimator.h:158-165) and the constants of Sdf (sdf_tracker/Sdf.h:63-68). */
+typedef struct gsdf_config {
+    int32_t variant;        /* GSDF_GRAD_SDF | GSDF_BASE_SDF (main_scan_3d.cpp --scan-type) */
+    float voxel_size;       /* metres */
+    float truncation;       /* T in metres = trunc_factor * voxel_size computed in float (main_scan_3d.cpp:191) */
+    float z_min, z_max;     /* 0.5, 3.5 (Sdf.h:67-68) */
+    int32_t width, height;  /* depth image size (main_scan_3d.cpp:183 hard-codes 640x480) */
+    float K[9];             /* row-major intrinsics */
+    int32_t normal_window;  /* 11 (main_scan_3d.cpp:183) */
+    int32_t log2_capacity;  /* voxel-block hash slots = 2^log2_capacity blocks of 8^3 voxels; 0 -> default 17 */
+    int32_t device;         /* CUDA device ordinal */
+    int32_t world_size;     /* >1: map sharded by block key, this handle owns blocks with owner(key) == rank */
+    int32_t rank;
+} gsdf_config;
+
+typedef struct gsdf_integrate_stats {
+    int64_t points;   /* the reference's "points integrated" counter (MapGradPixelSdfOmp.cpp:125-129) */
+    int64_t updates;  /* (pixel,k) samples with w>0 committed by this rank = voxel updates */
+    int64_t blocks;   /* voxel blocks allocated so far on this rank */
+} gsdf_integrate_stats;
+
+/* -- lifetime ------------------------------------------------------------------------------------------- */
+gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out);
+gsdf_status gsdf_destroy(gsdf_handle h);
+const char* gsdf_last_error(gsdf_handle h); /* h may be NULL: error of the last failed gsdf_create */
+/* Empties the map (all voxels back to weight 0) without reallocating. */
+gsdf_status gsdf_reset(gsdf_handle h);
+
+/* -- cv::NormalEstimator<float> (normals/NormalEstimator.h) ------------------------------------------------ */
+/* cache(): computed at gsdf_create in double on the host exactly as NormalEstimator.h:81-154 and uploaded.
+ * gsdf_get_normal_cache returns the 11 float planes (x0, y0, x0/n^2, y0/n^2, 1/n^2, Q11, Q12, Q13, Q22, Q23,
+ * Q33), i.e. what x0_ptr()/y0_ptr()/n_sq_inv_ptr() expose (NormalEstimator.h:206-210) plus the private ones. */
+gsdf_status gsdf_get_normal_cache(gsdf_handle h, float* planes11);
+/* compute(depth, nx, ny, nz) (NormalEstimator.h:179-204) on the current frame; planes of width*height floats. */
+gsdf_status gsdf_compute_normals(gsdf_handle h, float* nx, float* ny, float* nz);
+
+/* -- the depth frame (cv::Mat depth, CV_32FC1 metres, 0 = invalid, img_loader/ImageLoader.h:159-175) ------- */
+/* Host buffer -> device (async on the handle's stream, complete before the next call that uses it). */
+gsdf_status gsdf_upload_frame(gsdf_handle h, const float* depth_host);
+/* Frame already resident in HBM (device pointer, width*height floats, must stay valid while it is current). */
+gsdf_status gsdf_set_frame_device(gsdf_handle h, const float* depth_dev);
+
+/* -- Sdf::update / Sdf::setup (sdf_tracker/Sdf.h:117-121; MapGradPixelSdfOmp.cpp:44-130,
+ *    MapPixelSdfOmp.cpp:116-195): fuse the current frame at pose (R, t) = (pose.rotationMatrix(),
+ *    pose.translation()).  stats may be NULL (then no device->host read happens). */
+gsdf_status gsdf_integrate(gsdf_handle h, const float* R9, const float* t3, gsdf_integrate_stats* stats);
+/* Same with the pose as 7 floats; R is derived as Sophus/Eigen do (quaternion normalised, toRotationMatrix). */
+gsdf_status gsdf_integrate_pose(gsdf_handle h, const float* pose7, gsdf_integrate_stats* stats);
+
+/* -- RigidPointOptimizer (sdf_tracker/RigidOptimizer.h:90-110, RigidPointOptimizerOmp.cpp:44-106) ---------- */
+/* One pass of the per-pixel loop (RigidPointOptimizerOmp.cpp:69-91) over the current frame at (R, t):
+ * out29 = g[6], upper triangle of H row-major [21], E, counter.  With world_size > 1 the partials of all
+ * ranks are summed (NCCL) so every rank receives the same totals. */
+gsdf_status gsdf_accumulate(gsdf_handle h, const float* R9, const float* t3, int32_t sampling, float* out29);
+/* optimize(depth, K): Gauss-Newton from pose7 (updated in place) for at most max_iters iterations with the
+ * reference's stopping rule |xi|^2 < conv_threshold^2 (last xi not applied) and NaN guard.
+ * *converged = the bool optimize() returns; *iters_used = k at convergence (or max_iters). */
+gsdf_status gsdf_track(gsdf_handle h, float* pose7, int32_t max_iters, float conv_threshold, float damping,
+                       int32_t* converged, int32_t* iters_used);
+
+/* -- Sdf::weights / Sdf::tsdf (sdf_tracker/Sdf.h:113-115; MapGradPixelSdf.h:109-125; MapPixelSdf.h:107-143,
+ *    MapPixelSdfOmp.cpp:44-113), batched: per point w = weights(p); phi, grad = tsdf(p, &grad) if w > 0 else 0.
+ *    pts n*3, phi n, grad n*3, w n (host pointers). */
+gsdf_status gsdf_query(gsdf_handle h, const float* pts, int64_t n, float* phi, float* grad, float* w);
+
+/* -- map access (getSdf/get_tsdf, MapGradPixelSdf.h:127-138; the writers iterate the map,
+ *    MapGradPixelSdfOmp.cpp:144-151,189,285) ---------------------------------------------------------------- */
+gsdf_status gsdf_voxel_count(gsdf_handle h, int64_t* n_voxels, int64_t* n_blocks);
+/* Voxels with weight > 0 (this rank's shard): keys max_n*3 int32, dist, weight max_n, grad max_n*3 (zeros for
+ * base-sdf).  *n_out = number written; GSDF_ERR_INVALID if max_n is too small.  Order unspecified. */
+gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* dist, float* weight, float* grad,
+                          int64_t* n_out);
+
+/* -- pose algebra used by the tracker (Sophus::SE3f semantics: so3.hpp:297-303,325-339,356-366,583-619,
+ *    se3.hpp:761-782; Eigen toRotationMatrix), exported so callers without Sophus get identical poses -------- */
+void gsdf_pose_matrix(const float* pose7, float* R9, float* pose7_normalised /* may be NULL */);
+void gsdf_pose_apply_increment(const float* pose7_in, const float* xi6, float* pose7_out); /* exp(-xi) * pose */
+/* xi = LLT(H)^-1 g, H row-major 6x6 (RigidPointOptimizerOmp.cpp:93) */
+void gsdf_llt_solve6(const float* H36, const float* g6, float* xi6);
+
+/* -- plumbing ------------------------------------------------------------------------------------------- */
+gsdf_status gsdf_synchronize(gsdf_handle h);
+/* The handle's cudaStream_t (as void*), for CUDA-event timing and for ordering caller-owned device buffers. */
+void* gsdf_stream(gsdf_handle h);
+/* Kernel launches issued by this handle since creation (bench.py reports it as gpu_launches). */
+int64_t gsdf_launch_count(gsdf_handle h);
+/* Multi-GPU: rank 0 calls gsdf_comm_unique_id, the 128 bytes are distributed by the caller (any transport),
+ * then every rank calls gsdf_comm_init on its handle (cfg.world_size/rank).  Needed only for world_size > 1. */
+gsdf_status gsdf_comm_unique_id(uint8_t id128[128]);
+gsdf_status gsdf_comm_init(gsdf_handle h, const uint8_t id128[128]);
+const char* gsdf_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSDF_B200_H_ */

@@ -31,7 +31,7 @@ def to_mm(frames):
     return depth_mm
 
 
-def run(variant: int, voxel_size: float, trunc: float, name: str, free_run: bool = True) -> None:
+def run(variant: int, voxel_size: float, trunc: float, name: str, free_run=None) -> None:
     # kernel-level frames: the reference's own orbit step (100 frames per turn ~ matlab/poses.txt's 90)
     frames, poses, K, _ = synth.make_sequence(100, W, H)
     frames, poses = frames[:N_INJECT + 1], poses[:N_INJECT + 1]
@@ -72,11 +72,18 @@ def run(variant: int, voxel_size: float, trunc: float, name: str, free_run: bool
         print(name, "voxels", len(out["keys"]), "size %.0f KB" % (path.stat().st_size / 1024))
         return
 
-    # ---- L3: free-running, as main_scan_3d.cpp:208-266 without a pose file (frame 0 fused at identity);
-    # gentler camera motion (400 frames per turn: ~3 cm, 0.9 degrees per frame) so that the tracker converges
-    frames = synth.make_sequence(400, W, H)[0][:N_FRAMES]
+    # ---- L3: free-running, as main_scan_3d.cpp:208-266 without a pose file (frame 0 fused at identity).
+    # The grad-sdf tracker's 1e-3 stopping test is borderline on noisy data (the reference itself is not
+    # reproducible run to run there, SURVEY.md "three facts"), so the golden free run uses settings under which
+    # the reference converges with margin (2-3 iterations per frame); the borderline regime is covered by a
+    # tolerance test against the oracle run live.
+    fw, fh, fnoise, fturn, fvs = free_run
+    frames, _, Kf, _ = synth.make_sequence(fturn, fw, fh, noise=fnoise)
+    frames = frames[:N_FRAMES]
     out["free_depth_mm"] = to_mm(frames)
-    r = po.RefScan(variant, voxel_size, trunc, W, H, K)
+    out.update(free_K=Kf, free_width=fw, free_height=fh, free_voxel_size=np.float32(fvs))
+    W_, H_, K, voxel_size = fw, fh, Kf, fvs
+    r = po.RefScan(variant, voxel_size, trunc, W_, H_, K)
     ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
     r.update(frames[0], ident)
     r.set_pose(ident)
@@ -101,6 +108,6 @@ def run(variant: int, voxel_size: float, trunc: float, name: str, free_run: bool
 
 if __name__ == "__main__":
     assert po.have_ref(), "build oracle/_ref first (make -C oracle ref)"
-    run(0, 0.02, 5.0, "grad_160x120_2cm_t5")
-    run(1, 0.02, 5.0, "base_160x120_2cm_t5")
-    run(0, 0.01, 10.0, "grad_160x120_1cm_t10", free_run=False)
+    run(0, 0.02, 5.0, "grad_160x120_2cm_t5", free_run=(320, 240, False, 800, 0.01))
+    run(1, 0.02, 5.0, "base_160x120_2cm_t5", free_run=(160, 120, True, 400, 0.02))
+    run(0, 0.01, 10.0, "grad_160x120_1cm_t10")
