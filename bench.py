@@ -1,0 +1,427 @@
+#!/usr/bin/env python
+"""bench.py — Scan3D track+fuse throughput on B200 (metric and config of BASELINE.json).
+
+A "step" is one pass of the hot path over one synthetic 640x480 depth frame: track the camera against the map
+(RigidPointOptimizer::optimize) and, if converged, fuse the frame (Sdf::update) — the loop body of
+cpp/depth_scanning/src/main_scan_3d.cpp:255-265.  Frame 0 is fused at the identity pose before the warm-up.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--variant base|grad]
+
+One JSON line on stdout (rank 0).  `value` = frames/s with the frames resident in HBM; `e2e` = the same loop fed
+from pinned HOST buffers (H2D of every frame and D2H of every result inside the timed region).
+`--impl reference` times the reference's own OMP implementation (oracle/_ref, else the C port) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+W_IMG, H_IMG = 640, 480
+FRAMES_PER_TURN = 100  # ~ matlab/poses.txt: 90 poses per 360 degree orbit
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=90)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--variant", default="base", choices=["base", "grad"])
+    ap.add_argument("--voxel-size", type=float, default=0.01)
+    ap.add_argument("--trunc", type=float, default=5.0)
+    ap.add_argument("--log2-capacity", type=int, default=17)
+    ap.add_argument("--no-l2-flush", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=20.0, help="bound of the cpu_baseline leg")
+    ap.add_argument("--ref-budget-s", type=float, default=150.0, help="bound of the --impl reference run")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary grad-sdf measurement")
+    return ap.parse_args()
+
+
+def workload_name(variant, vs, trunc):
+    tag = "C2" if (variant == "base" and abs(vs - 0.01) < 1e-9) else "custom"
+    return (f"{tag}: Scan3D {variant}-sdf track+fuse, synthetic 5-sphere RenderSpheres-style sequence, "
+            f"{W_IMG}x{H_IMG} depth, {vs * 1000:g} mm voxels, trunc {trunc:g}")
+
+
+def make_frames(n_needed):
+    """Seeded synthetic sequence (cached under /tmp so that both arms of one box share the generation cost)."""
+    import gsdf_loader
+    gsdf_loader.load()
+    import importlib
+    synth = importlib.import_module("gradient_sdf_b200.synth")
+    n = max(FRAMES_PER_TURN, n_needed)
+    cache = Path(f"/tmp/gsdf_bench_seq_{n}_{W_IMG}x{H_IMG}.npz")
+    if cache.exists():
+        try:
+            z = np.load(cache)
+            return z["frames"][:n_needed], z["poses"][:n_needed], z["K"]
+        except Exception:
+            pass
+    frames, poses, K, _ = synth.make_sequence(n, W_IMG, H_IMG, turn=2 * np.pi * n / FRAMES_PER_TURN)
+    try:
+        tmp = cache.with_suffix(f".{os.getpid()}.npz")
+        np.savez(tmp, frames=frames, poses=poses, K=K)
+        os.replace(tmp, cache)
+    except Exception:
+        pass
+    return frames[:n_needed], poses[:n_needed], K
+
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.p = None
+        self.idx = gpu_index
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.QUERY}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            out = self.p.communicate(timeout=5)[0]
+        except Exception:
+            out = ""
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peak():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel):
+    p = ROOT / "profiles" / "ncu_traffic.json"
+    if p.exists():
+        try:
+            return json.loads(p.read_text()).get(kernel)
+        except Exception:
+            return None
+    return None
+
+
+# --------------------------------------------------------------------------------------------------------------
+def cpu_reference_run(variant, vs, trunc, frames, K, max_steps, warmup, budget_s):
+    """Times the reference's OMP track+fuse loop on the host cores (test infrastructure used as a BASELINE only)."""
+    import gsdf_loader
+    po = gsdf_loader.load_oracle()
+    v = 0 if variant == "grad" else 1
+    if po.have_ref():
+        scan, kind = po.RefScan(v, vs, trunc, W_IMG, H_IMG, K), "reference"
+        cores = po.threads_in_use()
+        note = (f"oracle/_ref (reference OMP TUs, -O2 -fopenmp, shim OpenCV), {cores} host threads for the first "
+                f"fusion then 4 (RigidPointOptimizerOmp.cpp:68 pins omp_set_num_threads(4))")
+    else:
+        scan, kind, cores = po.Oracle(v, vs, trunc, W_IMG, H_IMG, K), "port"
+        cores = 1
+        note = "oracle/gsdf_oracle.c (scalar C port), 1 thread"
+    ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+    scan.update(frames[0], ident)
+    scan.set_pose(ident)
+    t_all0 = time.perf_counter()
+    done, t_track, t_fuse, t_total = 0, 0.0, 0.0, 0.0
+    for i in range(1, min(len(frames), 1 + warmup + max_steps)):
+        t0 = time.perf_counter()
+        conv, _ = scan.optimize(frames[i])
+        t1 = time.perf_counter()
+        if conv:
+            scan.update(frames[i], scan.get_pose())
+        t2 = time.perf_counter()
+        if i > warmup:
+            done += 1
+            t_track += t1 - t0
+            t_fuse += t2 - t1
+            t_total += t2 - t0
+        if time.perf_counter() - t_all0 > budget_s and done >= 2:
+            break
+    fps = done / t_total if t_total > 0 else 0.0
+    sample = f"{done} timed frames after {min(warmup, max(0, len(frames) - 2))} warm-up frames of the same sequence; {note}"
+    return {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample,
+            "track_s_per_frame": t_track / max(1, done), "fuse_s_per_frame": t_fuse / max(1, done)}, done, t_total
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_needed = 1 + args.warmup + args.steps
+    frames, poses, K = make_frames(n_needed)
+    base, done, t_total = cpu_reference_run(args.variant, args.voxel_size, args.trunc, frames, K, args.steps,
+                                            args.warmup, args.ref_budget_s)
+    line = {
+        "impl": "reference", "metric": "scan3d_track_fuse_frames_per_s", "value": base["value"], "unit": "frames/s",
+        "n_gpus": args.gpus, "steps": done, "requested_steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * t_total / max(1, done), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.variant, args.voxel_size, args.trunc), "width": W_IMG,
+                   "height": H_IMG, "voxel_size": args.voxel_size, "trunc": args.trunc, "variant": args.variant},
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import gsdf_loader
+    pkg = gsdf_loader.load()
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    n_needed = 1 + args.warmup + args.steps
+    frames, poses, K = make_frames(n_needed)
+    host_frames = torch.from_numpy(frames).pin_memory()
+    dev_frames = host_frames.to("cuda", non_blocking=False)
+    flush_buf = None if args.no_l2_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def make_map(variant):
+        nest = pkg.NormalEstimator(W_IMG, H_IMG, K, 11)
+        cls = pkg.MapGradPixelSdf if variant == "grad" else pkg.MapPixelSdf
+        vs = np.float32(args.voxel_size)
+        sdf = cls(vs, np.float32(args.trunc) * vs, nest, log2_capacity=args.log2_capacity, device=local_rank,
+                  world_size=world, rank=rank)
+        if world > 1:
+            idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                import ctypes as C
+                buf = (C.c_uint8 * 128)()
+                assert pkg.lib().gsdf_comm_unique_id(buf) == 0
+                idt.copy_(torch.tensor(list(buf), dtype=torch.uint8))
+            dist.broadcast(idt, 0)
+            sdf.comm_init(bytes(idt.cpu().tolist()))
+        return sdf
+
+    ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+
+    def run_pass(sdf, mode, profile=False):
+        """Frame 0 at identity, W warm-up steps, K timed steps.  mode 'dev' = frames resident in HBM,
+        'host' = pinned host buffers through gsdf_upload_frame."""
+        sdf.reset()
+        sdf.profile_enable(False)
+        opt = pkg.RigidPointOptimizer(sdf)
+        opt.set_pose(ident)
+        ext = torch.cuda.ExternalStream(sdf.stream)
+        host_np = host_frames.numpy()
+
+        def set_frame(f):
+            if mode == "dev":
+                sdf.set_frame_device(dev_frames[f].data_ptr())
+            else:
+                sdf.upload_frame(host_np[f])
+
+        set_frame(0)
+        sdf.update(None, ident)
+        st = {"updates": 0, "valid": 0, "iters": 0, "conv": 0, "t_ms": 0.0, "t_fuse_ms": 0.0}
+
+        def step(f, timed):
+            if flush_buf is not None:
+                flush_buf.zero_()
+                torch.cuda.synchronize()
+            if timed:
+                e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+                e0.record(ext)
+            set_frame(f)
+            conv = opt.optimize(None)
+            if timed:
+                e1.record(ext)
+            upd = 0
+            if conv:
+                _, upd, _ = sdf.update(None, opt.pose(), stats=True, stored=True)
+            if timed:
+                e2.record(ext)
+                sdf.synchronize()
+                e2.synchronize()
+                st["t_ms"] += e0.elapsed_time(e2)
+                st["t_fuse_ms"] += e1.elapsed_time(e2)
+                st["updates"] += upd
+                st["iters"] += opt.last_iterations + (0 if conv else 0)
+                st["conv"] += int(conv)
+
+        for f in range(1, 1 + args.warmup):
+            step(f, False)
+        if profile:
+            sdf.profile_enable(True)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        launches0 = sdf.launch_count
+        it0, valid0 = sdf.track_stats()
+        wall0 = time.perf_counter()
+        for f in range(1 + args.warmup, 1 + args.warmup + args.steps):
+            step(f, True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        st["wall_s"] = time.perf_counter() - wall0
+        st["launches"] = sdf.launch_count - launches0
+        it1, valid1 = sdf.track_stats()
+        st["track_iters"], st["track_valid"] = it1 - it0, valid1 - valid0
+        st["pose_err_m"] = float(np.abs(opt.pose()[:3]).max())  # diagnostic only
+        st["final_pose"] = opt.pose().tolist()
+        return st
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def measure(variant):
+        sdf = make_map(variant)
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        a = run_pass(sdf, "dev")
+        b = run_pass(sdf, "host")
+        clocks = sampler.stop() if sampler else None
+        c = run_pass(sdf, "dev", profile=True)
+        n_f, ms_f = sdf.profile_read(1)
+        n_a, ms_a = sdf.profile_read(2)
+        n_n, ms_n = sdf.profile_read(0)
+        nv, nb = sdf.voxel_count()
+        K_steps = args.steps
+        t_dev = max_over_ranks(a["t_ms"])
+        t_host = max_over_ranks(b["t_ms"])
+        upd_total = sum_over_ranks(a["updates"])
+        t_fuse = max_over_ranks(a["t_fuse_ms"])
+        npx = W_IMG * H_IMG
+        # algorithmic bytes: fusion W*H*4 + N_upd*b_v ; tracking W*H*4 + N_valid*b_t per iteration
+        b_v = 40 if variant == "grad" else 16
+        b_t = 20 if variant == "grad" else 36
+        fuse_bytes = n_f * npx * 4 + c["updates"] * b_v
+        acc_bytes = n_a * npx * 4 + c["track_valid"] * b_t
+        res = {
+            "variant": variant, "frames_per_s": 1e3 * K_steps / t_dev, "ms_per_step": t_dev / K_steps,
+            "e2e_frames_per_s": 1e3 * K_steps / t_host, "voxel_updates_per_s": 1e3 * upd_total / max(t_fuse, 1e-9),
+            "updates_per_frame": upd_total / max(1, a["conv"]), "converged_steps": a["conv"],
+            "gn_iterations": a["iters"], "launches": a["launches"], "voxels": nv, "blocks": nb,
+            "kernel_ms": {"normals": [n_n, ms_n], "fuse": [n_f, ms_f], "accumulate": [n_a, ms_a]},
+            "fuse_bytes": fuse_bytes, "acc_bytes": acc_bytes, "fuse_GBps": fuse_bytes / max(ms_f, 1e-9) / 1e6 if n_f else None,
+            "clocks": clocks, "wall_s_dev": a["wall_s"], "wall_s_host": b["wall_s"], "b_v": b_v, "b_t": b_t,
+            "final_pose": a["final_pose"],
+        }
+        sdf.close()
+        return res
+
+    main = measure(args.variant)
+    extra = None
+    if not args.no_extra and world == 1:
+        other = "grad" if args.variant == "base" else "base"
+        extra = measure(other)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    (n_f, ms_f), (n_a, ms_a) = main["kernel_ms"]["fuse"], main["kernel_ms"]["accumulate"]
+    npx = W_IMG * H_IMG
+    if ms_f >= ms_a or n_a == 0:
+        kname, per_launch_bytes, per_launch_ms = f"fuse_kernel<{main['variant']}>", main["fuse_bytes"] / max(1, n_f), ms_f / max(1, n_f)
+    else:
+        kname, per_launch_bytes, per_launch_ms = (f"accumulate_kernel<{main['variant']}>",
+                                                  main["acc_bytes"] / max(1, n_a), ms_a / max(1, n_a))
+    achieved = per_launch_bytes / max(per_launch_ms, 1e-12) / 1e6  # GB/s
+    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "peak_source": peak_src,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(kname),
+                "algorithmic_bytes_per_launch": per_launch_bytes, "us_per_launch": 1e3 * per_launch_ms,
+                "kernel_share_of_step": {"fuse": ms_f / (main["ms_per_step"] * args.steps),
+                                         "accumulate": ms_a / (main["ms_per_step"] * args.steps)}}
+
+    cpu_base = None
+    if world == 1:
+        cpu_base, _, _ = cpu_reference_run(args.variant, args.voxel_size, args.trunc, frames, K, args.steps,
+                                           args.warmup, args.cpu_budget_s)
+
+    iters_per_step = main["gn_iterations"] / max(1, args.steps)
+    line = {
+        "metric": "scan3d_track_fuse_frames_per_s", "value": main["frames_per_s"], "unit": "frames/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": main["ms_per_step"],
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.variant, args.voxel_size, args.trunc), "width": W_IMG,
+                   "height": H_IMG, "voxel_size": args.voxel_size, "trunc": args.trunc, "variant": args.variant,
+                   "parallelism": "single GPU" if world == 1 else f"voxel-block hash sharded over {world} GPUs, "
+                   "29-float NCCL allreduce per Gauss-Newton iteration",
+                   "l2": "no flush (--no-l2-flush)" if args.no_l2_flush else
+                   "L2 flushed (256 MiB memset) before every step, outside the timed intervals",
+                   "timing": "sum over steps of CUDA-event intervals on the library's stream (host launch gaps "
+                             "included), max over ranks"},
+        "voxel_updates_per_s": main["voxel_updates_per_s"], "updates_per_frame": main["updates_per_frame"],
+        "converged_steps": main["converged_steps"], "gn_iterations_per_step": iters_per_step,
+        "map": {"voxels": main["voxels"], "blocks": main["blocks"]},
+        "e2e": {"value": main["e2e_frames_per_s"], "unit": "frames/s", "h2d_bytes_per_step": npx * 4,
+                "d2h_bytes_per_step": int(round(iters_per_step * 29 * 4 + 32))},
+        "gpu_launches": main["launches"], "clocks": main["clocks"], "roofline": roofline, "cpu_baseline": cpu_base,
+        "kernel_ms_total": main["kernel_ms"],
+    }
+    if extra:
+        line["extra"] = {k: extra[k] for k in ("variant", "frames_per_s", "e2e_frames_per_s", "voxel_updates_per_s",
+                                               "updates_per_frame", "converged_steps", "gn_iterations", "kernel_ms",
+                                               "fuse_GBps", "voxels")}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

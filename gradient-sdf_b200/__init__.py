@@ -33,7 +33,8 @@ EXPORTS = [
     "gsdf_create", "gsdf_destroy", "gsdf_last_error", "gsdf_reset", "gsdf_get_normal_cache", "gsdf_compute_normals",
     "gsdf_upload_frame", "gsdf_set_frame_device", "gsdf_integrate", "gsdf_integrate_pose", "gsdf_accumulate",
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
-    "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
+    "gsdf_profile_read", "gsdf_track_stats", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -99,6 +100,9 @@ def lib() -> C.CDLL:
     L.gsdf_stream.argtypes = [H]
     L.gsdf_launch_count.restype = C.c_int64
     L.gsdf_launch_count.argtypes = [H]
+    L.gsdf_track_stats.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    L.gsdf_profile_enable.argtypes = [H, C.c_int32]
+    L.gsdf_profile_read.argtypes = [H, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
     L.gsdf_comm_unique_id.argtypes = [C.POINTER(C.c_uint8)]
     L.gsdf_comm_init.argtypes = [H, C.POINTER(C.c_uint8)]
     L.gsdf_version.restype = C.c_char_p
@@ -201,6 +205,21 @@ class Sdf:
     def launch_count(self) -> int:
         return int(self.L.gsdf_launch_count(self.h))
 
+    def track_stats(self):
+        """(cumulative Gauss-Newton iterations, cumulative contributing pixels) of gsdf_track on this handle."""
+        a, b = C.c_int64(0), C.c_int64(0)
+        self._check(self.L.gsdf_track_stats(self.h, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
+
+    def profile_enable(self, on: bool = True):
+        self._check(self.L.gsdf_profile_enable(self.h, 1 if on else 0))
+
+    def profile_read(self, kind: int):
+        """(launches, total_ms) of kernel kind 0 = normals, 1 = fuse, 2 = accumulate since profile_enable."""
+        n, ms = C.c_int64(0), C.c_double(0.0)
+        self._check(self.L.gsdf_profile_read(self.h, kind, C.byref(n), C.byref(ms)))
+        return int(n.value), float(ms.value)
+
     def comm_init(self, id128: bytes):
         buf = (C.c_uint8 * 128).from_buffer_copy(id128)
         self._check(self.L.gsdf_comm_init(self.h, buf))
@@ -228,11 +247,13 @@ class Sdf:
         return n
 
     # -- Sdf::update / setup
-    def update(self, depth, pose7, stats: bool = True):
-        """Sdf::update(color, depth, K, pose, NEst): depth=None fuses the frame already set."""
+    def update(self, depth, pose7, stats: bool = True, stored: bool = False):
+        """Sdf::update(color, depth, K, pose, NEst): depth=None fuses the frame already set.
+        stored=False: pose7 is raw and goes through the SE3(quaternion, t) constructor (normalised once);
+        stored=True: pose7 is an SE3 as the tracker holds it (RigidPointOptimizer.pose()), used as is."""
         if depth is not None:
             self.upload_frame(depth)
-        p = _f32(pose7)
+        p = _f32(pose7) if stored else pose_matrix(pose7)[1]
         st = IntegrateStats()
         self._check(self.L.gsdf_integrate_pose(self.h, _fp(p), C.byref(st) if stats else None))
         return (st.points, st.updates, st.blocks) if stats else None

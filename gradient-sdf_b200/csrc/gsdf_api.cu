@@ -76,6 +76,11 @@ struct gsdf_map {
     std::vector<float> h_planes;
     int sm_count = 148;
     int64_t launches = 0;
+    int64_t track_iterations = 0, track_valid = 0;  // cumulative, for bytes-per-launch accounting
+    // per-kernel CUDA-event timing (off by default): pairs recorded around each launch, resolved on read
+    bool profiling = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[GSDF_PROF_KINDS];
+    size_t prof_used[GSDF_PROF_KINDS] = {0, 0, 0};
     ncclComm_t comm = nullptr;
     std::string err;
 };
@@ -225,6 +230,23 @@ gsdf_status check_launch(gsdf_map* h, const char* what) {
     return GSDF_OK;
 }
 
+struct ProfScope {
+    gsdf_map* h; int kind; cudaEvent_t stop = nullptr;
+    ProfScope(gsdf_map* h_, int kind_) : h(h_), kind(kind_) {
+        if (!h->profiling) return;
+        auto& v = h->prof_events[kind];
+        if (h->prof_used[kind] == v.size()) {
+            cudaEvent_t a, b;
+            cudaEventCreate(&a); cudaEventCreate(&b);
+            v.push_back({a, b});
+        }
+        auto& pr = v[h->prof_used[kind]++];
+        cudaEventRecord(pr.first, h->stream);
+        stop = pr.second;
+    }
+    ~ProfScope() { if (stop) cudaEventRecord(stop, h->stream); }
+};
+
 gsdf_status ensure_normals(gsdf_map* h) {
     if (!h->d_depth) { h->err = "no depth frame set"; return GSDF_ERR_NO_FRAME; }
     if (h->normals_valid) return GSDF_OK;
@@ -233,6 +255,7 @@ gsdf_status ensure_normals(gsdf_map* h) {
     const int tw = NT_W + 2 * r, th = NT_H + 2 * r;
     const size_t smem = ((sizeof(float) * 3 * tw * th + 7) & ~size_t(7)) + sizeof(double) * 3 * th * NT_W;
     dim3 grid((w + NT_W - 1) / NT_W, (ht + NT_H - 1) / NT_H), block(NT_W, NT_H);
+    ProfScope prof(h, GSDF_PROF_NORMALS);
     normals_kernel<<<grid, block, smem, h->stream>>>(h->d_depth, h->d_planes + 2 * n, h->d_planes + 3 * n,
                                                      h->d_planes + 4 * n, h->d_planes + 5 * n, h->d_normals,
                                                      h->d_normals + n, h->d_normals + 2 * n, w, ht, r);
@@ -261,6 +284,7 @@ void free_all(gsdf_map* h) {
     cudaFree(h->d_planes); cudaFree(h->d_depth_own); cudaFree(h->d_normals); cudaFree(h->d_ctr);
     cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
+    for (auto& v : h->prof_events) for (auto& pr : v) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -314,6 +338,7 @@ gsdf_status accumulate_device(gsdf_map* h, int sampling) {
     int blocks = (total + kAccThreads - 1) / kAccThreads;
     if (blocks > h->acc_blocks) blocks = h->acc_blocks;
     gsdf_status s = by_variant(h, [&](auto V) {
+        ProfScope prof(h, GSDF_PROF_ACCUMULATE);
         accumulate_kernel<decltype(V)::value><<<blocks, kAccThreads, 0, h->stream>>>(
             h->view, h->geom, ti, h->d_pose, h->d_depth, h->d_partials, h->d_ctr, h->d_out29);
         return check_launch(h, "accumulate_kernel");
@@ -450,6 +475,7 @@ gsdf_status gsdf_integrate(gsdf_handle h, const float* R9, const float* t3, gsdf
     const size_t np = (size_t)n;
     const int blocks = (n + 255) / 256;
     s = by_variant(h, [&](auto V) {
+        ProfScope prof(h, GSDF_PROF_FUSE);
         fuse_kernel<decltype(V)::value><<<blocks, 256, 0, h->stream>>>(
             h->view, h->geom, pose, h->d_depth, h->d_normals, h->d_normals + np, h->d_normals + 2 * np, h->d_planes,
             h->d_planes + np, h->d_planes + 4 * np, h->d_ctr);
@@ -473,9 +499,9 @@ gsdf_status gsdf_integrate(gsdf_handle h, const float* R9, const float* t3, gsdf
 
 gsdf_status gsdf_integrate_pose(gsdf_handle h, const float* pose7, gsdf_integrate_stats* stats) {
     if (!h || !pose7) return GSDF_ERR_INVALID;
-    float R[9], pn[7];
-    gsdf_pose_matrix(pose7, R, pn);
-    return gsdf_integrate(h, R, pn, stats);
+    float R[9];
+    quat_to_R(pose7 + 3, R);  // pose.rotationMatrix() of a stored SE3: no renormalisation
+    return gsdf_integrate(h, R, pose7, stats);
 }
 
 gsdf_status gsdf_accumulate(gsdf_handle h, const float* R9, const float* t3, int32_t sampling, float* out29) {
@@ -502,6 +528,8 @@ gsdf_status gsdf_track(gsdf_handle h, float* pose7, int32_t max_iters, float con
         quat_to_R(pose7 + 3, R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
         gsdf_status s = gsdf_accumulate(h, R, pose7, 1, out);
         if (s != GSDF_OK) return s;
+        h->track_iterations++;
+        h->track_valid += (int64_t)out[28];
         int o = 6;
         for (int a = 0; a < 6; ++a)
             for (int b = a; b < 6; ++b) { H[6 * a + b] = out[o]; H[6 * b + a] = out[o]; ++o; }
@@ -648,6 +676,35 @@ gsdf_status gsdf_synchronize(gsdf_handle h) {
     if (!h) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
     return check_overflow(h);
+}
+
+gsdf_status gsdf_track_stats(gsdf_handle h, int64_t* iterations, int64_t* valid_pixels) {
+    if (!h) return GSDF_ERR_INVALID;
+    if (iterations) *iterations = h->track_iterations;
+    if (valid_pixels) *valid_pixels = h->track_valid;
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_profile_enable(gsdf_handle h, int32_t on) {
+    if (!h) return GSDF_ERR_INVALID;
+    h->profiling = on != 0;
+    for (int k = 0; k < GSDF_PROF_KINDS; ++k) h->prof_used[k] = 0;
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_profile_read(gsdf_handle h, int32_t kind, int64_t* launches, double* total_ms) {
+    if (!h || kind < 0 || kind >= GSDF_PROF_KINDS || !launches || !total_ms) return GSDF_ERR_INVALID;
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    double tot = 0.0;
+    for (size_t i = 0; i < h->prof_used[kind]; ++i) {
+        float ms = 0.f;
+        CUDA_TRY(h, cudaEventElapsedTime(&ms, h->prof_events[kind][i].first, h->prof_events[kind][i].second));
+        tot += ms;
+    }
+    *launches = (int64_t)h->prof_used[kind];
+    *total_ms = tot;
+    return GSDF_OK;
 }
 
 void* gsdf_stream(gsdf_handle h) { return h ? (void*)h->stream : nullptr; }

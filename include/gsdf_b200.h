@@ -82,7 +82,8 @@ gsdf_status gsdf_set_frame_device(gsdf_handle h, const float* depth_dev);
  *    MapPixelSdfOmp.cpp:116-195): fuse the current frame at pose (R, t) = (pose.rotationMatrix(),
  *    pose.translation()).  stats may be NULL (then no device->host read happens). */
 gsdf_status gsdf_integrate(gsdf_handle h, const float* R9, const float* t3, gsdf_integrate_stats* stats);
-/* Same with the pose as 7 floats; R is derived as Sophus/Eigen do (quaternion normalised, toRotationMatrix). */
+/* Same with the pose as a stored Sophus::SE3f (7 floats, UNIT quaternion, e.g. the output of gsdf_track or of
+ * gsdf_pose_matrix): R = pose.rotationMatrix() without renormalising, as main_scan_3d.cpp:263 passes pOpt->pose(). */
 gsdf_status gsdf_integrate_pose(gsdf_handle h, const float* pose7, gsdf_integrate_stats* stats);
 
 /* -- RigidPointOptimizer (sdf_tracker/RigidOptimizer.h:90-110, RigidPointOptimizerOmp.cpp:44-106) ---------- */
@@ -122,6 +123,15 @@ gsdf_status gsdf_synchronize(gsdf_handle h);
 void* gsdf_stream(gsdf_handle h);
 /* Kernel launches issued by this handle since creation (bench.py reports it as gpu_launches). */
 int64_t gsdf_launch_count(gsdf_handle h);
+/* Cumulative Gauss-Newton iterations run by gsdf_track on this handle and the pixels that contributed to them
+ * (the reference's `counter`, RigidPointOptimizerOmp.cpp:66,89), for bytes-per-launch accounting. */
+gsdf_status gsdf_track_stats(gsdf_handle h, int64_t* iterations, int64_t* valid_pixels);
+/* Per-kernel device timing (the reference's only metrics are Timer tic/toc prints, Timer.h:59-78): when
+ * enabled, a CUDA-event pair brackets every launch of that kind on the handle's stream; gsdf_profile_read
+ * synchronises and returns the launches and their summed duration since gsdf_profile_enable(h, 1). */
+enum { GSDF_PROF_NORMALS = 0, GSDF_PROF_FUSE = 1, GSDF_PROF_ACCUMULATE = 2, GSDF_PROF_KINDS = 3 };
+gsdf_status gsdf_profile_enable(gsdf_handle h, int32_t on);
+gsdf_status gsdf_profile_read(gsdf_handle h, int32_t kind, int64_t* launches, double* total_ms);
 /* Multi-GPU: rank 0 calls gsdf_comm_unique_id, the 128 bytes are distributed by the caller (any transport),
  * then every rank calls gsdf_comm_init on its handle (cfg.world_size/rank).  Needed only for world_size > 1. */
 gsdf_status gsdf_comm_unique_id(uint8_t id128[128]);

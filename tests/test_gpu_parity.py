@@ -103,7 +103,7 @@ def test_golden_free_running(pkg, po, name):
         conv = opt.optimize(frames[i])
         assert conv == bool(g["free_conv"][i])
         if conv:
-            sdf.update(None, opt.pose())
+            sdf.update(None, opt.pose(), stored=True)
         dp = np.abs(opt.pose() - g["free_traj"][i])
         assert dp[:3].max() < 2e-3 and dp[3:].max() < 1e-3, (i, dp)  # 2 mm, ~0.1 deg
     k = sdf.download()[0]
@@ -169,7 +169,7 @@ def test_tracking_trajectory_vs_oracle(pkg, po, synth):
         assert dp[:3].max() < 2e-3 and dp[3:].max() < 1e-3, (i, dp)
         assert c == co
         if c:
-            sdf.update(None, opt.pose())
+            sdf.update(None, opt.pose(), stored=True)
             orc.update(frames[i], orc.get_pose())
         # GT check: the tracker follows the true camera motion
         assert np.abs(opt.pose()[:3] - poses[i][:3]).max() < 0.02
