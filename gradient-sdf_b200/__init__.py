@@ -34,7 +34,7 @@ EXPORTS = [
     "gsdf_upload_frame", "gsdf_set_frame_device", "gsdf_integrate", "gsdf_integrate_pose", "gsdf_accumulate",
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
-    "gsdf_profile_read", "gsdf_track_stats", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -100,6 +100,7 @@ def lib() -> C.CDLL:
     L.gsdf_stream.argtypes = [H]
     L.gsdf_launch_count.restype = C.c_int64
     L.gsdf_launch_count.argtypes = [H]
+    L.gsdf_accumulate_noalloc.argtypes = [H, _f32p, _f32p, C.c_int32, C.c_void_p]
     L.gsdf_track_stats.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gsdf_profile_enable.argtypes = [H, C.c_int32]
     L.gsdf_profile_read.argtypes = [H, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
@@ -282,6 +283,12 @@ class Sdf:
         R, t, out = _f32(R).reshape(9), _f32(t), np.zeros(29, np.float32)
         self._check(self.L.gsdf_accumulate(self.h, _fp(R), _fp(t), sampling, _fp(out)))
         return out
+
+    def accumulate_noalloc(self, R, t, out29_dev_ptr: int, sampling: int = 1):
+        """gsdf_accumulate_noalloc: same sums as accumulate(), no allocation anywhere on the way; the 29 floats
+        land in caller-owned DEVICE memory at out29_dev_ptr once the handle's stream gets there."""
+        R, t = _f32(R).reshape(9), _f32(t)
+        self._check(self.L.gsdf_accumulate_noalloc(self.h, _fp(R), _fp(t), sampling, C.c_void_p(out29_dev_ptr)))
 
     # -- map access
     def voxel_count(self):

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -677,6 +678,79 @@ gsdf_status gsdf_synchronize(gsdf_handle h) {
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
     return check_overflow(h);
 }
+
+}  // extern "C" (reopened below)
+
+// ----------------------------------------------------------------------------------------------------------
+// gsdf_accumulate_noalloc — the one entry point that never allocates.
+//
+// Who needs it: callers that must not (or cannot) reach the CUDA allocator when they call into the tracker —
+// a process whose device heap has been handed over to another allocator (a framework's caching pool that
+// already holds all free memory, so a cudaMalloc inside a library call would simply fail), a real-time scan
+// loop that cannot afford cudaMalloc's implicit device-wide synchronisation, or a host that pre-budgets every
+// byte of HBM per tenant.  gsdf_create reserves this handle's map and frame buffers up front, but the grid-level
+// reduction of the normal-equation sums also needs per-CTA scratch; here that scratch is NOT taken from the
+// handle: it is the file-scope array below, part of the library image, resident on every GPU that loads the
+// library until the process exits (kStaticScratchFloats * 4 B = 512.25 KiB).  The caller passes the inputs
+// (handle = map + current frame, pose, sampling) and the output buffer (29 floats in DEVICE memory).
+//
+// Limit: one CTA per 256 sampled pixels and at most kStaticMaxTiles (4096) CTAs, i.e. at most 1,048,576 sampled
+// pixels per call (1280x720 at sampling 1 fits); larger frames are rejected with GSDF_ERR_INVALID.
+// Set-up: the array's name is only a host-side stand-in for the device symbol, so the first call on each device
+// resolves the real device address once with cudaGetSymbolAddress (that device current) and caches it; make
+// that first call before starting any stream capture.  All calls on a device share the one array and it keeps
+// the previous call's contents: the arrival ticket is cleared on the stream before every launch (the partial
+// sums are fully overwritten by each launch and need no clearing), and two calls whose kernels overlap on the
+// GPU (different handles/streams on the same device) race on it — serialise them.
+static __device__ __align__(256) float g_noalloc_scratch[kStaticScratchFloats];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_noalloc_ptr[kMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+}  // namespace
+
+extern "C" gsdf_status gsdf_accumulate_noalloc(gsdf_handle h, const float* R9, const float* t3, int32_t sampling,
+                                               float* out29_dev) {
+    if (!h || !R9 || !t3 || !out29_dev || sampling < 1) return GSDF_ERR_INVALID;
+    if (!h->d_depth) { h->err = "no depth frame set"; return GSDF_ERR_NO_FRAME; }
+    if (h->cfg.world_size > 1) { h->err = "gsdf_accumulate_noalloc: single-GPU maps only"; return GSDF_ERR_INVALID; }
+    const int dev = h->cfg.device;
+    if (dev < 0 || dev >= kMaxDevices) { h->err = "gsdf_accumulate_noalloc: device ordinal out of range"; return GSDF_ERR_INVALID; }
+    TrackIntr ti;
+    ti.fx_inv = 1.f / h->cfg.K[0]; ti.fy_inv = 1.f / h->cfg.K[4]; ti.cx = h->cfg.K[2]; ti.cy = h->cfg.K[5];
+    ti.sampling = sampling;
+    ti.ws = (h->cfg.width + sampling - 1) / sampling; ti.hs = (h->cfg.height + sampling - 1) / sampling;
+    const long long total = (long long)ti.ws * ti.hs;
+    const long long tiles = (total + kAccThreads - 1) / kAccThreads;
+    if (tiles > kStaticMaxTiles) {
+        h->err = "gsdf_accumulate_noalloc: " + std::to_string(total) + " sampled pixels exceed the static scratch limit of " +
+                 std::to_string((long long)kStaticMaxTiles * kAccThreads) + " (use gsdf_accumulate or a larger sampling)";
+        return GSDF_ERR_INVALID;
+    }
+    CUDA_TRY(h, cudaSetDevice(dev));
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc_ptr[dev]) {  // once per device, with that device current
+            void* p = nullptr;
+            CUDA_TRY(h, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            g_noalloc_ptr[dev] = static_cast<float*>(p);
+        }
+        scratch = g_noalloc_ptr[dev];
+    }
+    Pose pose;
+    std::memcpy(pose.R, R9, sizeof(float) * 9);
+    std::memcpy(pose.t, t3, sizeof(float) * 3);
+    CUDA_TRY(h, cudaMemsetAsync(scratch + kStaticTicketOffset, 0, sizeof(unsigned int), h->stream));
+    return by_variant(h, [&](auto V) {
+        accumulate_static_kernel<decltype(V)::value><<<(unsigned)tiles, kAccThreads, 0, h->stream>>>(
+            h->view, h->geom, ti, pose, h->d_depth, scratch, out29_dev);
+        return check_launch(h, "accumulate_static_kernel");
+    });
+}
+
+extern "C" {
 
 gsdf_status gsdf_track_stats(gsdf_handle h, int64_t* iterations, int64_t* valid_pixels) {
     if (!h) return GSDF_ERR_INVALID;

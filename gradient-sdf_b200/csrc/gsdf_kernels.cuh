@@ -352,6 +352,92 @@ accumulate_kernel(MapView m, FrameGeom g, TrackIntr ti, const Pose* __restrict__
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Normal-equation sums for callers that cannot allocate: same per-pixel maths and the same warp -> block ->
+// last-block reduction as accumulate_kernel, but the per-block partial sums and the arrival ticket live in a
+// caller-independent scratch array that the library owns statically (see gsdf_accumulate_noalloc in
+// gsdf_api.cu), and the pose arrives by value.  One CTA per 256 sampled pixels, so the scratch needed is
+// 32 floats per CTA; kStaticMaxTiles bounds it.
+constexpr int kStaticMaxTiles = 4096;                               // 4096 * 256 = 1,048,576 sampled pixels
+constexpr int kStaticTicketOffset = kStaticMaxTiles * kAccStride;   // float index of the ticket word
+constexpr int kStaticScratchFloats = kStaticTicketOffset + 64;
+
+template <int VARIANT>
+__global__ void __launch_bounds__(kAccThreads)
+accumulate_static_kernel(MapView m, FrameGeom g, TrackIntr ti, Pose pose, const float* __restrict__ depth,
+                         float* __restrict__ scratch, float* __restrict__ out29) {
+    float acc[kAccTerms];
+#pragma unroll
+    for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
+    const float* R = pose.R;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < ti.ws * ti.hs) {
+        const int ys = i / ti.ws, xs = i - ys * ti.ws;
+        const int x = xs * ti.sampling, y = ys * ti.sampling;
+        const float z = depth[(size_t)y * g.w + x];
+        if (!(z <= g.z_min || z >= g.z_max)) {
+            const float x0 = ((float)x - ti.cx) * ti.fx_inv, y0 = ((float)y - ti.cy) * ti.fy_inv;
+            const float cx_ = x0 * z, cy_ = y0 * z;
+            const float px = dot3_rn(R[0], R[1], R[2], cx_, cy_, z) + pose.t[0];
+            const float py = dot3_rn(R[3], R[4], R[5], cx_, cy_, z) + pose.t[1];
+            const float pz = dot3_rn(R[6], R[7], R[8], cx_, cy_, z) + pose.t[2];
+            float phi, g0, g1, g2;
+            const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2);
+            if (w0 > 0.f) {
+                float J[6];
+                J[0] = g0; J[1] = g1; J[2] = g2;
+                J[3] = py * g2 - pz * g1;
+                J[4] = pz * g0 - px * g2;
+                J[5] = px * g1 - py * g0;
+                int o = 6;
+#pragma unroll
+                for (int a = 0; a < 6; ++a) {
+                    acc[a] = phi * J[a];
+#pragma unroll
+                    for (int b = a; b < 6; ++b) acc[o++] = J[a] * J[b];
+                }
+                acc[27] = phi * phi;
+                acc[28] = 1.f;
+            }
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < kAccTerms; ++t) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc[t] += __shfl_xor_sync(0xffffffffu, acc[t], off);
+    }
+    __shared__ float sm[kAccThreads / 32][kAccStride];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int t = 0; t < kAccTerms; ++t) sm[warp][t] = acc[t];
+    }
+    __syncthreads();
+    if (threadIdx.x < kAccTerms) {
+        float s = 0.f;
+#pragma unroll
+        for (int wq = 0; wq < kAccThreads / 32; ++wq) s += sm[wq][threadIdx.x];
+        scratch[(size_t)blockIdx.x * kAccStride + threadIdx.x] = s;
+    }
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + kStaticTicketOffset);
+        is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);  // the host clears the ticket before every launch
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    for (int term = warp; term < kAccTerms; term += kAccThreads / 32) {
+        float s = 0.f;
+        for (int b = lane; b < (int)gridDim.x; b += 32) s += __ldcg(scratch + (size_t)b * kAccStride + term);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        if (lane == 0) out29[term] = s;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Map iteration: count / compact voxels with weight > 0.
 template <int VARIANT>
 __global__ void __launch_bounds__(256)

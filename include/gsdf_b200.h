@@ -97,6 +97,18 @@ gsdf_status gsdf_accumulate(gsdf_handle h, const float* R9, const float* t3, int
 gsdf_status gsdf_track(gsdf_handle h, float* pose7, int32_t max_iters, float conv_threshold, float damping,
                        int32_t* converged, int32_t* iters_used);
 
+/* No counterpart in the reference (it has no device and no allocator to avoid): gsdf_accumulate for callers
+ * that cannot allocate device memory when they call — the CUDA heap is owned by another allocator, or the
+ * call sits in a real-time loop where cudaMalloc's device-wide synchronisation is not acceptable.  It performs no
+ * cudaMalloc/cudaFree and uses no handle-owned scratch: the reduction's per-CTA partial sums live in a static
+ * 512 KiB device array inside the library.  Same sums as gsdf_accumulate, written to out29_dev (29 floats in
+ * DEVICE memory, ready when the handle's stream reaches that point; gsdf_synchronize waits for it).
+ * Limit: at most 1,048,576 sampled pixels ((width/sampling)*(height/sampling)), else GSDF_ERR_INVALID; single-GPU
+ * maps only.  The first call on a device resolves the array's device address (do it before any stream capture).
+ * All calls on a device share the array: calls that overlap on the GPU race — keep them on one stream. */
+gsdf_status gsdf_accumulate_noalloc(gsdf_handle h, const float* R9, const float* t3, int32_t sampling,
+                                    float* out29_dev);
+
 /* -- Sdf::weights / Sdf::tsdf (sdf_tracker/Sdf.h:113-115; MapGradPixelSdf.h:109-125; MapPixelSdf.h:107-143,
  *    MapPixelSdfOmp.cpp:44-113), batched: per point w = weights(p); phi, grad = tsdf(p, &grad) if w > 0 else 0.
  *    pts n*3, phi n, grad n*3, w n (host pointers). */
