@@ -242,71 +242,73 @@ def run_ours(args):
 
     ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
 
-    def run_pass(sdf, mode, profile=False):
-        """Frame 0 at identity, W warm-up steps, K timed steps.  mode 'dev' = frames resident in HBM,
-        'host' = pinned host buffers through gsdf_upload_frame."""
+    def run_pass(sdf, mode, profile=False, do_flush=True):
+        """Frame 0 fused at identity, W warm-up steps, K timed steps, all through the asynchronous frame pipeline
+        (gsdf_scan_submit / gsdf_scan_collect, up to 4 frames in flight).  mode 'dev' = frames resident in HBM,
+        'host' = pinned host buffers (H2D of every frame on the copy stream + D2H of every result)."""
         sdf.reset()
         sdf.profile_enable(False)
-        opt = pkg.RigidPointOptimizer(sdf)
-        opt.set_pose(ident)
+        sdf.scan_set_pose(ident)
+        sdf.scan_set_tracker(25, 1e-3, 1.0)
         ext = torch.cuda.ExternalStream(sdf.stream)
         host_np = host_frames.numpy()
+        st = {"updates": 0, "iters": 0, "conv": 0, "track_iters": 0, "track_valid": 0, "t_ms": 0.0}
 
-        def set_frame(f):
+        def submit(f, track=True):
             if mode == "dev":
-                sdf.set_frame_device(dev_frames[f].data_ptr())
+                sdf.scan_submit(depth_dev=dev_frames[f].data_ptr(), track=track)
             else:
-                sdf.upload_frame(host_np[f])
+                sdf.scan_submit(depth_host=host_np[f], track=track)
 
-        set_frame(0)
-        sdf.update(None, ident)
-        st = {"updates": 0, "valid": 0, "iters": 0, "conv": 0, "t_ms": 0.0, "t_fuse_ms": 0.0}
+        def flush():
+            # L2 flush ON the library's stream, between the timed intervals ('dev' passes only: host frames
+            # arrive from host memory anyway, and an untimed gap would hide their upload)
+            if flush_buf is not None and mode == "dev" and do_flush:
+                with torch.cuda.stream(ext):
+                    flush_buf.zero_()
 
-        def step(f, timed):
-            if flush_buf is not None:
-                flush_buf.zero_()
-                torch.cuda.synchronize()
-            if timed:
-                e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-                e0.record(ext)
-            set_frame(f)
-            conv = opt.optimize(None)
-            if timed:
-                e1.record(ext)
-            upd = 0
-            if conv:
-                _, upd, _ = sdf.update(None, opt.pose(), stats=True, stored=True)
-            if timed:
-                e2.record(ext)
-                sdf.synchronize()
-                e2.synchronize()
-                st["t_ms"] += e0.elapsed_time(e2)
-                st["t_fuse_ms"] += e1.elapsed_time(e2)
-                st["updates"] += upd
-                st["iters"] += opt.last_iterations + (0 if conv else 0)
-                st["conv"] += int(conv)
-
+        submit(0, track=False)
         for f in range(1, 1 + args.warmup):
-            step(f, False)
+            flush()
+            submit(f)
+            if sdf.scan_pending() == 4:
+                sdf.scan_collect()
+        while sdf.scan_pending():
+            sdf.scan_collect()
         if profile:
             sdf.profile_enable(True)
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
         launches0 = sdf.launch_count
-        it0, valid0 = sdf.track_stats()
+        events, results = [], []
         wall0 = time.perf_counter()
         for f in range(1 + args.warmup, 1 + args.warmup + args.steps):
-            step(f, True)
+            flush()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ext)
+            submit(f)
+            e1.record(ext)
+            events.append((e0, e1))
+            if sdf.scan_pending() == 4:
+                results.append(sdf.scan_collect())
+        while sdf.scan_pending():
+            results.append(sdf.scan_collect())
+        sdf.synchronize()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         st["wall_s"] = time.perf_counter() - wall0
+        st["t_ms"] = sum(a.elapsed_time(b) for a, b in events)
+        st["span_ms"] = events[0][0].elapsed_time(events[-1][1])
+        for r in results:
+            st["updates"] += r.updates
+            st["iters"] += r.iters
+            st["conv"] += r.converged
+            st["track_iters"] += r.track_iterations
+            st["track_valid"] += r.track_valid
         st["launches"] = sdf.launch_count - launches0
-        it1, valid1 = sdf.track_stats()
-        st["track_iters"], st["track_valid"] = it1 - it0, valid1 - valid0
-        st["pose_err_m"] = float(np.abs(opt.pose()[:3]).max())  # diagnostic only
-        st["final_pose"] = opt.pose().tolist()
+        st["final_pose"] = list(results[-1].pose7)
         return st
 
     def max_over_ranks(x):
@@ -328,6 +330,7 @@ def run_ours(args):
         sampler = ClockSampler(local_rank) if rank == 0 else None
         a = run_pass(sdf, "dev")
         b = run_pass(sdf, "host")
+        a2 = run_pass(sdf, "dev", do_flush=False)
         clocks = sampler.stop() if sampler else None
         c = run_pass(sdf, "dev", profile=True)
         n_f, ms_f = sdf.profile_read(1)
@@ -336,18 +339,20 @@ def run_ours(args):
         nv, nb = sdf.voxel_count()
         K_steps = args.steps
         t_dev = max_over_ranks(a["t_ms"])
-        t_host = max_over_ranks(b["t_ms"])
+        t_host = max_over_ranks(b["span_ms"])      # no untimed gaps: first submit -> last result on the stream
+        t_dev_nf = max_over_ranks(a2["span_ms"])
         upd_total = sum_over_ranks(a["updates"])
-        t_fuse = max_over_ranks(a["t_fuse_ms"])
         npx = W_IMG * H_IMG
         # algorithmic bytes: fusion W*H*4 + N_upd*b_v ; tracking W*H*4 + N_valid*b_t per iteration
         b_v = 40 if variant == "grad" else 16
         b_t = 20 if variant == "grad" else 36
         fuse_bytes = n_f * npx * 4 + c["updates"] * b_v
-        acc_bytes = n_a * npx * 4 + c["track_valid"] * b_t
+        acc_bytes = c["track_iters"] * npx * 4 + c["track_valid"] * b_t
+        nrm_bytes = n_n * npx * (4 + 36 + 12)
         res = {
             "variant": variant, "frames_per_s": 1e3 * K_steps / t_dev, "ms_per_step": t_dev / K_steps,
-            "e2e_frames_per_s": 1e3 * K_steps / t_host, "voxel_updates_per_s": 1e3 * upd_total / max(t_fuse, 1e-9),
+            "e2e_frames_per_s": 1e3 * K_steps / t_host, "frames_per_s_no_flush": 1e3 * K_steps / t_dev_nf,
+            "track_iters": c["track_iters"], "nrm_bytes": nrm_bytes, "voxel_updates_per_s": 1e3 * c["updates"] / max(ms_f, 1e-9),
             "updates_per_frame": upd_total / max(1, a["conv"]), "converged_steps": a["conv"],
             "gn_iterations": a["iters"], "launches": a["launches"], "voxels": nv, "blocks": nb,
             "kernel_ms": {"normals": [n_n, ms_n], "fuse": [n_f, ms_f], "accumulate": [n_a, ms_a]},
@@ -370,19 +375,25 @@ def run_ours(args):
         return
 
     peak, peak_src = measured_peak()
-    (n_f, ms_f), (n_a, ms_a) = main["kernel_ms"]["fuse"], main["kernel_ms"]["accumulate"]
+    (n_f, ms_f), (n_a, ms_a), (n_n, ms_n) = (main["kernel_ms"]["fuse"], main["kernel_ms"]["accumulate"],
+                                             main["kernel_ms"]["normals"])
     npx = W_IMG * H_IMG
-    if ms_f >= ms_a or n_a == 0:
-        kname, per_launch_bytes, per_launch_ms = f"fuse_kernel<{main['variant']}>", main["fuse_bytes"] / max(1, n_f), ms_f / max(1, n_f)
-    else:
-        kname, per_launch_bytes, per_launch_ms = (f"accumulate_kernel<{main['variant']}>",
-                                                  main["acc_bytes"] / max(1, n_a), ms_a / max(1, n_a))
+    v = main["variant"]
+    cands = [(ms_f, f"fuse_list_kernel<{v}>", main["fuse_bytes"], n_f),
+             (ms_a, f"track_kernel<{v}> (whole Gauss-Newton loop, {main['track_iters'] / max(1, n_a):.2f} passes/launch)",
+              main["acc_bytes"], n_a),
+             (ms_n, "normals_tile_kernel", main["nrm_bytes"], n_n)]
+    ms_k, kname, bytes_k, n_k = max(cands, key=lambda t: t[0])
+    per_launch_bytes, per_launch_ms = bytes_k / max(1, n_k), ms_k / max(1, n_k)
     achieved = per_launch_bytes / max(per_launch_ms, 1e-12) / 1e6  # GB/s
+    step_ms = main["ms_per_step"] * args.steps
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "peak_source": peak_src,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(kname),
+                "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(kname.split(" ")[0]),
                 "algorithmic_bytes_per_launch": per_launch_bytes, "us_per_launch": 1e3 * per_launch_ms,
-                "kernel_share_of_step": {"fuse": ms_f / (main["ms_per_step"] * args.steps),
-                                         "accumulate": ms_a / (main["ms_per_step"] * args.steps)}}
+                "kernel_share_of_step": {"fuse": ms_f / step_ms, "track": ms_a / step_ms, "normals": ms_n / step_ms},
+                "per_kernel_GBps": {"fuse": main["fuse_bytes"] / max(ms_f, 1e-9) / 1e6,
+                                    "track": main["acc_bytes"] / max(ms_a, 1e-9) / 1e6,
+                                    "normals": main["nrm_bytes"] / max(ms_n, 1e-9) / 1e6}}
 
     cpu_base = None
     if world == 1:
@@ -400,20 +411,24 @@ def run_ours(args):
                    "29-float NCCL allreduce per Gauss-Newton iteration",
                    "l2": "no flush (--no-l2-flush)" if args.no_l2_flush else
                    "L2 flushed (256 MiB memset) before every step, outside the timed intervals",
-                   "timing": "sum over steps of CUDA-event intervals on the library's stream (host launch gaps "
-                             "included), max over ranks"},
+                   "timing": "sum over steps of CUDA-event intervals on the library's stream around each frame's "
+                             "enqueued work (gsdf_scan_submit, up to 4 frames in flight), max over ranks",
+                   "api": "gsdf_scan_submit / gsdf_scan_collect"},
         "voxel_updates_per_s": main["voxel_updates_per_s"], "updates_per_frame": main["updates_per_frame"],
         "converged_steps": main["converged_steps"], "gn_iterations_per_step": iters_per_step,
         "map": {"voxels": main["voxels"], "blocks": main["blocks"]},
         "e2e": {"value": main["e2e_frames_per_s"], "unit": "frames/s", "h2d_bytes_per_step": npx * 4,
-                "d2h_bytes_per_step": int(round(iters_per_step * 29 * 4 + 32))},
+                "d2h_bytes_per_step": 224,
+                "timing": "K / device-timeline span from the first submit to the last result, pinned host frames, "
+                          "uploads on the copy stream overlapped with the previous frame, no L2 flush, no gaps"},
+        "value_no_flush": main["frames_per_s_no_flush"],
         "gpu_launches": main["launches"], "clocks": main["clocks"], "roofline": roofline, "cpu_baseline": cpu_base,
         "kernel_ms_total": main["kernel_ms"],
     }
     if extra:
         line["extra"] = {k: extra[k] for k in ("variant", "frames_per_s", "e2e_frames_per_s", "voxel_updates_per_s",
                                                "updates_per_frame", "converged_steps", "gn_iterations", "kernel_ms",
-                                               "fuse_GBps", "voxels")}
+                                               "fuse_GBps", "voxels", "frames_per_s_no_flush")}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

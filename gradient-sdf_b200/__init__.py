@@ -34,7 +34,8 @@ EXPORTS = [
     "gsdf_upload_frame", "gsdf_set_frame_device", "gsdf_integrate", "gsdf_integrate_pose", "gsdf_accumulate",
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
-    "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
+    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -50,6 +51,12 @@ class Config(C.Structure):
                 ("z_max", C.c_float), ("width", C.c_int32), ("height", C.c_int32), ("K", C.c_float * 9),
                 ("normal_window", C.c_int32), ("log2_capacity", C.c_int32), ("device", C.c_int32),
                 ("world_size", C.c_int32), ("rank", C.c_int32)]
+
+
+class FrameResult(C.Structure):
+    _fields_ = [("pose7", C.c_float * 7), ("converged", C.c_int32), ("iters", C.c_int32), ("fused", C.c_int32),
+                ("n_valid", C.c_int32), ("points", C.c_int64), ("updates", C.c_int64), ("blocks", C.c_int64),
+                ("track_iterations", C.c_int64), ("track_valid", C.c_int64)]
 
 
 class IntegrateStats(C.Structure):
@@ -100,6 +107,12 @@ def lib() -> C.CDLL:
     L.gsdf_stream.argtypes = [H]
     L.gsdf_launch_count.restype = C.c_int64
     L.gsdf_launch_count.argtypes = [H]
+    L.gsdf_scan_set_pose.argtypes = [H, _f32p]
+    L.gsdf_scan_set_tracker.argtypes = [H, C.c_int32, C.c_float, C.c_float]
+    L.gsdf_scan_submit.argtypes = [H, C.c_void_p, C.c_void_p, C.c_int32]
+    L.gsdf_scan_collect.argtypes = [H, C.POINTER(FrameResult)]
+    L.gsdf_scan_pending.restype = C.c_int32
+    L.gsdf_scan_pending.argtypes = [H]
     L.gsdf_accumulate_noalloc.argtypes = [H, _f32p, _f32p, C.c_int32, C.c_void_p]
     L.gsdf_track_stats.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gsdf_profile_enable.argtypes = [H, C.c_int32]
@@ -270,6 +283,34 @@ class Sdf:
     def setup(self, depth):
         """Sdf::setup = update at the identity pose (Sdf.h:119-121)."""
         return self.update(depth, np.array([0, 0, 0, 0, 0, 0, 1], np.float32))
+
+    # -- the asynchronous frame pipeline (main_scan_3d.cpp:208-266 without the host in the loop)
+    def scan_set_pose(self, pose7):
+        p = _f32(pose7)
+        self._check(self.L.gsdf_scan_set_pose(self.h, _fp(p)))
+
+    def scan_set_tracker(self, max_iters=25, conv_threshold=1e-3, damping=1.0):
+        self._check(self.L.gsdf_scan_set_tracker(self.h, max_iters, conv_threshold, damping))
+
+    def scan_submit(self, depth_host=None, depth_dev: int = 0, track: bool = True):
+        """Enqueue one frame (returns at once).  depth_host: float32 array (pinned for true overlap), kept alive by
+        the caller until collected; depth_dev: device pointer."""
+        hp = None
+        if depth_host is not None:
+            d = depth_host if (isinstance(depth_host, np.ndarray) and depth_host.dtype == np.float32
+                               and depth_host.flags["C_CONTIGUOUS"]) else _f32(depth_host)
+            self._pending_keep = getattr(self, "_pending_keep", [])[-8:] + [d]
+            hp = d.ctypes.data
+        self._check(self.L.gsdf_scan_submit(self.h, hp, C.c_void_p(depth_dev) if depth_dev else None,
+                                            1 if track else 0))
+
+    def scan_collect(self) -> FrameResult:
+        r = FrameResult()
+        self._check(self.L.gsdf_scan_collect(self.h, C.byref(r)))
+        return r
+
+    def scan_pending(self) -> int:
+        return int(self.L.gsdf_scan_pending(self.h))
 
     # -- Sdf::tsdf / weights (batched)
     def query(self, pts):

@@ -1,7 +1,9 @@
 // libgsdf_b200.so — C ABI (include/gsdf_b200.h) and host logic of the B200 Scan3D hot path.
-// Host side: handle lifetime, the one-time FALS cache (cv::NormalEstimator::cache, double precision),
-// pose algebra with Sophus::SE3f semantics, the Gauss-Newton driver loop, NCCL plumbing for sharded maps.
-// Device side: gsdf_kernels.cuh.  There is no CPU implementation of the per-frame path in this library.
+// Host side: handle lifetime, the one-time FALS cache (cv::NormalEstimator::cache, double precision), stream and
+// event plumbing of the frame pipeline, NCCL plumbing for sharded maps.
+// Device side: gsdf_kernels.cuh (v1 kernels, still used by the fine-grained entry points) and gsdf_pipeline.cuh
+// (compaction, persistent tracker, list-driven fusion, tile-skipping normals).
+// There is no CPU implementation of the per-frame path in this library.
 #include "../../include/gsdf_b200.h"
 
 #include <cuda_runtime.h>
@@ -15,7 +17,7 @@
 #include <string>
 #include <vector>
 
-#include "gsdf_kernels.cuh"
+#include "gsdf_pipeline.cuh"
 
 using namespace gsdf;
 
@@ -49,36 +51,59 @@ struct NcclApi {
 NcclApi g_nccl;
 constexpr int kNcclFloat = 7, kNcclSum = 0;  // ncclFloat32, ncclSum (nccl.h)
 std::string g_create_error;
+constexpr int kRing = 4;  // frames in flight in the submit/collect pipeline
 }  // namespace
+
+struct FrameSlot {
+    float* d_depth = nullptr;              // landing buffer for host uploads
+    cudaEvent_t ev_up = nullptr, ev_norm = nullptr, ev_fused = nullptr, ev_done = nullptr;
+    FrameState* h_state = nullptr;         // pinned result staging
+    Counters* h_ctr = nullptr;
+    int mode = 0;
+};
 
 struct gsdf_map {
     gsdf_config cfg;
     FrameGeom geom;
     MapView view;
     size_t cap = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;    // main: prepare, track, fuse, results
+    cudaStream_t stream_n = nullptr;  // normals (overlaps tracking in the pipeline)
+    cudaStream_t stream_c = nullptr;  // host -> device frame copies
     // device buffers
-    float* d_planes = nullptr;   // 11 cached planes
-    float* d_depth_own = nullptr;
-    const float* d_depth = nullptr;  // current frame (own buffer or caller's)
-    float* d_normals = nullptr;  // 3 planes
-    bool normals_valid = false;
+    float* d_planes = nullptr;        // 11 cached planes
+    const float* d_depth = nullptr;   // current frame (ring slot or caller's device buffer)
+    float* d_normals[2] = {nullptr, nullptr};
+    int normals_buf = 0;              // buffer holding the current frame's normals
+    bool normals_valid = false, prepared = false;
+    int2* d_vlist = nullptr;
+    int* d_seg_counts = nullptr;
+    int nseg = 0;
+    FrameState* d_state = nullptr;
     Counters* d_ctr = nullptr;
-    float* d_partials = nullptr;
+    float* d_partials = nullptr;      // v1 accumulate / accumulate_list: [acc_blocks][32]
     int acc_blocks = 0;
+    float* d_track_partials = nullptr;  // track_kernel: [2][track_blocks][32]
+    int track_blocks = 0;
     Pose* d_pose = nullptr;
     float* d_out29 = nullptr;
+    unsigned long long* d_count2 = nullptr;
     // pinned host staging
     float* h_out29 = nullptr;
     Counters* h_ctr = nullptr;
     Pose* h_pose = nullptr;
-    unsigned long long* d_count2 = nullptr;
+    FrameState* h_state = nullptr;
     unsigned long long* h_count2 = nullptr;
     std::vector<float> h_planes;
+    // frame pipeline
+    FrameSlot ring[kRing];
+    int64_t seq_submitted = 0, seq_collected = 0;
+    int sync_slot = 0;                // ring slot used by gsdf_upload_frame
+    TrackParams scan_tp{25, 1e-6f, 1.f};
+    unsigned long long last_points = 0, last_updates = 0;  // cumulative counters at the last report
     int sm_count = 148;
     int64_t launches = 0;
-    int64_t track_iterations = 0, track_valid = 0;  // cumulative, for bytes-per-launch accounting
-    // per-kernel CUDA-event timing (off by default): pairs recorded around each launch, resolved on read
+    int64_t track_iterations = 0, track_valid = 0;
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[GSDF_PROF_KINDS];
     size_t prof_used[GSDF_PROF_KINDS] = {0, 0, 0};
@@ -157,70 +182,6 @@ void build_normal_cache(const gsdf_config& c, std::vector<float>& P) {
     }
 }
 
-// ---- pose algebra, Sophus::SE3f semantics (quaternion x,y,z,w + translation) ------------------------------
-float dot3h(const float* a, const float* b) { const float p0 = a[0] * b[0], s = a[1] * b[1] + a[2] * b[2]; return p0 + s; }
-void matvec3h(const float* R, const float* v, float* o) { o[0] = dot3h(R, v); o[1] = dot3h(R + 3, v); o[2] = dot3h(R + 6, v); }
-void quat_normalize(float* q) {  // so3.hpp:297-303; Eigen packet sum pairs (x^2+z^2)+(y^2+w^2)
-    const float len = std::sqrt((q[0] * q[0] + q[2] * q[2]) + (q[1] * q[1] + q[3] * q[3]));
-    for (int i = 0; i < 4; ++i) q[i] /= len;
-}
-void quat_to_R(const float* q, float* R) {  // Eigen QuaternionBase::toRotationMatrix
-    const float x = q[0], y = q[1], z = q[2], w = q[3];
-    const float tx = 2.f * x, ty = 2.f * y, tz = 2.f * z;
-    const float twx = tx * w, twy = ty * w, twz = tz * w;
-    const float txx = tx * x, txy = ty * x, txz = tz * x, tyy = ty * y, tyz = tz * y, tzz = tz * z;
-    R[0] = 1.f - (tyy + tzz); R[1] = txy - twz; R[2] = txz + twy;
-    R[3] = txy + twz; R[4] = 1.f - (txx + tzz); R[5] = tyz - twx;
-    R[6] = txz - twy; R[7] = tyz + twx; R[8] = 1.f - (txx + tyy);
-}
-void cross3(const float* a, const float* b, float* o) {
-    o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
-}
-void quat_rotate(const float* q, const float* p, float* o) {  // so3.hpp:356-366
-    float uv[3], c2[3];
-    cross3(q, p, uv);
-    for (int i = 0; i < 3; ++i) uv[i] += uv[i];
-    cross3(q, uv, c2);
-    for (int i = 0; i < 3; ++i) o[i] = (p[i] + q[3] * uv[i]) + c2[i];
-}
-void quat_mul(const float* a, const float* b, float* o) {  // so3.hpp:325-339, then SO3(quat) normalises
-    const float ax = a[0], ay = a[1], az = a[2], aw = a[3], bx = b[0], by = b[1], bz = b[2], bw = b[3];
-    o[3] = aw * bw - ax * bx - ay * by - az * bz;
-    o[0] = aw * bx + ax * bw + ay * bz - az * by;
-    o[1] = aw * by + ay * bw + az * bx - ax * bz;
-    o[2] = aw * bz + az * bw + ax * by - ay * bx;
-    quat_normalize(o);
-}
-void se3_exp(const float* a, float* q, float* tr) {  // se3.hpp:761-782, so3.hpp:583-619
-    const float* om = a + 3;
-    const float eps = 1e-5f;
-    const float theta_sq = dot3h(om, om);
-    float theta, imag, real;
-    if (theta_sq < eps * eps) {
-        theta = 0.f;
-        const float p4 = theta_sq * theta_sq;
-        imag = 0.5f - (float)(1.0 / 48.0) * theta_sq + (float)(1.0 / 3840.0) * p4;
-        real = 1.f - (float)(1.0 / 8.0) * theta_sq + (float)(1.0 / 384.0) * p4;
-    } else {
-        theta = std::sqrt(theta_sq);
-        const float half = 0.5f * theta;
-        imag = std::sin(half) / theta;
-        real = std::cos(half);
-    }
-    q[0] = imag * om[0]; q[1] = imag * om[1]; q[2] = imag * om[2]; q[3] = real;
-    const float O[9] = {0.f, -om[2], om[1], om[2], 0.f, -om[0], -om[1], om[0], 0.f};
-    float O2[9], V[9];
-    for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) { const float col[3] = {O[j], O[3 + j], O[6 + j]}; O2[3 * i + j] = dot3h(O + 3 * i, col); }
-    if (theta < eps) quat_to_R(q, V);
-    else {
-        const float tsq = theta * theta;
-        const float c1 = (1.f - std::cos(theta)) / tsq, c2 = (theta - std::sin(theta)) / (tsq * theta);
-        for (int i = 0; i < 9; ++i) V[i] = ((i % 4 == 0 ? 1.f : 0.f) + c1 * O[i]) + c2 * O2[i];
-    }
-    matvec3h(V, a, tr);
-}
-
 template <typename F>
 gsdf_status by_variant(gsdf_map* h, F f) { return h->cfg.variant == GSDF_GRAD_SDF ? f(std::integral_constant<int, 0>()) : f(std::integral_constant<int, 1>()); }
 
@@ -232,8 +193,9 @@ gsdf_status check_launch(gsdf_map* h, const char* what) {
 }
 
 struct ProfScope {
-    gsdf_map* h; int kind; cudaEvent_t stop = nullptr;
-    ProfScope(gsdf_map* h_, int kind_) : h(h_), kind(kind_) {
+    cudaStream_t st = nullptr;
+    cudaEvent_t stop = nullptr;
+    ProfScope(gsdf_map* h, int kind, cudaStream_t stream) : st(stream) {
         if (!h->profiling) return;
         auto& v = h->prof_events[kind];
         if (h->prof_used[kind] == v.size()) {
@@ -242,27 +204,132 @@ struct ProfScope {
             v.push_back({a, b});
         }
         auto& pr = v[h->prof_used[kind]++];
-        cudaEventRecord(pr.first, h->stream);
+        cudaEventRecord(pr.first, st);
         stop = pr.second;
     }
-    ~ProfScope() { if (stop) cudaEventRecord(stop, h->stream); }
+    ~ProfScope() { if (stop) cudaEventRecord(stop, st); }
 };
 
-gsdf_status ensure_normals(gsdf_map* h) {
-    if (!h->d_depth) { h->err = "no depth frame set"; return GSDF_ERR_NO_FRAME; }
-    if (h->normals_valid) return GSDF_OK;
+TrackIntr make_intr(const gsdf_map* h, int sampling) {
+    TrackIntr ti;
+    ti.fx_inv = 1.f / h->cfg.K[0]; ti.fy_inv = 1.f / h->cfg.K[4]; ti.cx = h->cfg.K[2]; ti.cy = h->cfg.K[5];
+    ti.sampling = sampling;
+    ti.ws = (h->cfg.width + sampling - 1) / sampling; ti.hs = (h->cfg.height + sampling - 1) / sampling;
+    return ti;
+}
+
+size_t normals_smem(const gsdf_map* h) {
+    const int r = h->cfg.normal_window / 2, tw = NT_W + 2 * r, th = NT_H + 2 * r;
+    return sizeof(double) * 3 * tw * th + sizeof(double) * 3 * th * NT_W;
+}
+
+// normals of `depth` into buffer `buf` on `stream`; skip_empty = false computes every tile (gsdf_compute_normals)
+gsdf_status launch_normals(gsdf_map* h, const float* depth, int buf, cudaStream_t stream, bool skip_empty) {
     const int w = h->cfg.width, ht = h->cfg.height, r = h->cfg.normal_window / 2;
     const size_t n = (size_t)w * ht;
-    const int tw = NT_W + 2 * r, th = NT_H + 2 * r;
-    const size_t smem = ((sizeof(float) * 3 * tw * th + 7) & ~size_t(7)) + sizeof(double) * 3 * th * NT_W;
     dim3 grid((w + NT_W - 1) / NT_W, (ht + NT_H - 1) / NT_H), block(NT_W, NT_H);
-    ProfScope prof(h, GSDF_PROF_NORMALS);
-    normals_kernel<<<grid, block, smem, h->stream>>>(h->d_depth, h->d_planes + 2 * n, h->d_planes + 3 * n,
-                                                     h->d_planes + 4 * n, h->d_planes + 5 * n, h->d_normals,
-                                                     h->d_normals + n, h->d_normals + 2 * n, w, ht, r);
-    gsdf_status s = check_launch(h, "normals_kernel");
+    float* nrm = h->d_normals[buf];
+    const float zmin = skip_empty ? h->geom.z_min : -INFINITY, zmax = skip_empty ? h->geom.z_max : INFINITY;
+    ProfScope prof(h, GSDF_PROF_NORMALS, stream);
+    normals_tile_kernel<<<grid, block, normals_smem(h), stream>>>(depth, h->d_planes + 2 * n, h->d_planes + 3 * n,
+                                                                  h->d_planes + 4 * n, h->d_planes + 5 * n, nrm, nrm + n,
+                                                                  nrm + 2 * n, w, ht, r, zmin, zmax);
+    return check_launch(h, "normals_tile_kernel");
+}
+
+// compaction of the current frame's z-valid pixels (deterministic order) into d_vlist, count into d_state->n_valid
+gsdf_status launch_prepare(gsdf_map* h, const float* depth, cudaStream_t stream) {
+    const int n = h->cfg.width * h->cfg.height;
+    valid_count_kernel<<<h->nseg, 256, 0, stream>>>(depth, n, h->geom.z_min, h->geom.z_max, h->d_seg_counts);
+    gsdf_status s = check_launch(h, "valid_count_kernel");
+    if (s != GSDF_OK) return s;
+    valid_write_kernel<<<h->nseg, 256, 0, stream>>>(depth, n, h->geom.z_min, h->geom.z_max, h->d_seg_counts, h->d_vlist,
+                                                    h->d_state);
+    return check_launch(h, "valid_write_kernel");
+}
+
+gsdf_status ensure_frame(gsdf_map* h) {
+    if (!h->d_depth) { h->err = "no depth frame set"; return GSDF_ERR_NO_FRAME; }
+    return GSDF_OK;
+}
+
+gsdf_status ensure_prepared(gsdf_map* h) {
+    gsdf_status s = ensure_frame(h);
+    if (s != GSDF_OK || h->prepared) return s;
+    s = launch_prepare(h, h->d_depth, h->stream);
+    if (s == GSDF_OK) h->prepared = true;
+    return s;
+}
+
+gsdf_status ensure_normals(gsdf_map* h) {
+    gsdf_status s = ensure_frame(h);
+    if (s != GSDF_OK || h->normals_valid) return s;
+    s = launch_normals(h, h->d_depth, h->normals_buf, h->stream, true);
     if (s == GSDF_OK) h->normals_valid = true;
     return s;
+}
+
+gsdf_status launch_fuse(gsdf_map* h, const Pose& pose, int pose_src, int nbuf, cudaStream_t stream) {
+    const size_t np = (size_t)h->cfg.width * h->cfg.height;
+    int blocks = (int)((np + 255) / 256);
+    if (blocks > h->sm_count * 8) blocks = h->sm_count * 8;
+    const float* nrm = h->d_normals[nbuf];
+    return by_variant(h, [&](auto V) {
+        ProfScope prof(h, GSDF_PROF_FUSE, stream);
+        fuse_list_kernel<decltype(V)::value><<<blocks, 256, 0, stream>>>(
+            h->view, h->geom, pose, pose_src, h->d_vlist, h->d_state, nrm, nrm + np, nrm + 2 * np, h->d_planes,
+            h->d_planes + np, h->d_planes + 4 * np, h->d_ctr);
+        return check_launch(h, "fuse_list_kernel");
+    });
+}
+
+// the Gauss-Newton loop from the pose in d_state; result (pose, converged, iters) stays in d_state
+gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, cudaStream_t stream) {
+    const TrackIntr ti = make_intr(h, 1);
+    if (h->cfg.world_size == 1) {
+        return by_variant(h, [&](auto V) {
+            ProfScope prof(h, GSDF_PROF_ACCUMULATE, stream);
+            MapView view = h->view;
+            FrameGeom geom = h->geom;
+            TrackIntr ti_ = ti;
+            const int2* vlist = h->d_vlist;
+            FrameState* st = h->d_state;
+            float* partials = h->d_track_partials;
+            TrackParams tp_ = tp;
+            void* args[] = {&view, &geom, &ti_, &vlist, &st, &partials, &tp_};
+            cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_kernel<decltype(V)::value>, dim3(h->track_blocks),
+                                                        dim3(kTrackThreads), args, 0, stream);
+            if (e != cudaSuccess) { h->err = std::string("cudaLaunchCooperativeKernel(track_kernel): ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
+            return check_launch(h, "track_kernel");
+        });
+    }
+    // sharded map: per-iteration launches with an all-reduce between the sums and the solve
+    if (!h->comm) { h->err = "world_size > 1 but gsdf_comm_init was not called"; return GSDF_ERR_NCCL; }
+    track_begin_kernel<<<1, 32, 0, stream>>>(h->d_state);
+    gsdf_status s = check_launch(h, "track_begin_kernel");
+    if (s != GSDF_OK) return s;
+    const int batch = 4;
+    for (int k0 = 0; k0 < tp.max_iters; k0 += batch) {
+        for (int k = k0; k < k0 + batch && k < tp.max_iters; ++k) {
+            s = by_variant(h, [&](auto V) {
+                ProfScope prof(h, GSDF_PROF_ACCUMULATE, stream);
+                accumulate_list_kernel<decltype(V)::value><<<h->acc_blocks, kAccThreads, 0, stream>>>(
+                    h->view, h->geom, ti, h->d_vlist, h->d_state, h->d_partials, h->d_ctr, h->d_out29);
+                return check_launch(h, "accumulate_list_kernel");
+            });
+            if (s != GSDF_OK) return s;
+            const int rc = g_nccl.AllReduce(h->d_out29, h->d_out29, kAccTerms, kNcclFloat, kNcclSum, h->comm, stream);
+            if (rc != 0) { h->err = std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?"); return GSDF_ERR_NCCL; }
+            solve_kernel<<<1, 32, 0, stream>>>(h->d_state, h->d_out29, tp);
+            s = check_launch(h, "solve_kernel");
+            if (s != GSDF_OK) return s;
+        }
+        // every rank holds identical sums, hence identical `done` flags: all ranks leave the loop together
+        CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->d_state, sizeof(FrameState), cudaMemcpyDeviceToHost, stream));
+        CUDA_TRY(h, cudaStreamSynchronize(stream));
+        if (h->h_state->done) break;
+    }
+    return GSDF_OK;
 }
 
 gsdf_status clear_map(gsdf_map* h) {
@@ -274,6 +341,15 @@ gsdf_status clear_map(gsdf_map* h) {
         CUDA_TRY(h, cudaMemsetAsync(h->view.acc2, 0, sizeof(float2) * h->cap * kBlockVoxels, h->stream));
     }
     CUDA_TRY(h, cudaMemsetAsync(h->d_ctr, 0, sizeof(Counters), h->stream));
+    FrameState zero;
+    std::memset(&zero, 0, sizeof(zero));
+    zero.pose7[6] = 1.f;
+    *h->h_state = zero;
+    CUDA_TRY(h, cudaMemcpyAsync(h->d_state, h->h_state, sizeof(FrameState), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    h->last_points = h->last_updates = 0;
+    h->track_iterations = h->track_valid = 0;
+    h->prepared = false;  // n_valid lives in the state that was just cleared
     return GSDF_OK;
 }
 
@@ -282,11 +358,22 @@ void free_all(gsdf_map* h) {
     cudaSetDevice(h->cfg.device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
-    cudaFree(h->d_planes); cudaFree(h->d_depth_own); cudaFree(h->d_normals); cudaFree(h->d_ctr);
+    cudaFree(h->d_planes); cudaFree(h->d_normals[0]); cudaFree(h->d_normals[1]); cudaFree(h->d_ctr);
+    cudaFree(h->d_vlist); cudaFree(h->d_seg_counts); cudaFree(h->d_state); cudaFree(h->d_track_partials);
     cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
+    cudaFreeHost(h->h_state);
+    for (auto& sl : h->ring) {
+        cudaFree(sl.d_depth); cudaFreeHost(sl.h_state); cudaFreeHost(sl.h_ctr);
+        if (sl.ev_up) cudaEventDestroy(sl.ev_up);
+        if (sl.ev_norm) cudaEventDestroy(sl.ev_norm);
+        if (sl.ev_fused) cudaEventDestroy(sl.ev_fused);
+        if (sl.ev_done) cudaEventDestroy(sl.ev_done);
+    }
     for (auto& v : h->prof_events) for (auto& pr : v) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->stream_n) cudaStreamDestroy(h->stream_n);
+    if (h->stream_c) cudaStreamDestroy(h->stream_c);
     delete h;
 }
 
@@ -296,7 +383,10 @@ gsdf_status create_impl(gsdf_map* h) {
     cudaDeviceProp prop;
     CUDA_TRY(h, cudaGetDeviceProperties(&prop, c.device));
     h->sm_count = prop.multiProcessorCount;
+    if (!prop.cooperativeLaunch) { h->err = "device lacks cooperative launch"; return GSDF_ERR_CUDA; }
     CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream_n, cudaStreamNonBlocking));
+    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream_c, cudaStreamNonBlocking));
     const size_t n = (size_t)c.width * c.height;
     h->cap = (size_t)1 << c.log2_capacity;
     h->view.cap_mask = (uint32_t)(h->cap - 1);
@@ -309,37 +399,54 @@ gsdf_status create_impl(gsdf_map* h) {
         CUDA_TRY(h, cudaMalloc(&h->view.acc2, sizeof(float2) * h->cap * kBlockVoxels));
     }
     CUDA_TRY(h, cudaMalloc(&h->d_planes, sizeof(float) * n * 11));
-    CUDA_TRY(h, cudaMalloc(&h->d_depth_own, sizeof(float) * n));
-    CUDA_TRY(h, cudaMalloc(&h->d_normals, sizeof(float) * n * 3));
+    CUDA_TRY(h, cudaMalloc(&h->d_normals[0], sizeof(float) * n * 3));
+    CUDA_TRY(h, cudaMalloc(&h->d_normals[1], sizeof(float) * n * 3));
+    CUDA_TRY(h, cudaMalloc(&h->d_vlist, sizeof(int2) * n));
+    h->nseg = (int)((n + kSegPixels - 1) / kSegPixels);
+    CUDA_TRY(h, cudaMalloc(&h->d_seg_counts, sizeof(int) * h->nseg));
+    CUDA_TRY(h, cudaMalloc(&h->d_state, sizeof(FrameState)));
     CUDA_TRY(h, cudaMalloc(&h->d_ctr, sizeof(Counters)));
-    h->acc_blocks = h->sm_count * 4;
-    CUDA_TRY(h, cudaMalloc(&h->d_partials, sizeof(float) * kAccStride * h->acc_blocks));
+    h->acc_blocks = h->sm_count * 2;
+    CUDA_TRY(h, cudaMalloc(&h->d_partials, sizeof(float) * kAccStride * h->sm_count * 4));
+    // persistent tracker: one CTA per SM (all co-resident, as grid.sync requires)
+    int per_sm = 0;
+    if (c.variant == GSDF_GRAD_SDF) CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<0>, kTrackThreads, 0));
+    else CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<1>, kTrackThreads, 0));
+    if (per_sm < 1) { h->err = "track_kernel does not fit on an SM"; return GSDF_ERR_CUDA; }
+    h->track_blocks = h->sm_count;
+    CUDA_TRY(h, cudaMalloc(&h->d_track_partials, sizeof(float) * 2 * kAccStride * h->track_blocks));
     CUDA_TRY(h, cudaMalloc(&h->d_pose, sizeof(Pose)));
     CUDA_TRY(h, cudaMalloc(&h->d_out29, sizeof(float) * kAccStride));
     CUDA_TRY(h, cudaMalloc(&h->d_count2, sizeof(unsigned long long) * 4));
     CUDA_TRY(h, cudaHostAlloc(&h->h_out29, sizeof(float) * kAccStride, cudaHostAllocDefault));
     CUDA_TRY(h, cudaHostAlloc(&h->h_ctr, sizeof(Counters), cudaHostAllocDefault));
     CUDA_TRY(h, cudaHostAlloc(&h->h_pose, sizeof(Pose), cudaHostAllocDefault));
+    CUDA_TRY(h, cudaHostAlloc(&h->h_state, sizeof(FrameState), cudaHostAllocDefault));
     CUDA_TRY(h, cudaHostAlloc(&h->h_count2, sizeof(unsigned long long) * 4, cudaHostAllocDefault));
+    for (auto& sl : h->ring) {
+        CUDA_TRY(h, cudaMalloc(&sl.d_depth, sizeof(float) * n));
+        CUDA_TRY(h, cudaHostAlloc(&sl.h_state, sizeof(FrameState), cudaHostAllocDefault));
+        CUDA_TRY(h, cudaHostAlloc(&sl.h_ctr, sizeof(Counters), cudaHostAllocDefault));
+        CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_up, cudaEventDisableTiming));
+        CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_norm, cudaEventDisableTiming));
+        CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_fused, cudaEventDisableTiming));
+        CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
+    }
+    if (normals_smem(h) > 48 * 1024)
+        CUDA_TRY(h, cudaFuncSetAttribute(normals_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
     build_normal_cache(c, h->h_planes);
     CUDA_TRY(h, cudaMemcpyAsync(h->d_planes, h->h_planes.data(), sizeof(float) * n * 11, cudaMemcpyHostToDevice, h->stream));
-    gsdf_status s = clear_map(h);
-    if (s != GSDF_OK) return s;
-    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
-    return GSDF_OK;
+    return clear_map(h);
 }
 
+// v1 reduction over the pixel grid (supports sampling): result lands in d_out29, pose taken from d_pose
 gsdf_status accumulate_device(gsdf_map* h, int sampling) {
-    // launches the reduction; result lands in d_out29 (all 29 terms), pose taken from d_pose
-    TrackIntr ti;
-    ti.fx_inv = 1.f / h->cfg.K[0]; ti.fy_inv = 1.f / h->cfg.K[4]; ti.cx = h->cfg.K[2]; ti.cy = h->cfg.K[5];
-    ti.sampling = sampling;
-    ti.ws = (h->cfg.width + sampling - 1) / sampling; ti.hs = (h->cfg.height + sampling - 1) / sampling;
+    const TrackIntr ti = make_intr(h, sampling);
     const int total = ti.ws * ti.hs;
     int blocks = (total + kAccThreads - 1) / kAccThreads;
-    if (blocks > h->acc_blocks) blocks = h->acc_blocks;
+    if (blocks > h->sm_count * 4) blocks = h->sm_count * 4;
     gsdf_status s = by_variant(h, [&](auto V) {
-        ProfScope prof(h, GSDF_PROF_ACCUMULATE);
+        ProfScope prof(h, GSDF_PROF_ACCUMULATE, h->stream);
         accumulate_kernel<decltype(V)::value><<<blocks, kAccThreads, 0, h->stream>>>(
             h->view, h->geom, ti, h->d_pose, h->d_depth, h->d_partials, h->d_ctr, h->d_out29);
         return check_launch(h, "accumulate_kernel");
@@ -371,11 +478,27 @@ gsdf_status set_pose_device(gsdf_map* h, const float* R9, const float* t3) {
     return GSDF_OK;
 }
 
+// pose7 -> d_state.pose7 (stream-ordered; the rest of the state is left alone)
+gsdf_status set_state_pose(gsdf_map* h, const float* pose7) {
+    // pageable source would make the copy synchronous anyway; use the pinned pose buffer as staging
+    std::memcpy(h->h_pose, pose7, sizeof(float) * 7);
+    CUDA_TRY(h, cudaMemcpyAsync(h->d_state, h->h_pose, sizeof(float) * 7, cudaMemcpyHostToDevice, h->stream));
+    return GSDF_OK;
+}
+
+gsdf_status pipeline_idle(gsdf_map* h) {
+    if (h->seq_submitted != h->seq_collected) {
+        h->err = "frames submitted with gsdf_scan_submit are still pending: collect them first";
+        return GSDF_ERR_INVALID;
+    }
+    return GSDF_OK;
+}
+
 }  // namespace
 
 extern "C" {
 
-const char* gsdf_version(void) { return "gsdf_b200 0.1 (sm_100a)"; }
+const char* gsdf_version(void) { return "gsdf_b200 0.2 (sm_100a)"; }
 
 const char* gsdf_last_error(gsdf_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
 
@@ -417,6 +540,8 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
 gsdf_status gsdf_destroy(gsdf_handle h) {
     if (!h) return GSDF_ERR_INVALID;
     cudaSetDevice(h->cfg.device);
+    cudaStreamSynchronize(h->stream_c);
+    cudaStreamSynchronize(h->stream_n);
     cudaStreamSynchronize(h->stream);
     free_all(h);
     return GSDF_OK;
@@ -425,6 +550,9 @@ gsdf_status gsdf_destroy(gsdf_handle h) {
 gsdf_status gsdf_reset(gsdf_handle h) {
     if (!h) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream_n));
     return clear_map(h);
 }
 
@@ -437,29 +565,41 @@ gsdf_status gsdf_get_normal_cache(gsdf_handle h, float* planes11) {
 gsdf_status gsdf_upload_frame(gsdf_handle h, const float* depth_host) {
     if (!h || !depth_host) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
     const size_t n = (size_t)h->cfg.width * h->cfg.height;
-    CUDA_TRY(h, cudaMemcpyAsync(h->d_depth_own, depth_host, sizeof(float) * n, cudaMemcpyHostToDevice, h->stream));
-    h->d_depth = h->d_depth_own;
+    float* dst = h->ring[h->sync_slot].d_depth;
+    CUDA_TRY(h, cudaMemcpyAsync(dst, depth_host, sizeof(float) * n, cudaMemcpyHostToDevice, h->stream));
+    h->d_depth = dst;
     h->normals_valid = false;
+    h->prepared = false;
     return GSDF_OK;
 }
 
 gsdf_status gsdf_set_frame_device(gsdf_handle h, const float* depth_dev) {
     if (!h || !depth_dev) return GSDF_ERR_INVALID;
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
     h->d_depth = depth_dev;
     h->normals_valid = false;
+    h->prepared = false;
     return GSDF_OK;
 }
 
 gsdf_status gsdf_compute_normals(gsdf_handle h, float* nx, float* ny, float* nz) {
     if (!h || !nx || !ny || !nz) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
-    gsdf_status s = ensure_normals(h);
+    gsdf_status s = ensure_frame(h);
     if (s != GSDF_OK) return s;
+    // every tile, including those without a valid pixel (the pipeline skips them): compute() of the whole image
+    s = launch_normals(h, h->d_depth, h->normals_buf, h->stream, false);
+    if (s != GSDF_OK) return s;
+    h->normals_valid = true;
     const size_t n = (size_t)h->cfg.width * h->cfg.height;
-    CUDA_TRY(h, cudaMemcpyAsync(nx, h->d_normals, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(h, cudaMemcpyAsync(ny, h->d_normals + n, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(h, cudaMemcpyAsync(nz, h->d_normals + 2 * n, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+    const float* nrm = h->d_normals[h->normals_buf];
+    CUDA_TRY(h, cudaMemcpyAsync(nx, nrm, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(ny, nrm + n, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(nz, nrm + 2 * n, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     return GSDF_OK;
 }
@@ -467,29 +607,25 @@ gsdf_status gsdf_compute_normals(gsdf_handle h, float* nx, float* ny, float* nz)
 gsdf_status gsdf_integrate(gsdf_handle h, const float* R9, const float* t3, gsdf_integrate_stats* stats) {
     if (!h || !R9 || !t3) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
-    gsdf_status s = ensure_normals(h);  // MapGradPixelSdfOmp.cpp:59
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    s = ensure_prepared(h);
+    if (s != GSDF_OK) return s;
+    s = ensure_normals(h);  // MapGradPixelSdfOmp.cpp:59
     if (s != GSDF_OK) return s;
     Pose pose;
     std::memcpy(pose.R, R9, sizeof(float) * 9);
     std::memcpy(pose.t, t3, sizeof(float) * 3);
-    const int n = h->cfg.width * h->cfg.height;
-    const size_t np = (size_t)n;
-    const int blocks = (n + 255) / 256;
-    s = by_variant(h, [&](auto V) {
-        ProfScope prof(h, GSDF_PROF_FUSE);
-        fuse_kernel<decltype(V)::value><<<blocks, 256, 0, h->stream>>>(
-            h->view, h->geom, pose, h->d_depth, h->d_normals, h->d_normals + np, h->d_normals + 2 * np, h->d_planes,
-            h->d_planes + np, h->d_planes + 4 * np, h->d_ctr);
-        return check_launch(h, "fuse_kernel");
-    });
+    s = launch_fuse(h, pose, 0, h->normals_buf, h->stream);
     if (s != GSDF_OK) return s;
     if (stats) {
         CUDA_TRY(h, cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
-        CUDA_TRY(h, cudaMemsetAsync(h->d_ctr, 0, 2 * sizeof(unsigned long long), h->stream));  // points, updates
         CUDA_TRY(h, cudaStreamSynchronize(h->stream));
-        stats->points = (int64_t)h->h_ctr->points;
-        stats->updates = (int64_t)h->h_ctr->updates;
+        stats->points = (int64_t)(h->h_ctr->points - h->last_points);
+        stats->updates = (int64_t)(h->h_ctr->updates - h->last_updates);
         stats->blocks = (int64_t)h->h_ctr->blocks;
+        h->last_points = h->h_ctr->points;
+        h->last_updates = h->h_ctr->updates;
         if (h->h_ctr->overflow) {
             h->err = "voxel-block hash full: samples dropped; raise gsdf_config.log2_capacity";
             return GSDF_ERR_CAPACITY;
@@ -509,7 +645,9 @@ gsdf_status gsdf_accumulate(gsdf_handle h, const float* R9, const float* t3, int
     if (!h || !R9 || !t3 || !out29 || sampling < 1) return GSDF_ERR_INVALID;
     if (!h->d_depth) { h->err = "no depth frame set"; return GSDF_ERR_NO_FRAME; }
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
-    gsdf_status s = set_pose_device(h, R9, t3);
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    s = set_pose_device(h, R9, t3);
     if (s != GSDF_OK) return s;
     s = accumulate_device(h, sampling);
     if (s != GSDF_OK) return s;
@@ -521,27 +659,30 @@ gsdf_status gsdf_accumulate(gsdf_handle h, const float* R9, const float* t3, int
 
 gsdf_status gsdf_track(gsdf_handle h, float* pose7, int32_t max_iters, float conv_threshold, float damping,
                        int32_t* converged, int32_t* iters_used) {
-    if (!h || !pose7 || !converged) return GSDF_ERR_INVALID;
-    const float thr_sq = conv_threshold * conv_threshold;  // RigidOptimizer.h:72
+    if (!h || !pose7 || !converged || max_iters < 0) return GSDF_ERR_INVALID;
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
     *converged = 0;
-    for (int k = 0; k < max_iters; ++k) {
-        float R[9], out[kAccTerms], H[36], xi[6];
-        quat_to_R(pose7 + 3, R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
-        gsdf_status s = gsdf_accumulate(h, R, pose7, 1, out);
-        if (s != GSDF_OK) return s;
-        h->track_iterations++;
-        h->track_valid += (int64_t)out[28];
-        int o = 6;
-        for (int a = 0; a < 6; ++a)
-            for (int b = a; b < 6; ++b) { H[6 * a + b] = out[o]; H[6 * b + a] = out[o]; ++o; }
-        gsdf_llt_solve6(H, out, xi);
-        bool has_nan = false;
-        float nrm = 0.f;
-        for (int i = 0; i < 6; ++i) { xi[i] = damping * xi[i]; has_nan |= std::isnan(xi[i]); nrm += xi[i] * xi[i]; }
-        if (nrm < thr_sq) { *converged = 1; if (iters_used) *iters_used = k; return GSDF_OK; }  // :95-98
-        if (!has_nan) { float np[7]; gsdf_pose_apply_increment(pose7, xi, np); std::memcpy(pose7, np, sizeof(np)); }  // :101-102
-    }
-    if (iters_used) *iters_used = max_iters;
+    if (iters_used) *iters_used = 0;
+    if (max_iters == 0) return ensure_frame(h);
+    s = ensure_prepared(h);
+    if (s != GSDF_OK) return s;
+    s = set_state_pose(h, pose7);
+    if (s != GSDF_OK) return s;
+    TrackParams tp;
+    tp.max_iters = max_iters;
+    tp.thr_sq = conv_threshold * conv_threshold;  // RigidOptimizer.h:72
+    tp.damping = damping;
+    s = launch_track(h, tp, h->stream);
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->d_state, sizeof(FrameState), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    std::memcpy(pose7, h->h_state->pose7, sizeof(float) * 7);
+    *converged = h->h_state->converged;
+    if (iters_used) *iters_used = h->h_state->iters;
+    h->track_iterations = (int64_t)h->h_state->track_iters;
+    h->track_valid = (int64_t)h->h_state->track_valid;
     return GSDF_OK;
 }
 
@@ -623,6 +764,110 @@ gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* di
     return s;
 }
 
+// ---- the asynchronous frame pipeline ------------------------------------------------------------------------
+gsdf_status gsdf_scan_set_pose(gsdf_handle h, const float* pose7) {
+    if (!h || !pose7) return GSDF_ERR_INVALID;
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    float R[9], pn[7];
+    gsdf_pose_matrix(pose7, R, pn);  // SE3(quaternion, t): normalised once, like RigidOptimizer::set_pose(SE3)
+    // stream-ordered after the frames already submitted; staging must outlive the copy -> synchronise the copy
+    CUDA_TRY(h, cudaMemcpyAsync(h->d_state, pn, sizeof(float) * 7, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_scan_set_tracker(gsdf_handle h, int32_t max_iters, float conv_threshold, float damping) {
+    if (!h || max_iters < 1) return GSDF_ERR_INVALID;
+    h->scan_tp.max_iters = max_iters;
+    h->scan_tp.thr_sq = conv_threshold * conv_threshold;
+    h->scan_tp.damping = damping;
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float* depth_dev, int32_t mode) {
+    if (!h || (!depth_host && !depth_dev) || (depth_host && depth_dev) || (mode != GSDF_SCAN_FUSE && mode != GSDF_SCAN_TRACK_FUSE))
+        return GSDF_ERR_INVALID;
+    if (h->seq_submitted - h->seq_collected >= kRing) {
+        h->err = "gsdf_scan_submit: 4 frames already in flight, call gsdf_scan_collect";
+        return GSDF_ERR_INVALID;
+    }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    const int64_t seq = h->seq_submitted;
+    FrameSlot& sl = h->ring[seq % kRing];
+    const size_t n = (size_t)h->cfg.width * h->cfg.height;
+    const float* frame = depth_dev;
+    if (depth_host) {
+        CUDA_TRY(h, cudaMemcpyAsync(sl.d_depth, depth_host, sizeof(float) * n, cudaMemcpyHostToDevice, h->stream_c));
+        CUDA_TRY(h, cudaEventRecord(sl.ev_up, h->stream_c));
+        CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_up, 0));
+        CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, sl.ev_up, 0));
+        frame = sl.d_depth;
+    }
+    // normals on their own stream: they overlap the tracker; buffer (seq & 1) was last read by the fusion of frame seq-2
+    const int nbuf = (int)(seq & 1);
+    if (seq >= 2) CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, h->ring[(seq - 2) % kRing].ev_fused, 0));
+    gsdf_status s = launch_normals(h, frame, nbuf, h->stream_n, true);
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaEventRecord(sl.ev_norm, h->stream_n));
+    s = launch_prepare(h, frame, h->stream);
+    if (s != GSDF_OK) return s;
+    if (mode == GSDF_SCAN_TRACK_FUSE) {
+        s = launch_track(h, h->scan_tp, h->stream);
+        if (s != GSDF_OK) return s;
+    }
+    CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_norm, 0));
+    Pose unused;
+    std::memset(&unused, 0, sizeof(unused));
+    s = launch_fuse(h, unused, mode == GSDF_SCAN_TRACK_FUSE ? 2 : 1, nbuf, h->stream);
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaEventRecord(sl.ev_fused, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(sl.h_state, h->d_state, sizeof(FrameState), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(sl.h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaEventRecord(sl.ev_done, h->stream));
+    sl.mode = mode;
+    h->seq_submitted++;
+    // the synchronous entry points see this frame as current once the pipeline has drained
+    h->d_depth = frame;
+    h->normals_buf = nbuf;
+    h->normals_valid = true;
+    h->prepared = true;
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
+    if (!h || !out) return GSDF_ERR_INVALID;
+    if (h->seq_collected == h->seq_submitted) { h->err = "gsdf_scan_collect: nothing pending"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    FrameSlot& sl = h->ring[h->seq_collected % kRing];
+    CUDA_TRY(h, cudaEventSynchronize(sl.ev_done));
+    h->seq_collected++;
+    const FrameState& st = *sl.h_state;
+    const Counters& c = *sl.h_ctr;
+    std::memcpy(out->pose7, st.pose7, sizeof(float) * 7);
+    const bool tracked = sl.mode == GSDF_SCAN_TRACK_FUSE;
+    out->converged = tracked ? st.converged : 1;
+    out->iters = tracked ? st.iters : 0;
+    out->fused = out->converged;
+    out->n_valid = st.n_valid;
+    out->points = (int64_t)(c.points - h->last_points);
+    out->updates = (int64_t)(c.updates - h->last_updates);
+    out->blocks = (int64_t)c.blocks;
+    out->track_iterations = (int64_t)st.track_iters - h->track_iterations;
+    out->track_valid = (int64_t)st.track_valid - h->track_valid;
+    h->last_points = c.points;
+    h->last_updates = c.updates;
+    h->track_iterations = (int64_t)st.track_iters;
+    h->track_valid = (int64_t)st.track_valid;
+    if (c.overflow) {
+        h->err = "voxel-block hash full: samples dropped; raise gsdf_config.log2_capacity";
+        return GSDF_ERR_CAPACITY;
+    }
+    return GSDF_OK;
+}
+
+int32_t gsdf_scan_pending(gsdf_handle h) { return h ? (int32_t)(h->seq_submitted - h->seq_collected) : 0; }
+
+// ---- pose algebra ---------------------------------------------------------------------------------------------
 void gsdf_pose_matrix(const float* pose7, float* R9, float* pose7_normalised) {
     float q[4] = {pose7[3], pose7[4], pose7[5], pose7[6]};
     quat_normalize(q);  // SE3(quaternion, t) constructor normalises
@@ -634,48 +879,16 @@ void gsdf_pose_matrix(const float* pose7, float* R9, float* pose7_normalised) {
 }
 
 void gsdf_pose_apply_increment(const float* pose7_in, const float* xi6, float* pose7_out) {
-    float a[6], qa[4], ta[3], qo[4], rt[3];
-    const float qb[4] = {pose7_in[3], pose7_in[4], pose7_in[5], pose7_in[6]};
-    for (int i = 0; i < 6; ++i) a[i] = -xi6[i];
-    se3_exp(a, qa, ta);
-    quat_mul(qa, qb, qo);
-    quat_rotate(qa, pose7_in, rt);
-    for (int i = 0; i < 3; ++i) pose7_out[i] = ta[i] + rt[i];
-    for (int i = 0; i < 4; ++i) pose7_out[3 + i] = qo[i];
+    pose_apply_increment(pose7_in, xi6, pose7_out);
 }
 
-void gsdf_llt_solve6(const float* H36, const float* g6, float* xi6) {
-    // unblocked lower Cholesky in place, stopping at the first non-positive pivot as Eigen's LLT does, then
-    // forward/back substitution
-    float A[36], y[6];
-    std::memcpy(A, H36, sizeof(A));
-    for (int k = 0; k < 6; ++k) {
-        float x = A[6 * k + k];
-        for (int j = 0; j < k; ++j) x -= A[6 * k + j] * A[6 * k + j];
-        if (x <= 0.f) break;
-        x = std::sqrt(x);
-        A[6 * k + k] = x;
-        for (int i = k + 1; i < 6; ++i) {
-            float s = A[6 * i + k];
-            for (int j = 0; j < k; ++j) s -= A[6 * i + j] * A[6 * k + j];
-            A[6 * i + k] = s / x;
-        }
-    }
-    for (int i = 0; i < 6; ++i) {
-        float s = g6[i];
-        for (int j = 0; j < i; ++j) s -= A[6 * i + j] * y[j];
-        y[i] = s / A[6 * i + i];
-    }
-    for (int i = 5; i >= 0; --i) {
-        float s = y[i];
-        for (int j = i + 1; j < 6; ++j) s -= A[6 * j + i] * xi6[j];
-        xi6[i] = s / A[6 * i + i];
-    }
-}
+void gsdf_llt_solve6(const float* H36, const float* g6, float* xi6) { llt_solve6(H36, g6, xi6); }
 
 gsdf_status gsdf_synchronize(gsdf_handle h) {
     if (!h) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream_c));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream_n));
     return check_overflow(h);
 }
 
@@ -769,6 +982,7 @@ gsdf_status gsdf_profile_enable(gsdf_handle h, int32_t on) {
 gsdf_status gsdf_profile_read(gsdf_handle h, int32_t kind, int64_t* launches, double* total_ms) {
     if (!h || kind < 0 || kind >= GSDF_PROF_KINDS || !launches || !total_ms) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream_n));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     double tot = 0.0;
     for (size_t i = 0; i < h->prof_used[kind]; ++i) {

@@ -1,0 +1,439 @@
+// Frame pipeline kernels (v2): everything a frame needs runs on the stream without a host round trip.
+//
+//   valid_count_kernel / valid_write_kernel   deterministic compaction of the z-valid pixels of the frame into
+//                                             vlist = {pixel index, z} (ascending pixel order), so that every
+//                                             lane of every warp downstream has work (the sphere scenes have
+//                                             ~20 % valid pixels, spatially clustered: a per-pixel grid leaves
+//                                             most warps idle and a few with all the work);
+//   track_kernel<V>                           the WHOLE Gauss-Newton loop of RigidPointOptimizer::optimize_sampled
+//                                             (RigidPointOptimizerOmp.cpp:44-106) as one persistent cooperative
+//                                             kernel: per-pixel lookup + Jacobian, warp -> block -> grid tree
+//                                             reduction of the 29 sums, and — redundantly in every CTA, on
+//                                             identical data, so no broadcast is needed — the 6x6 LLT solve,
+//                                             the stopping test and pose <- exp(-xi) * pose.  One grid.sync per
+//                                             iteration, no host involvement until the loop ends;
+//   accumulate_list_kernel<V> + solve_kernel  the same split into per-iteration launches, for sharded maps where
+//                                             an NCCL all-reduce sits between the sums and the solve;
+//   fuse_list_kernel<V>                       fusion over vlist, pose and converged flag read from the device;
+//   normals_tile_kernel                       FALS normals, skipping tiles without any valid pixel.
+#pragma once
+
+#include <cooperative_groups.h>
+
+#include "gsdf_kernels.cuh"
+#include "gsdf_pose.cuh"
+
+namespace gsdf {
+
+namespace cg = cooperative_groups;
+
+// Device-resident tracker / frame state (RigidOptimizer::pose_ and friends live here between calls).
+struct FrameState {
+    float pose7[7];             // tx ty tz qx qy qz qw, unit quaternion
+    int converged;              // result of the last optimize
+    int iters;                  // k at convergence, or max_iters
+    int n_valid;                // compacted z-valid pixels of the current frame
+    int done;                   // per-iteration path: loop finished (converged or exhausted)
+    int k;                      // per-iteration path: iteration counter
+    unsigned long long track_iters;   // cumulative Gauss-Newton iterations
+    unsigned long long track_valid;   // cumulative contributing pixels (the reference's `counter`)
+    float sums[32];             // last reduced sums
+};
+
+constexpr int kSegPixels = 2048;  // pixels per compaction segment (256 threads x 8)
+
+__device__ __forceinline__ bool z_valid(float z, float z_min, float z_max) { return !(z <= z_min || z >= z_max); }
+
+__global__ void __launch_bounds__(256)
+valid_count_kernel(const float* __restrict__ depth, int n, float z_min, float z_max, int* __restrict__ seg_counts) {
+    const int base = blockIdx.x * kSegPixels;
+    int c = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int i = base + k * 256 + threadIdx.x;
+        c += (i < n && z_valid(depth[i], z_min, z_max)) ? 1 : 0;
+    }
+    c = __reduce_add_sync(0xffffffffu, c);
+    __shared__ int sm[8];
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int s = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += sm[w];
+        seg_counts[blockIdx.x] = s;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+valid_write_kernel(const float* __restrict__ depth, int n, float z_min, float z_max, const int* __restrict__ seg_counts,
+                   int2* __restrict__ vlist, FrameState* st) {
+    __shared__ int s_base;
+    __shared__ int s_warp[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp == 0) {  // exclusive prefix of the segment counts before this block
+        int s = 0;
+        for (int b = lane; b < (int)blockIdx.x; b += 32) s += seg_counts[b];
+        s = __reduce_add_sync(0xffffffffu, s);
+        if (lane == 0) s_base = s;
+    }
+    __syncthreads();
+    int run = s_base;
+    const int base = blockIdx.x * kSegPixels;
+    float z[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int i = base + k * 256 + threadIdx.x;
+        z[k] = i < n ? depth[i] : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int i = base + k * 256 + threadIdx.x;
+        const bool v = i < n && z_valid(z[k], z_min, z_max);
+        const unsigned int mask = __ballot_sync(0xffffffffu, v);
+        if (lane == 0) s_warp[warp] = __popc(mask);
+        __syncthreads();
+        int off = run, tot = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { const int c = s_warp[w]; off += w < warp ? c : 0; tot += c; }
+        if (v) vlist[off + __popc(mask & ((1u << lane) - 1))] = make_int2(i, __float_as_int(z[k]));
+        run += tot;
+        __syncthreads();
+    }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) st->n_valid = run;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Per-pixel tracker term: residual, Jacobian, 29 accumulations (RigidPointOptimizerOmp.cpp:72-90).
+template <int VARIANT>
+__device__ __forceinline__ void track_pixel(const MapView& m, const FrameGeom& g, const TrackIntr& ti, const float* R,
+                                            const float* t, int idx, float z, float* acc) {
+    const int y = idx / g.w, x = idx - y * g.w;
+    const float x0 = ((float)x - ti.cx) * ti.fx_inv, y0 = ((float)y - ti.cy) * ti.fy_inv;
+    const float cx_ = x0 * z, cy_ = y0 * z;
+    const float px = dot3_rn(R[0], R[1], R[2], cx_, cy_, z) + t[0];
+    const float py = dot3_rn(R[3], R[4], R[5], cx_, cy_, z) + t[1];
+    const float pz = dot3_rn(R[6], R[7], R[8], cx_, cy_, z) + t[2];
+    float phi, g0, g1, g2;
+    const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2);
+    if (w0 > 0.f) {
+        float J[6];
+        J[0] = g0; J[1] = g1; J[2] = g2;
+        J[3] = py * g2 - pz * g1;
+        J[4] = pz * g0 - px * g2;
+        J[5] = px * g1 - py * g0;
+        int o = 6;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            acc[a] += phi * J[a];
+#pragma unroll
+            for (int b = a; b < 6; ++b) acc[o++] += J[a] * J[b];
+        }
+        acc[27] += phi * phi;
+        acc[28] += 1.f;
+    }
+}
+
+constexpr int kTrackThreads = 512;
+constexpr int kTrackWarps = kTrackThreads / 32;
+
+struct TrackParams {
+    int max_iters;
+    float thr_sq;
+    float damping;
+};
+
+// block-level stage of the tree: acc[29] per thread -> 29 sums per block in dst[0..28]
+template <int NWARPS>
+__device__ __forceinline__ void block_reduce_29(float* acc, float (*sm)[kAccStride], float* dst) {
+#pragma unroll
+    for (int i = 0; i < kAccTerms; ++i) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], off);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < kAccTerms; ++i) sm[warp][i] = acc[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < kAccTerms) {
+        float s = 0.f;
+#pragma unroll
+        for (int wq = 0; wq < NWARPS; ++wq) s += sm[wq][threadIdx.x];
+        dst[threadIdx.x] = s;
+    }
+}
+
+// grid-level stage, executed identically by whoever calls it: tot[term] = sum over blocks in block order
+template <int NWARPS>
+__device__ __forceinline__ void grid_reduce_29(const float* partials, int nblocks, float* tot) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int term = warp; term < kAccTerms; term += NWARPS) {
+        float s = 0.f;
+#pragma unroll 4
+        for (int b = lane; b < nblocks; b += 32) s += __ldcg(partials + (size_t)b * kAccStride + term);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        if (lane == 0) tot[term] = s;
+    }
+}
+
+template <int VARIANT>
+__global__ void __launch_bounds__(kTrackThreads, 1)
+track_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist, FrameState* st,
+             float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ float s_pose7[8];
+    __shared__ Pose s_pose;
+    __shared__ float s_tot[kAccStride];
+    __shared__ float s_warp[kTrackWarps][kAccStride];
+    __shared__ int s_conv;
+    if (threadIdx.x < 7) s_pose7[threadIdx.x] = st->pose7[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
+        s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+    }
+    __syncthreads();
+    const int n_valid = st->n_valid;
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+    int converged = 0, k = 0;
+    float valid_sum = 0.f;
+    for (k = 0; k < tp.max_iters; ++k) {
+        float acc[kAccTerms];
+#pragma unroll
+        for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
+        for (int j = gtid; j < n_valid; j += nthreads) {
+            const int2 e = __ldg(vlist + j);
+            track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc);
+        }
+        float* mine = partials + ((size_t)(k & 1) * gridDim.x + blockIdx.x) * kAccStride;
+        block_reduce_29<kTrackWarps>(acc, s_warp, mine);
+        grid.sync();
+        grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_tot);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            valid_sum += s_tot[28];
+            s_conv = gauss_newton_step(s_tot, tp.damping, tp.thr_sq, s_pose7);
+            quat_to_R(s_pose7 + 3, s_pose.R);
+            s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+        }
+        __syncthreads();
+        if (s_conv) { converged = 1; break; }
+    }
+    if (blockIdx.x == 0) {
+        if (threadIdx.x < 7) st->pose7[threadIdx.x] = s_pose7[threadIdx.x];
+        if (threadIdx.x < kAccTerms) st->sums[threadIdx.x] = s_tot[threadIdx.x];
+        if (threadIdx.x == 0) {
+            st->converged = converged;
+            st->iters = converged ? k : tp.max_iters;
+            st->track_iters += (unsigned long long)(converged ? k + 1 : tp.max_iters);
+            st->track_valid += (unsigned long long)valid_sum;
+        }
+    }
+}
+
+// Per-iteration variant (sharded maps): sums of this rank's pixels -> out29 (last-block-done), the caller
+// all-reduces out29 across ranks and then runs solve_kernel.  Exits at once when the loop is already done.
+template <int VARIANT>
+__global__ void __launch_bounds__(kAccThreads)
+accumulate_list_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist, const FrameState* st,
+                       float* __restrict__ partials, Counters* ctr, float* __restrict__ out29) {
+    if (st->done) return;
+    __shared__ Pose s_pose;
+    __shared__ float sm[kAccThreads / 32][kAccStride];
+    if (threadIdx.x == 0) {
+        float q[4] = {st->pose7[3], st->pose7[4], st->pose7[5], st->pose7[6]};
+        quat_to_R(q, s_pose.R);
+        s_pose.t[0] = st->pose7[0]; s_pose.t[1] = st->pose7[1]; s_pose.t[2] = st->pose7[2];
+    }
+    __syncthreads();
+    float acc[kAccTerms];
+#pragma unroll
+    for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
+    const int n_valid = st->n_valid;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += gridDim.x * blockDim.x) {
+        const int2 e = __ldg(vlist + j);
+        track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc);
+    }
+    block_reduce_29<kAccThreads / 32>(acc, sm, partials + (size_t)blockIdx.x * kAccStride);
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicInc(&ctr->ticket, gridDim.x - 1) == gridDim.x - 1);
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    grid_reduce_29<kAccThreads / 32>(partials, gridDim.x, out29);
+}
+
+__global__ void solve_kernel(FrameState* st, const float* __restrict__ sums29, TrackParams tp) {
+    if (threadIdx.x != 0 || st->done) return;
+    float pose7[7], sums[kAccTerms];
+    for (int i = 0; i < 7; ++i) pose7[i] = st->pose7[i];
+    for (int i = 0; i < kAccTerms; ++i) { sums[i] = sums29[i]; st->sums[i] = sums[i]; }
+    const int conv = gauss_newton_step(sums, tp.damping, tp.thr_sq, pose7);
+    for (int i = 0; i < 7; ++i) st->pose7[i] = pose7[i];
+    st->track_iters += 1;
+    st->track_valid += (unsigned long long)sums[28];
+    if (conv) { st->converged = 1; st->iters = st->k; st->done = 1; }
+    else if (++st->k >= tp.max_iters) { st->converged = 0; st->iters = tp.max_iters; st->done = 1; }
+}
+
+__global__ void track_begin_kernel(FrameState* st) {
+    if (threadIdx.x == 0) { st->done = 0; st->k = 0; st->converged = 0; st->iters = 0; }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Fusion over the compacted list.  pose_src: 0 = pose by value, 1 = pose from the device state (any), 2 = pose from
+// the device state and only if the last optimize converged (main_scan_3d.cpp:261).
+template <int VARIANT>
+__global__ void __launch_bounds__(256)
+fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2* __restrict__ vlist,
+                 const FrameState* __restrict__ st, const float* __restrict__ nx, const float* __restrict__ ny,
+                 const float* __restrict__ nz, const float* __restrict__ x0, const float* __restrict__ y0,
+                 const float* __restrict__ hom_inv, Counters* ctr) {
+    if (pose_src == 2 && !st->converged) return;
+    __shared__ Pose pose;
+    if (threadIdx.x == 0) {
+        if (pose_src == 0) pose = pose_arg;
+        else {
+            float q[4] = {st->pose7[3], st->pose7[4], st->pose7[5], st->pose7[6]};
+            quat_to_R(q, pose.R);  // pose.rotationMatrix() of the stored SE3
+            pose.t[0] = st->pose7[0]; pose.t[1] = st->pose7[1]; pose.t[2] = st->pose7[2];
+        }
+    }
+    __syncthreads();
+    const float* R = pose.R;
+    const int n_valid = st->n_valid;
+    unsigned int n_upd = 0, n_pts = 0;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += gridDim.x * blockDim.x) {
+        const int2 e = __ldg(vlist + j);
+        const int idx = e.x;
+        const float z = __int_as_float(e.y);
+        const float hx = x0[idx], hy = y0[idx];
+        const float a = nx[idx], b = ny[idx], c = nz[idx];
+        const float hi = hom_inv[idx];
+        const float nsq = dot3_rn(a, b, c, a, b, c);
+        const float d = dot3_rn(a, b, c, hx, hy, 1.f);
+        if ((double)nsq < .1) continue;                                       // MapGradPixelSdfOmp.cpp:97
+        if ((double)__fmul_rn(__fmul_rn(d, d), hi) < .25) continue;           // :100
+        ++n_pts;
+        const float Rxy0 = dot3_rn(R[0], R[1], R[2], hx, hy, 1.f);            // :93
+        const float Rxy1 = dot3_rn(R[3], R[4], R[5], hx, hy, 1.f);
+        const float Rxy2 = dot3_rn(R[6], R[7], R[8], hx, hy, 1.f);
+        float Rn0 = 0.f, Rn1 = 0.f, Rn2 = 0.f;
+        if (VARIANT == 0) {
+            Rn0 = dot3_rn(R[0], R[1], R[2], a, b, c);                         // :95
+            Rn1 = dot3_rn(R[3], R[4], R[5], a, b, c);
+            Rn2 = dot3_rn(R[6], R[7], R[8], a, b, c);
+        }
+        unsigned long long last_key = kEmptyKey;
+        int slot = -1;
+        for (int kk = -g.factor; kk <= g.factor; ++kk) {                      // :103
+            const float s = __fadd_rn(z, __fmul_rn((float)kk, g.vs));
+            const float px = __fadd_rn(__fmul_rn(s, Rxy0), pose.t[0]);        // :105
+            const float py = __fadd_rn(__fmul_rn(s, Rxy1), pose.t[1]);
+            const float pz = __fadd_rn(__fmul_rn(s, Rxy2), pose.t[2]);
+            const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
+            const float qx = __fsub_rn(__fmul_rn(g.vs, (float)vx), pose.t[0]);  // :107
+            const float qy = __fsub_rn(__fmul_rn(g.vs, (float)vy), pose.t[1]);
+            const float qz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pose.t[2]);
+            const float sdf = __fsub_rn(dot3_rn(R[2], R[5], R[8], qx, qy, qz), z);  // :107-108
+            const float wgt = sdf_weight(sdf, g.T, g.inv_T);
+            if (wgt > 0.f) {
+                const unsigned long long key = block_key_of(vx, vy, vz);
+                if (key != last_key) {
+                    last_key = key;
+                    if (m.world > 1 && block_owner(key, m.world) != m.rank) slot = -2;
+                    else {
+                        slot = map_find_or_insert(m, key, ctr);
+                        if (slot < 0) atomicAdd(&ctr->overflow, 1u);
+                    }
+                }
+                if (slot >= 0) {
+                    const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
+                    const float ws = wgt * sdf_truncate(sdf, g.T);
+                    if (VARIANT == 0) {
+                        atomicAdd(m.acc4 + addr, make_float4(ws, wgt * Rn0, wgt * Rn1, wgt * Rn2));  // :115-117
+                        atomicAdd(m.accW + addr, wgt);
+                    } else {
+                        atomicAdd(m.acc2 + addr, make_float2(wgt, ws));
+                    }
+                    ++n_upd;
+                }
+            }
+        }
+    }
+    n_pts = __reduce_add_sync(0xffffffffu, n_pts);
+    n_upd = __reduce_add_sync(0xffffffffu, n_upd);
+    if ((threadIdx.x & 31) == 0 && (n_pts | n_upd)) {
+        atomicAdd(&ctr->points, (unsigned long long)n_pts);
+        atomicAdd(&ctr->updates, (unsigned long long)n_upd);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// FALS normals per 32x16 tile (same arithmetic and summation order as normals_kernel, so bit-identical), but
+//   * tiles whose interior holds no z-valid pixel are skipped (fusion never reads normals of invalid pixels);
+//   * the z_inv products are widened to double once, when staged, instead of once per window tap.
+__global__ void __launch_bounds__(NT_W* NT_H)
+normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x0n, const float* __restrict__ y0n,
+                    const float* __restrict__ nsi, const float* __restrict__ Q, float* __restrict__ nx,
+                    float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r, float z_min, float z_max) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int tw = NT_W + 2 * r, th = NT_H + 2 * r;
+    double* a = reinterpret_cast<double*>(smem_raw);   // [3][th][tw] products, widened
+    double* rs = a + 3 * tw * th;                      // [3][th][NT_W] row sums
+    const int tid = threadIdx.y * NT_W + threadIdx.x;
+    const int x_base = blockIdx.x * NT_W, y_base = blockIdx.y * NT_H;
+    const int x = x_base + threadIdx.x, y = y_base + threadIdx.y;
+    const size_t n = (size_t)w * h;
+    const bool inside = x < w && y < h;
+    const float zc = inside ? depth[(size_t)y * w + x] : 0.f;
+    if (!__syncthreads_or(inside && z_valid(zc, z_min, z_max))) return;
+
+    for (int ly = threadIdx.y; ly < th; ly += NT_H) {
+        const int gy = reflect101(min(y_base + ly - r, h - 1 + r), h);
+        for (int lx = threadIdx.x; lx < tw; lx += NT_W) {
+            const int gx = reflect101(min(x_base + lx - r, w - 1 + r), w);
+            const size_t gi = (size_t)gy * w + gx;
+            const float z = depth[gi];
+            const float zi = z != 0.f ? __fdiv_rn(1.f, z) : 0.f;           // NormalEstimator.h:181-187
+            const int i = ly * tw + lx;
+            a[i] = (double)__fmul_rn(x0n[gi], zi);                          // :191
+            a[tw * th + i] = (double)__fmul_rn(y0n[gi], zi);                // :192
+            a[2 * tw * th + i] = (double)__fmul_rn(nsi[gi], zi);            // :193
+        }
+    }
+    __syncthreads();
+    for (int p = 0; p < 3; ++p)
+        for (int ly = threadIdx.y; ly < th; ly += NT_H) {
+            const double* row = a + p * tw * th + ly * tw + threadIdx.x;
+            double s = 0.0;
+            for (int d = 0; d <= 2 * r; ++d) s = __dadd_rn(s, row[d]);      // left -> right
+            rs[(p * th + ly) * NT_W + threadIdx.x] = s;
+        }
+    __syncthreads();
+    if (!inside) return;
+    double s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    for (int d = 0; d <= 2 * r; ++d) {                                      // top -> bottom
+        const int j = (threadIdx.y + d) * NT_W + threadIdx.x;
+        s1 = __dadd_rn(s1, rs[j]);
+        s2 = __dadd_rn(s2, rs[th * NT_W + j]);
+        s3 = __dadd_rn(s3, rs[2 * th * NT_W + j]);
+    }
+    const float b1 = (float)s1, b2 = (float)s2, b3 = (float)s3;
+    const size_t gi = (size_t)y * w + x;
+    const float q11 = Q[gi], q12 = Q[n + gi], q13 = Q[2 * n + gi], q22 = Q[3 * n + gi], q23 = Q[4 * n + gi], q33 = Q[5 * n + gi];
+    const float vx = __fadd_rn(__fadd_rn(__fmul_rn(b1, q11), __fmul_rn(b2, q12)), __fmul_rn(b3, q13));
+    const float vy = __fadd_rn(__fadd_rn(__fmul_rn(b1, q12), __fmul_rn(b2, q22)), __fmul_rn(b3, q23));
+    const float vz = __fadd_rn(__fadd_rn(__fmul_rn(b1, q13), __fmul_rn(b2, q23)), __fmul_rn(b3, q33));
+    const float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)), __fmul_rn(vz, vz)));
+    nx[gi] = __fdiv_rn(vx, nn);
+    ny[gi] = __fdiv_rn(vy, nn);
+    nz[gi] = __fdiv_rn(vz, nn);
+}
+
+}  // namespace gsdf

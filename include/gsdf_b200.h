@@ -122,6 +122,40 @@ gsdf_status gsdf_voxel_count(gsdf_handle h, int64_t* n_voxels, int64_t* n_blocks
 gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* dist, float* weight, float* grad,
                           int64_t* n_out);
 
+/* -- the frame pipeline: main_scan_3d.cpp:208-266 without the host in the loop --------------------------------
+ * The reference's loop body is "optimize(depth); if (converged) update(depth, pose())" with the pose living in the
+ * optimizer object.  Here the pose, the converged flag and the frame's compacted pixel list live on the device, so a
+ * whole frame (upload, pixel compaction, the complete Gauss-Newton loop, normals, conditional fusion, result
+ * read-back) is enqueued by ONE call and up to 4 frames may be in flight: the host only feeds frames and collects
+ * results, it never gates the GPU.  Frame i+1 is tracked from the pose frame i ended with (as pose_ persists in
+ * RigidOptimizer, RigidOptimizer.h:66).  Do not mix with the synchronous calls while frames are pending. */
+enum { GSDF_SCAN_FUSE = 0,        /* fuse at the current pose without tracking: setup() / ground-truth poses */
+       GSDF_SCAN_TRACK_FUSE = 1   /* optimize, then update iff converged (main_scan_3d.cpp:258-264) */ };
+
+typedef struct gsdf_frame_result {
+    float pose7[7];            /* pose after this frame (RigidOptimizer::pose()) */
+    int32_t converged;         /* optimize()'s return value (1 for GSDF_SCAN_FUSE frames) */
+    int32_t iters;             /* k at convergence, or max_iters */
+    int32_t fused;             /* whether the frame was integrated */
+    int32_t n_valid;           /* pixels inside the depth range */
+    int64_t points, updates;   /* this frame's "points integrated" and voxel updates */
+    int64_t blocks;            /* blocks allocated so far */
+    int64_t track_iterations;  /* Gauss-Newton passes run for this frame (iters + 1 when converged) */
+    int64_t track_valid;       /* contributing pixels summed over those passes */
+} gsdf_frame_result;
+
+/* RigidOptimizer::set_pose (RigidOptimizer.h:104): pose7 goes through the SE3(quaternion, t) constructor. */
+gsdf_status gsdf_scan_set_pose(gsdf_handle h, const float* pose7);
+/* set_num_iterations / set_conv_threshold / set_damping (RigidOptimizer.h:90-102); defaults 25, 1e-3, 1. */
+gsdf_status gsdf_scan_set_tracker(gsdf_handle h, int32_t max_iters, float conv_threshold, float damping);
+/* Enqueue one frame: exactly one of depth_host (pinned memory recommended; copied on a separate copy stream, so
+ * the upload of frame i+1 overlaps the work on frame i) or depth_dev (already in HBM, must stay valid until the
+ * frame is collected).  Returns at once; GSDF_ERR_INVALID if 4 frames are already pending. */
+gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float* depth_dev, int32_t mode);
+/* Wait for the oldest pending frame and return its result. */
+gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out);
+int32_t gsdf_scan_pending(gsdf_handle h);
+
 /* -- pose algebra used by the tracker (Sophus::SE3f semantics: so3.hpp:297-303,325-339,356-366,583-619,
  *    se3.hpp:761-782; Eigen toRotationMatrix), exported so callers without Sophus get identical poses -------- */
 void gsdf_pose_matrix(const float* pose7, float* R9, float* pose7_normalised /* may be NULL */);
