@@ -336,6 +336,7 @@ def run_ours(args):
         n_f, ms_f = sdf.profile_read(1)
         n_a, ms_a = sdf.profile_read(2)
         n_n, ms_n = sdf.profile_read(0)
+        n_p, ms_p = sdf.profile_read(3)
         nv, nb = sdf.voxel_count()
         K_steps = args.steps
         t_dev = max_over_ranks(a["t_ms"])
@@ -355,7 +356,8 @@ def run_ours(args):
             "track_iters": c["track_iters"], "nrm_bytes": nrm_bytes, "voxel_updates_per_s": 1e3 * c["updates"] / max(ms_f, 1e-9),
             "updates_per_frame": upd_total / max(1, a["conv"]), "converged_steps": a["conv"],
             "gn_iterations": a["iters"], "launches": a["launches"], "voxels": nv, "blocks": nb,
-            "kernel_ms": {"normals": [n_n, ms_n], "fuse": [n_f, ms_f], "accumulate": [n_a, ms_a]},
+            "kernel_ms": {"normals": [n_n, ms_n], "fuse": [n_f, ms_f], "accumulate": [n_a, ms_a],
+                          "prepare": [n_p, ms_p]},
             "fuse_bytes": fuse_bytes, "acc_bytes": acc_bytes, "fuse_GBps": fuse_bytes / max(ms_f, 1e-9) / 1e6 if n_f else None,
             "clocks": clocks, "wall_s_dev": a["wall_s"], "wall_s_host": b["wall_s"], "b_v": b_v, "b_t": b_t,
             "final_pose": a["final_pose"],

@@ -74,10 +74,11 @@ struct gsdf_map {
     float* d_planes = nullptr;        // 11 cached planes
     const float* d_depth = nullptr;   // current frame (ring slot or caller's device buffer)
     float* d_normals[2] = {nullptr, nullptr};
-    int normals_buf = 0;              // buffer holding the current frame's normals
+    int normals_buf = 0;              // buffer index (normals, vlist, nvalid) of the current frame
     bool normals_valid = false, prepared = false;
-    int2* d_vlist = nullptr;
-    int* d_seg_counts = nullptr;
+    int2* d_vlist[2] = {nullptr, nullptr};  // compacted valid pixels, double-buffered like the normals
+    int* d_nvalid = nullptr;                // [2] counts of the two lists
+    int* d_seg_counts = nullptr;            // [2][nseg]
     int nseg = 0;
     FrameState* d_state = nullptr;
     Counters* d_ctr = nullptr;
@@ -97,6 +98,7 @@ struct gsdf_map {
     std::vector<float> h_planes;
     // frame pipeline
     FrameSlot ring[kRing];
+    cudaEvent_t ev_main = nullptr;    // orders the side streams after earlier synchronous-API work on `stream`
     int64_t seq_submitted = 0, seq_collected = 0;
     int sync_slot = 0;                // ring slot used by gsdf_upload_frame
     TrackParams scan_tp{25, 1e-6f, 1.f};
@@ -106,7 +108,7 @@ struct gsdf_map {
     int64_t track_iterations = 0, track_valid = 0;
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[GSDF_PROF_KINDS];
-    size_t prof_used[GSDF_PROF_KINDS] = {0, 0, 0};
+    size_t prof_used[GSDF_PROF_KINDS] = {0, 0, 0, 0};
     ncclComm_t comm = nullptr;
     std::string err;
 };
@@ -237,14 +239,16 @@ gsdf_status launch_normals(gsdf_map* h, const float* depth, int buf, cudaStream_
     return check_launch(h, "normals_tile_kernel");
 }
 
-// compaction of the current frame's z-valid pixels (deterministic order) into d_vlist, count into d_state->n_valid
-gsdf_status launch_prepare(gsdf_map* h, const float* depth, cudaStream_t stream) {
+// compaction of a frame's z-valid pixels (deterministic, ascending order) into d_vlist[buf], count into d_nvalid[buf]
+gsdf_status launch_prepare(gsdf_map* h, const float* depth, int buf, cudaStream_t stream) {
     const int n = h->cfg.width * h->cfg.height;
-    valid_count_kernel<<<h->nseg, 256, 0, stream>>>(depth, n, h->geom.z_min, h->geom.z_max, h->d_seg_counts);
+    int* counts = h->d_seg_counts + (size_t)buf * h->nseg;
+    ProfScope prof(h, GSDF_PROF_PREPARE, stream);
+    valid_count_kernel<<<h->nseg, 256, 0, stream>>>(depth, n, h->geom.z_min, h->geom.z_max, counts);
     gsdf_status s = check_launch(h, "valid_count_kernel");
     if (s != GSDF_OK) return s;
-    valid_write_kernel<<<h->nseg, 256, 0, stream>>>(depth, n, h->geom.z_min, h->geom.z_max, h->d_seg_counts, h->d_vlist,
-                                                    h->d_state);
+    valid_write_kernel<<<h->nseg, 256, 0, stream>>>(depth, n, h->geom.z_min, h->geom.z_max, counts, h->d_vlist[buf],
+                                                    h->d_nvalid + buf);
     return check_launch(h, "valid_write_kernel");
 }
 
@@ -256,7 +260,7 @@ gsdf_status ensure_frame(gsdf_map* h) {
 gsdf_status ensure_prepared(gsdf_map* h) {
     gsdf_status s = ensure_frame(h);
     if (s != GSDF_OK || h->prepared) return s;
-    s = launch_prepare(h, h->d_depth, h->stream);
+    s = launch_prepare(h, h->d_depth, h->normals_buf, h->stream);
     if (s == GSDF_OK) h->prepared = true;
     return s;
 }
@@ -277,14 +281,15 @@ gsdf_status launch_fuse(gsdf_map* h, const Pose& pose, int pose_src, int nbuf, c
     return by_variant(h, [&](auto V) {
         ProfScope prof(h, GSDF_PROF_FUSE, stream);
         fuse_list_kernel<decltype(V)::value><<<blocks, 256, 0, stream>>>(
-            h->view, h->geom, pose, pose_src, h->d_vlist, h->d_state, nrm, nrm + np, nrm + 2 * np, h->d_planes,
+            h->view, h->geom, pose, pose_src, h->d_vlist[nbuf], h->d_nvalid + nbuf, h->d_state, nrm, nrm + np,
+            nrm + 2 * np, h->d_planes,
             h->d_planes + np, h->d_planes + 4 * np, h->d_ctr);
         return check_launch(h, "fuse_list_kernel");
     });
 }
 
 // the Gauss-Newton loop from the pose in d_state; result (pose, converged, iters) stays in d_state
-gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, cudaStream_t stream) {
+gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream_t stream) {
     const TrackIntr ti = make_intr(h, 1);
     if (h->cfg.world_size == 1) {
         return by_variant(h, [&](auto V) {
@@ -292,11 +297,12 @@ gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, cudaStream_t stream
             MapView view = h->view;
             FrameGeom geom = h->geom;
             TrackIntr ti_ = ti;
-            const int2* vlist = h->d_vlist;
+            const int2* vlist = h->d_vlist[buf];
+            const int* nvalid = h->d_nvalid + buf;
             FrameState* st = h->d_state;
             float* partials = h->d_track_partials;
             TrackParams tp_ = tp;
-            void* args[] = {&view, &geom, &ti_, &vlist, &st, &partials, &tp_};
+            void* args[] = {&view, &geom, &ti_, &vlist, &nvalid, &st, &partials, &tp_};
             cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_kernel<decltype(V)::value>, dim3(h->track_blocks),
                                                         dim3(kTrackThreads), args, 0, stream);
             if (e != cudaSuccess) { h->err = std::string("cudaLaunchCooperativeKernel(track_kernel): ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
@@ -314,7 +320,8 @@ gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, cudaStream_t stream
             s = by_variant(h, [&](auto V) {
                 ProfScope prof(h, GSDF_PROF_ACCUMULATE, stream);
                 accumulate_list_kernel<decltype(V)::value><<<h->acc_blocks, kAccThreads, 0, stream>>>(
-                    h->view, h->geom, ti, h->d_vlist, h->d_state, h->d_partials, h->d_ctr, h->d_out29);
+                    h->view, h->geom, ti, h->d_vlist[buf], h->d_nvalid + buf, h->d_state, h->d_partials, h->d_ctr,
+                    h->d_out29);
                 return check_launch(h, "accumulate_list_kernel");
             });
             if (s != GSDF_OK) return s;
@@ -359,7 +366,7 @@ void free_all(gsdf_map* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
     cudaFree(h->d_planes); cudaFree(h->d_normals[0]); cudaFree(h->d_normals[1]); cudaFree(h->d_ctr);
-    cudaFree(h->d_vlist); cudaFree(h->d_seg_counts); cudaFree(h->d_state); cudaFree(h->d_track_partials);
+    cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_seg_counts); cudaFree(h->d_state); cudaFree(h->d_track_partials);
     cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
     cudaFreeHost(h->h_state);
@@ -371,6 +378,7 @@ void free_all(gsdf_map* h) {
         if (sl.ev_done) cudaEventDestroy(sl.ev_done);
     }
     for (auto& v : h->prof_events) for (auto& pr : v) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+    if (h->ev_main) cudaEventDestroy(h->ev_main);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->stream_n) cudaStreamDestroy(h->stream_n);
     if (h->stream_c) cudaStreamDestroy(h->stream_c);
@@ -401,9 +409,12 @@ gsdf_status create_impl(gsdf_map* h) {
     CUDA_TRY(h, cudaMalloc(&h->d_planes, sizeof(float) * n * 11));
     CUDA_TRY(h, cudaMalloc(&h->d_normals[0], sizeof(float) * n * 3));
     CUDA_TRY(h, cudaMalloc(&h->d_normals[1], sizeof(float) * n * 3));
-    CUDA_TRY(h, cudaMalloc(&h->d_vlist, sizeof(int2) * n));
+    CUDA_TRY(h, cudaMalloc(&h->d_vlist[0], sizeof(int2) * n));
+    CUDA_TRY(h, cudaMalloc(&h->d_vlist[1], sizeof(int2) * n));
+    CUDA_TRY(h, cudaMalloc(&h->d_nvalid, sizeof(int) * 2));
+    CUDA_TRY(h, cudaMemset(h->d_nvalid, 0, sizeof(int) * 2));
     h->nseg = (int)((n + kSegPixels - 1) / kSegPixels);
-    CUDA_TRY(h, cudaMalloc(&h->d_seg_counts, sizeof(int) * h->nseg));
+    CUDA_TRY(h, cudaMalloc(&h->d_seg_counts, sizeof(int) * 2 * h->nseg));
     CUDA_TRY(h, cudaMalloc(&h->d_state, sizeof(FrameState)));
     CUDA_TRY(h, cudaMalloc(&h->d_ctr, sizeof(Counters)));
     h->acc_blocks = h->sm_count * 2;
@@ -432,6 +443,7 @@ gsdf_status create_impl(gsdf_map* h) {
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_fused, cudaEventDisableTiming));
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
     }
+    CUDA_TRY(h, cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
     if (normals_smem(h) > 48 * 1024)
         CUDA_TRY(h, cudaFuncSetAttribute(normals_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
     build_normal_cache(c, h->h_planes);
@@ -578,6 +590,7 @@ gsdf_status gsdf_upload_frame(gsdf_handle h, const float* depth_host) {
 
 gsdf_status gsdf_set_frame_device(gsdf_handle h, const float* depth_dev) {
     if (!h || !depth_dev) return GSDF_ERR_INVALID;
+    if ((uintptr_t)depth_dev & 15) { h->err = "device frame must be 16-byte aligned"; return GSDF_ERR_INVALID; }
     gsdf_status s = pipeline_idle(h);
     if (s != GSDF_OK) return s;
     h->d_depth = depth_dev;
@@ -674,7 +687,7 @@ gsdf_status gsdf_track(gsdf_handle h, float* pose7, int32_t max_iters, float con
     tp.max_iters = max_iters;
     tp.thr_sq = conv_threshold * conv_threshold;  // RigidOptimizer.h:72
     tp.damping = damping;
-    s = launch_track(h, tp, h->stream);
+    s = launch_track(h, tp, h->normals_buf, h->stream);
     if (s != GSDF_OK) return s;
     CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->d_state, sizeof(FrameState), cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));
@@ -787,6 +800,7 @@ gsdf_status gsdf_scan_set_tracker(gsdf_handle h, int32_t max_iters, float conv_t
 gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float* depth_dev, int32_t mode) {
     if (!h || (!depth_host && !depth_dev) || (depth_host && depth_dev) || (mode != GSDF_SCAN_FUSE && mode != GSDF_SCAN_TRACK_FUSE))
         return GSDF_ERR_INVALID;
+    if (depth_dev && ((uintptr_t)depth_dev & 15)) { h->err = "device frame must be 16-byte aligned"; return GSDF_ERR_INVALID; }
     if (h->seq_submitted - h->seq_collected >= kRing) {
         h->err = "gsdf_scan_submit: 4 frames already in flight, call gsdf_scan_collect";
         return GSDF_ERR_INVALID;
@@ -796,6 +810,13 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
     FrameSlot& sl = h->ring[seq % kRing];
     const size_t n = (size_t)h->cfg.width * h->cfg.height;
     const float* frame = depth_dev;
+    if (h->seq_submitted == h->seq_collected) {
+        // pipeline was idle: whatever the synchronous entry points left running on the main stream may still use
+        // the buffers the side streams are about to overwrite
+        CUDA_TRY(h, cudaEventRecord(h->ev_main, h->stream));
+        CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, h->ev_main, 0));
+        CUDA_TRY(h, cudaStreamWaitEvent(h->stream_c, h->ev_main, 0));
+    }
     if (depth_host) {
         CUDA_TRY(h, cudaMemcpyAsync(sl.d_depth, depth_host, sizeof(float) * n, cudaMemcpyHostToDevice, h->stream_c));
         CUDA_TRY(h, cudaEventRecord(sl.ev_up, h->stream_c));
@@ -803,19 +824,21 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
         CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, sl.ev_up, 0));
         frame = sl.d_depth;
     }
-    // normals on their own stream: they overlap the tracker; buffer (seq & 1) was last read by the fusion of frame seq-2
+    // Pixel compaction and normals depend only on the frame, not on the map or the pose: they run on the side
+    // stream and, with two or more frames in flight, overlap the previous frame's tracking and fusion.  Their
+    // buffers (index seq & 1) were last read by the tracker/fusion of frame seq-2.
     const int nbuf = (int)(seq & 1);
     if (seq >= 2) CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, h->ring[(seq - 2) % kRing].ev_fused, 0));
-    gsdf_status s = launch_normals(h, frame, nbuf, h->stream_n, true);
+    gsdf_status s = launch_prepare(h, frame, nbuf, h->stream_n);
+    if (s != GSDF_OK) return s;
+    s = launch_normals(h, frame, nbuf, h->stream_n, true);
     if (s != GSDF_OK) return s;
     CUDA_TRY(h, cudaEventRecord(sl.ev_norm, h->stream_n));
-    s = launch_prepare(h, frame, h->stream);
-    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_norm, 0));
     if (mode == GSDF_SCAN_TRACK_FUSE) {
-        s = launch_track(h, h->scan_tp, h->stream);
+        s = launch_track(h, h->scan_tp, nbuf, h->stream);
         if (s != GSDF_OK) return s;
     }
-    CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_norm, 0));
     Pose unused;
     std::memset(&unused, 0, sizeof(unused));
     s = launch_fuse(h, unused, mode == GSDF_SCAN_TRACK_FUSE ? 2 : 1, nbuf, h->stream);

@@ -71,9 +71,18 @@ __device__ __forceinline__ int block_owner(unsigned long long key, int world) {
     return (int)((mix64(key) >> 40) % (unsigned long long)world);
 }
 
+// Table hash: 32-bit multiply/xorshift mixing (the 64-bit finaliser above costs ~4x the integer instructions and
+// sits on the dependent path of every lookup; the hash function is not observable, only the key set is).
+__device__ __forceinline__ uint32_t hash_key(unsigned long long key) {
+    uint32_t h = (uint32_t)key * 0x9E3779B1u;
+    h ^= (uint32_t)(key >> 32) * 0x85EBCA6Bu;
+    h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 12; h *= 0x297A2D39u; h ^= h >> 15;
+    return h;
+}
+
 // Read-only probe.  Returns the slot or -1.
 __device__ __forceinline__ int map_find(const MapView& m, unsigned long long key) {
-    uint32_t slot = (uint32_t)mix64(key) & m.cap_mask;
+    uint32_t slot = hash_key(key) & m.cap_mask;
 #pragma unroll 1
     for (int probe = 0; probe < kMaxProbe; ++probe) {
         const unsigned long long k = __ldcg(m.keys + slot);
@@ -87,7 +96,7 @@ __device__ __forceinline__ int map_find(const MapView& m, unsigned long long key
 // Find-or-insert (the reference's tsdf_[vi], MapGradPixelSdfOmp.cpp:114, at block granularity).
 // Returns the slot, or -1 if kMaxProbe slots were all taken by other keys (caller raises overflow).
 __device__ __forceinline__ int map_find_or_insert(const MapView& m, unsigned long long key, Counters* ctr) {
-    uint32_t slot = (uint32_t)mix64(key) & m.cap_mask;
+    uint32_t slot = hash_key(key) & m.cap_mask;
 #pragma unroll 1
     for (int probe = 0; probe < kMaxProbe; ++probe) {
         unsigned long long k = __ldcg(m.keys + slot);

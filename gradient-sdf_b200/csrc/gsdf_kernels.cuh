@@ -181,12 +181,17 @@ struct Lookup;
 template <>
 struct Lookup<0> {  // MapGradPixelSdf.h:109-125
     // returns weight; if > 0 fills phi and grad
+    // ck/cs: caller-held cache of the last probed block (key -> slot, slot < 0 = absent).  The map does not change
+    // while it is being tracked against, so a thread that revisits the same pixel in the next Gauss-Newton pass
+    // (the pose moves by far less than a block) skips the dependent key load.
     __device__ static __forceinline__ float eval(const MapView& m, const FrameGeom& g, float px, float py, float pz,
-                                                 float& phi, float& g0, float& g1, float& g2) {
+                                                 float& phi, float& g0, float& g1, float& g2,
+                                                 unsigned long long& ck, int& cs) {
         const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
         const unsigned long long key = block_key_of(vx, vy, vz);
         if (m.world > 1 && block_owner(key, m.world) != m.rank) return 0.f;
-        const int slot = map_find(m, key);
+        if (key != ck) { ck = key; cs = map_find(m, key); }
+        const int slot = cs;
         if (slot < 0) return 0.f;
         const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
         const float W = m.accW[addr];
@@ -209,26 +214,38 @@ struct Lookup<0> {  // MapGradPixelSdf.h:109-125
 template <>
 struct Lookup<1> {  // MapPixelSdf.h:107-143 + interp3, MapPixelSdfOmp.cpp:44-113
     __device__ static __forceinline__ float eval(const MapView& m, const FrameGeom& g, float px, float py, float pz,
-                                                 float& phi, float& g0, float& g1, float& g2) {
+                                                 float& phi, float& g0, float& g1, float& g2,
+                                                 unsigned long long& ck, int& cs) {
         const float fx = __fmul_rn(g.vs_inv, px), fy = __fmul_rn(g.vs_inv, py), fz = __fmul_rn(g.vs_inv, pz);
         const int im = (int)floorf(fx), jm = (int)floorf(fy), km = (int)floorf(fz);
         float d[8];
         float Wn = 0.f;
         const int rx = (int)roundf(fx) - im, ry = (int)roundf(fy) - jm, rz = (int)roundf(fz) - km;  // nearest corner
-        unsigned long long last_key = kEmptyKey;
-        int slot = -1;
+        // resolve the (at most 8, usually 1) blocks first, then issue all 8 voxel loads before looking at any of
+        // them: one memory round trip instead of eight dependent ones
+        size_t addr[8];
+        unsigned long long last_key = ck;
+        int slot = cs;
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
-            const int i0 = c & 1, j0 = (c >> 1) & 1, k0 = c >> 2;
-            const int vx = im + i0, vy = jm + j0, vz = km + k0;
+            const int vx = im + (c & 1), vy = jm + ((c >> 1) & 1), vz = km + (c >> 2);
             const unsigned long long key = block_key_of(vx, vy, vz);
             if (key != last_key) { last_key = key; slot = map_find(m, key); }
+            if (c == 0) { ck = last_key; cs = slot; }
             if (slot < 0) return 0.f;  // weights(): all 8 corners must exist (MapPixelSdf.h:127-136)
-            const float2 v = m.acc2[(size_t)slot * kBlockVoxels + local_index(vx, vy, vz)];
-            if (!(v.x > 0.f)) return 0.f;
-            d[c] = v.y / v.x;
-            if (i0 == rx && j0 == ry && k0 == rz) Wn = v.x;
+            addr[c] = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
         }
+        float2 v[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) v[c] = m.acc2[addr[c]];
+        bool all = true;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            all = all && (v[c].x > 0.f);
+            d[c] = v[c].y / v[c].x;
+            if ((c & 1) == rx && ((c >> 1) & 1) == ry && (c >> 2) == rz) Wn = v[c].x;
+        }
+        if (!all) return 0.f;
         const float dx = fx - (float)im, dy = fy - (float)jm, dz = fz - (float)km;
         const float d01 = (1.f - dx) * d[0] + dx * d[1], d23 = (1.f - dx) * d[2] + dx * d[3];
         const float d45 = (1.f - dx) * d[4] + dx * d[5], d67 = (1.f - dx) * d[6] + dx * d[7];
@@ -250,7 +267,9 @@ query_kernel(MapView m, FrameGeom g, const float* __restrict__ pts, long long n,
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float f = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f;
-    const float w0 = Lookup<VARIANT>::eval(m, g, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], f, g0, g1, g2);
+    unsigned long long ck = kEmptyKey;
+    int cs = -1;
+    const float w0 = Lookup<VARIANT>::eval(m, g, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], f, g0, g1, g2, ck, cs);
     if (!(w0 > 0.f)) { f = 0.f; g0 = g1 = g2 = 0.f; }
     w[i] = w0; phi[i] = f;
     grad[3 * i] = g0; grad[3 * i + 1] = g1; grad[3 * i + 2] = g2;
@@ -293,7 +312,9 @@ accumulate_kernel(MapView m, FrameGeom g, TrackIntr ti, const Pose* __restrict__
         const float py = dot3_rn(R[3], R[4], R[5], cx_, cy_, z) + pose.t[1];
         const float pz = dot3_rn(R[6], R[7], R[8], cx_, cy_, z) + pose.t[2];
         float phi, g0, g1, g2;
-        const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2);
+        unsigned long long ck = kEmptyKey;
+        int cs = -1;
+        const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2, ck, cs);
         if (w0 > 0.f) {
             float J[6];
             J[0] = g0; J[1] = g1; J[2] = g2;
@@ -381,7 +402,9 @@ accumulate_static_kernel(MapView m, FrameGeom g, TrackIntr ti, Pose pose, const 
             const float py = dot3_rn(R[3], R[4], R[5], cx_, cy_, z) + pose.t[1];
             const float pz = dot3_rn(R[6], R[7], R[8], cx_, cy_, z) + pose.t[2];
             float phi, g0, g1, g2;
-            const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2);
+            unsigned long long ck = kEmptyKey;
+            int cs = -1;
+            const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2, ck, cs);
             if (w0 > 0.f) {
                 float J[6];
                 J[0] = g0; J[1] = g1; J[2] = g2;

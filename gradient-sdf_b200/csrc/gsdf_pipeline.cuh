@@ -44,15 +44,27 @@ constexpr int kSegPixels = 2048;  // pixels per compaction segment (256 threads 
 
 __device__ __forceinline__ bool z_valid(float z, float z_min, float z_max) { return !(z <= z_min || z >= z_max); }
 
+// Each thread owns 8 CONSECUTIVE pixels (two 16-byte loads), so ascending pixel order is thread order and one
+// block-wide exclusive scan of the per-thread counts places everything.
+__device__ __forceinline__ void load8(const float* __restrict__ depth, int i0, int n, float* z) {
+    if (i0 + 8 <= n) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(depth + i0));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(depth + i0 + 4));
+        z[0] = a.x; z[1] = a.y; z[2] = a.z; z[3] = a.w; z[4] = b.x; z[5] = b.y; z[6] = b.z; z[7] = b.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) z[k] = (i0 + k < n) ? depth[i0 + k] : 0.f;
+    }
+}
+
 __global__ void __launch_bounds__(256)
 valid_count_kernel(const float* __restrict__ depth, int n, float z_min, float z_max, int* __restrict__ seg_counts) {
-    const int base = blockIdx.x * kSegPixels;
+    const int i0 = blockIdx.x * kSegPixels + threadIdx.x * 8;
+    float z[8];
+    load8(depth, i0, n, z);
     int c = 0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const int i = base + k * 256 + threadIdx.x;
-        c += (i < n && z_valid(depth[i], z_min, z_max)) ? 1 : 0;
-    }
+    for (int k = 0; k < 8; ++k) c += (i0 + k < n && z_valid(z[k], z_min, z_max)) ? 1 : 0;
     c = __reduce_add_sync(0xffffffffu, c);
     __shared__ int sm[8];
     if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = c;
@@ -67,47 +79,46 @@ valid_count_kernel(const float* __restrict__ depth, int n, float z_min, float z_
 
 __global__ void __launch_bounds__(256)
 valid_write_kernel(const float* __restrict__ depth, int n, float z_min, float z_max, const int* __restrict__ seg_counts,
-                   int2* __restrict__ vlist, FrameState* st) {
+                   int2* __restrict__ vlist, int* __restrict__ n_valid_out) {
     __shared__ int s_base;
     __shared__ int s_warp[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i0 = blockIdx.x * kSegPixels + threadIdx.x * 8;
+    float z[8];
+    load8(depth, i0, n, z);
     if (warp == 0) {  // exclusive prefix of the segment counts before this block
         int s = 0;
         for (int b = lane; b < (int)blockIdx.x; b += 32) s += seg_counts[b];
         s = __reduce_add_sync(0xffffffffu, s);
         if (lane == 0) s_base = s;
     }
+    unsigned int flags = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) flags |= (i0 + k < n && z_valid(z[k], z_min, z_max)) ? (1u << k) : 0u;
+    const int c = __popc(flags);
+    int incl = c;  // warp inclusive scan
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    int run = s_base;
-    const int base = blockIdx.x * kSegPixels;
-    float z[8];
+    int off = s_base + incl - c, tot = 0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const int i = base + k * 256 + threadIdx.x;
-        z[k] = i < n ? depth[i] : 0.f;
-    }
+    for (int w = 0; w < 8; ++w) { const int cw = s_warp[w]; off += w < warp ? cw : 0; tot += cw; }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const int i = base + k * 256 + threadIdx.x;
-        const bool v = i < n && z_valid(z[k], z_min, z_max);
-        const unsigned int mask = __ballot_sync(0xffffffffu, v);
-        if (lane == 0) s_warp[warp] = __popc(mask);
-        __syncthreads();
-        int off = run, tot = 0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) { const int c = s_warp[w]; off += w < warp ? c : 0; tot += c; }
-        if (v) vlist[off + __popc(mask & ((1u << lane) - 1))] = make_int2(i, __float_as_int(z[k]));
-        run += tot;
-        __syncthreads();
-    }
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) st->n_valid = run;
+    for (int k = 0; k < 8; ++k)
+        if (flags & (1u << k)) vlist[off++] = make_int2(i0 + k, __float_as_int(z[k]));
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) *n_valid_out = s_base + tot;
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // Per-pixel tracker term: residual, Jacobian, 29 accumulations (RigidPointOptimizerOmp.cpp:72-90).
 template <int VARIANT>
 __device__ __forceinline__ void track_pixel(const MapView& m, const FrameGeom& g, const TrackIntr& ti, const float* R,
-                                            const float* t, int idx, float z, float* acc) {
+                                            const float* t, int idx, float z, float* acc, unsigned long long& ck,
+                                            int& cs) {
     const int y = idx / g.w, x = idx - y * g.w;
     const float x0 = ((float)x - ti.cx) * ti.fx_inv, y0 = ((float)y - ti.cy) * ti.fy_inv;
     const float cx_ = x0 * z, cy_ = y0 * z;
@@ -115,7 +126,7 @@ __device__ __forceinline__ void track_pixel(const MapView& m, const FrameGeom& g
     const float py = dot3_rn(R[3], R[4], R[5], cx_, cy_, z) + t[1];
     const float pz = dot3_rn(R[6], R[7], R[8], cx_, cy_, z) + t[2];
     float phi, g0, g1, g2;
-    const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2);
+    const float w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2, ck, cs);
     if (w0 > 0.f) {
         float J[6];
         J[0] = g0; J[1] = g1; J[2] = g2;
@@ -143,19 +154,34 @@ struct TrackParams {
     float damping;
 };
 
-// block-level stage of the tree: acc[29] per thread -> 29 sums per block in dst[0..28]
+// Warp stage of the tree as a reduce-scatter butterfly: instead of 29 independent 5-step shuffle reductions
+// (145 SHFL per warp) the 32 (29 + 3 zero) values are halved at every step — lanes whose `off` bit is clear keep
+// the lower half and receive the partner's lower half, the others the upper half — so 16+8+4+2+1 = 31 SHFL suffice
+// and lane L ends up holding the warp total of term L.  Fixed pairing => bit-reproducible.
+__device__ __forceinline__ float warp_reduce_scatter_32(float* v /* [32], destroyed */) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const bool up = (lane & half) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            const float lo = v[i], hi = v[i + half];
+            const float send = up ? lo : hi, keep = up ? hi : lo;
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+        }
+    }
+    return v[0];
+}
+
+// block-level stage: acc[29] per thread -> 29 sums per block in dst[0..28] (dst may be global or shared)
 template <int NWARPS>
-__device__ __forceinline__ void block_reduce_29(float* acc, float (*sm)[kAccStride], float* dst) {
+__device__ __forceinline__ void block_reduce_29(const float* acc, float (*sm)[kAccStride], float* dst) {
+    float v[32];
 #pragma unroll
-    for (int i = 0; i < kAccTerms; ++i) {
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], off);
-    }
+    for (int i = 0; i < 32; ++i) v[i] = i < kAccTerms ? acc[i] : 0.f;
+    const float mine = warp_reduce_scatter_32(v);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane == 0) {
-#pragma unroll
-        for (int i = 0; i < kAccTerms; ++i) sm[warp][i] = acc[i];
-    }
+    sm[warp][lane] = mine;
     __syncthreads();
     if (threadIdx.x < kAccTerms) {
         float s = 0.f;
@@ -165,24 +191,39 @@ __device__ __forceinline__ void block_reduce_29(float* acc, float (*sm)[kAccStri
     }
 }
 
-// grid-level stage, executed identically by whoever calls it: tot[term] = sum over blocks in block order
+// grid-level stage, executed identically by whoever calls it: tot[term] = sum over blocks, fixed grouping.
+// Thread (grp, t) sums blocks grp, grp+NWARPS, ... of term t with all its loads in flight at once (coalesced
+// 128 B rows), then the NWARPS group sums are added in order.
 template <int NWARPS>
-__device__ __forceinline__ void grid_reduce_29(const float* partials, int nblocks, float* tot) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int term = warp; term < kAccTerms; term += NWARPS) {
-        float s = 0.f;
-#pragma unroll 4
-        for (int b = lane; b < nblocks; b += 32) s += __ldcg(partials + (size_t)b * kAccStride + term);
+__device__ __forceinline__ void grid_reduce_29(const float* partials, int nblocks, float (*sm)[kAccStride], float* tot) {
+    const int t = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    constexpr int kMaxJ = 12;  // up to 12 * NWARPS blocks with every load issued up front
+    float s = 0.f;
+    for (int b0 = grp; b0 < nblocks; b0 += NWARPS * kMaxJ) {
+        float v[kMaxJ];
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
-        if (lane == 0) tot[term] = s;
+        for (int j = 0; j < kMaxJ; ++j) {
+            const int b = b0 + j * NWARPS;
+            v[j] = (b < nblocks) ? __ldcg(partials + (size_t)b * kAccStride + t) : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < kMaxJ; ++j) s += v[j];
+    }
+    __syncthreads();  // sm may still be read by the block stage of slower warps
+    sm[grp][t] = s;
+    __syncthreads();
+    if (threadIdx.x < kAccTerms) {
+        float r = 0.f;
+#pragma unroll
+        for (int wq = 0; wq < NWARPS; ++wq) r += sm[wq][threadIdx.x];
+        tot[threadIdx.x] = r;
     }
 }
 
 template <int VARIANT>
 __global__ void __launch_bounds__(kTrackThreads, 1)
-track_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist, FrameState* st,
-             float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp) {
+track_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist, const int* __restrict__ n_valid_ptr,
+             FrameState* st, float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp) {
     cg::grid_group grid = cg::this_grid();
     __shared__ float s_pose7[8];
     __shared__ Pose s_pose;
@@ -196,22 +237,24 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlis
         s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
     }
     __syncthreads();
-    const int n_valid = st->n_valid;
+    const int n_valid = *n_valid_ptr;
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
     int converged = 0, k = 0;
     float valid_sum = 0.f;
+    unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
+    int cs = -1;
     for (k = 0; k < tp.max_iters; ++k) {
         float acc[kAccTerms];
 #pragma unroll
         for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
         for (int j = gtid; j < n_valid; j += nthreads) {
             const int2 e = __ldg(vlist + j);
-            track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc);
+            track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
         }
         float* mine = partials + ((size_t)(k & 1) * gridDim.x + blockIdx.x) * kAccStride;
         block_reduce_29<kTrackWarps>(acc, s_warp, mine);
         grid.sync();
-        grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_tot);
+        grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
         __syncthreads();
         if (threadIdx.x == 0) {
             valid_sum += s_tot[28];
@@ -226,6 +269,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlis
         if (threadIdx.x < 7) st->pose7[threadIdx.x] = s_pose7[threadIdx.x];
         if (threadIdx.x < kAccTerms) st->sums[threadIdx.x] = s_tot[threadIdx.x];
         if (threadIdx.x == 0) {
+            st->n_valid = n_valid;
             st->converged = converged;
             st->iters = converged ? k : tp.max_iters;
             st->track_iters += (unsigned long long)(converged ? k + 1 : tp.max_iters);
@@ -238,8 +282,9 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlis
 // all-reduces out29 across ranks and then runs solve_kernel.  Exits at once when the loop is already done.
 template <int VARIANT>
 __global__ void __launch_bounds__(kAccThreads)
-accumulate_list_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist, const FrameState* st,
-                       float* __restrict__ partials, Counters* ctr, float* __restrict__ out29) {
+accumulate_list_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist,
+                       const int* __restrict__ n_valid_ptr, const FrameState* st, float* __restrict__ partials,
+                       Counters* ctr, float* __restrict__ out29) {
     if (st->done) return;
     __shared__ Pose s_pose;
     __shared__ float sm[kAccThreads / 32][kAccStride];
@@ -252,10 +297,12 @@ accumulate_list_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restr
     float acc[kAccTerms];
 #pragma unroll
     for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
-    const int n_valid = st->n_valid;
+    const int n_valid = *n_valid_ptr;
+    unsigned long long ck = kEmptyKey;
+    int cs = -1;
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += gridDim.x * blockDim.x) {
         const int2 e = __ldg(vlist + j);
-        track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc);
+        track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
     }
     block_reduce_29<kAccThreads / 32>(acc, sm, partials + (size_t)blockIdx.x * kAccStride);
     __shared__ bool is_last;
@@ -265,7 +312,7 @@ accumulate_list_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restr
     __syncthreads();
     if (!is_last) return;
     __threadfence();
-    grid_reduce_29<kAccThreads / 32>(partials, gridDim.x, out29);
+    grid_reduce_29<kAccThreads / 32>(partials, gridDim.x, sm, out29);
 }
 
 __global__ void solve_kernel(FrameState* st, const float* __restrict__ sums29, TrackParams tp) {
@@ -291,7 +338,7 @@ __global__ void track_begin_kernel(FrameState* st) {
 template <int VARIANT>
 __global__ void __launch_bounds__(256)
 fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2* __restrict__ vlist,
-                 const FrameState* __restrict__ st, const float* __restrict__ nx, const float* __restrict__ ny,
+                 const int* __restrict__ n_valid_ptr, FrameState* st, const float* __restrict__ nx, const float* __restrict__ ny,
                  const float* __restrict__ nz, const float* __restrict__ x0, const float* __restrict__ y0,
                  const float* __restrict__ hom_inv, Counters* ctr) {
     if (pose_src == 2 && !st->converged) return;
@@ -306,7 +353,8 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
     }
     __syncthreads();
     const float* R = pose.R;
-    const int n_valid = st->n_valid;
+    const int n_valid = *n_valid_ptr;
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->n_valid = n_valid;  // reported with the frame result
     unsigned int n_upd = 0, n_pts = 0;
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += gridDim.x * blockDim.x) {
         const int2 e = __ldg(vlist + j);

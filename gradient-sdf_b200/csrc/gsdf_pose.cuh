@@ -24,6 +24,7 @@ GSDF_HD void matvec3p(const float* R, const float* v, float* o) {
 }
 GSDF_HD void quat_normalize(float* q) {  // Eigen sums the 4-float packet as (x^2 + z^2) + (y^2 + w^2)
     const float len = sqrtf((q[0] * q[0] + q[2] * q[2]) + (q[1] * q[1] + q[3] * q[3]));
+#pragma unroll
     for (int i = 0; i < 4; ++i) q[i] /= len;
 }
 GSDF_HD void quat_to_R(const float* q, float* R) {
@@ -41,8 +42,10 @@ GSDF_HD void cross3p(const float* a, const float* b, float* o) {
 GSDF_HD void quat_rotate(const float* q, const float* p, float* o) {
     float uv[3], c2[3];
     cross3p(q, p, uv);
+#pragma unroll
     for (int i = 0; i < 3; ++i) uv[i] += uv[i];
     cross3p(q, uv, c2);
+#pragma unroll
     for (int i = 0; i < 3; ++i) o[i] = (p[i] + q[3] * uv[i]) + c2[i];
 }
 GSDF_HD void quat_mul(const float* a, const float* b, float* o) {  // product, then SO3(quaternion) normalises
@@ -72,16 +75,17 @@ GSDF_HD void se3_exp(const float* a, float* q, float* tr) {
     q[0] = imag * om[0]; q[1] = imag * om[1]; q[2] = imag * om[2]; q[3] = real;
     const float O[9] = {0.f, -om[2], om[1], om[2], 0.f, -om[0], -om[1], om[0], 0.f};  // hat(omega)
     float O2[9], V[9];
+#pragma unroll
     for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) {
-            const float col[3] = {O[j], O[3 + j], O[6 + j]};
-            O2[3 * i + j] = dot3p(O + 3 * i, col);
-        }
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            O2[3 * i + j] = O[3 * i] * O[j] + (O[3 * i + 1] * O[3 + j] + O[3 * i + 2] * O[6 + j]);
     if (theta < eps) {
         quat_to_R(q, V);
     } else {
         const float tsq = theta * theta;
         const float c1 = (1.f - cosf(theta)) / tsq, c2 = (theta - sinf(theta)) / (tsq * theta);
+#pragma unroll
         for (int i = 0; i < 9; ++i) V[i] = ((i % 4 == 0 ? 1.f : 0.f) + c1 * O[i]) + c2 * O2[i];
     }
     matvec3p(V, a, tr);
@@ -90,41 +94,68 @@ GSDF_HD void se3_exp(const float* a, float* q, float* tr) {
 GSDF_HD void pose_apply_increment(const float* pose7_in, const float* xi6, float* pose7_out) {
     float a[6], qa[4], ta[3], qo[4], rt[3];
     const float qb[4] = {pose7_in[3], pose7_in[4], pose7_in[5], pose7_in[6]};
+#pragma unroll
     for (int i = 0; i < 6; ++i) a[i] = -xi6[i];
     se3_exp(a, qa, ta);
     quat_mul(qa, qb, qo);
     quat_rotate(qa, pose7_in, rt);
+#pragma unroll
     for (int i = 0; i < 3; ++i) pose7_out[i] = ta[i] + rt[i];
+#pragma unroll
     for (int i = 0; i < 4; ++i) pose7_out[3 + i] = qo[i];
 }
 // xi = LLT(H)^-1 g: unblocked lower Cholesky in place, stopping at the first non-positive pivot as Eigen's LLT
 // does (the rest of the matrix is then left as is and the substitution yields inf/NaN for H = 0), then
 // forward/back substitution.  H row-major 6x6.
 GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
-    float A[36], y[6];
+    // every loop has constant bounds and is fully unrolled, so that on the device the matrix lives in registers
+    // (the solve runs on one thread per CTA between two barriers of the persistent tracker: it is on the
+    // critical path of every Gauss-Newton pass)
+    // (loops run over the full fixed range with a predicate instead of triangular bounds: nvcc keeps A in
+    // registers only then)
+    float A[36], y[6], x6[6];
+#pragma unroll
     for (int i = 0; i < 36; ++i) A[i] = H36[i];
+    bool ok = true;  // false once a pivot was non-positive: Eigen stops there and leaves the remaining columns as is
+#pragma unroll
     for (int k = 0; k < 6; ++k) {
         float x = A[6 * k + k];
-        for (int j = 0; j < k; ++j) x -= A[6 * k + j] * A[6 * k + j];
-        if (x <= 0.f) break;
-        x = sqrtf(x);
-        A[6 * k + k] = x;
-        for (int i = k + 1; i < 6; ++i) {
-            float s = A[6 * i + k];
-            for (int j = 0; j < k; ++j) s -= A[6 * i + j] * A[6 * k + j];
-            A[6 * i + k] = s / x;
-        }
+#pragma unroll
+        for (int j = 0; j < 6; ++j)
+            if (j < k) x -= A[6 * k + j] * A[6 * k + j];
+        const bool good = ok && !(x <= 0.f);
+        const float r = sqrtf(x);
+        A[6 * k + k] = good ? r : A[6 * k + k];
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            if (i > k) {
+                float s = A[6 * i + k];
+#pragma unroll
+                for (int j = 0; j < 6; ++j)
+                    if (j < k) s -= A[6 * i + j] * A[6 * k + j];
+                A[6 * i + k] = good ? s / r : A[6 * i + k];
+            }
+        ok = good;
     }
+#pragma unroll
     for (int i = 0; i < 6; ++i) {
         float s = g6[i];
-        for (int j = 0; j < i; ++j) s -= A[6 * i + j] * y[j];
+#pragma unroll
+        for (int j = 0; j < 6; ++j)
+            if (j < i) s -= A[6 * i + j] * y[j];
         y[i] = s / A[6 * i + i];
     }
-    for (int i = 5; i >= 0; --i) {
+#pragma unroll
+    for (int ii = 0; ii < 6; ++ii) {
+        const int i = 5 - ii;
         float s = y[i];
-        for (int j = i + 1; j < 6; ++j) s -= A[6 * j + i] * xi6[j];
-        xi6[i] = s / A[6 * i + i];
+#pragma unroll
+        for (int j = 0; j < 6; ++j)
+            if (j > i) s -= A[6 * j + i] * x6[j];
+        x6[i] = s / A[6 * i + i];
     }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) xi6[i] = x6[i];
 }
 
 // One Gauss-Newton step of RigidPointOptimizer::optimize_sampled (RigidPointOptimizerOmp.cpp:93-102) from the
@@ -133,11 +164,14 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
 GSDF_HD int gauss_newton_step(const float* sums29, float damping, float thr_sq, float* pose7) {
     float H[36], xi[6];
     int o = 6;
+#pragma unroll
     for (int a = 0; a < 6; ++a)
+#pragma unroll
         for (int b = a; b < 6; ++b) { H[6 * a + b] = sums29[o]; H[6 * b + a] = sums29[o]; ++o; }
     llt_solve6(H, sums29, xi);
     bool has_nan = false;
     float nrm = 0.f;
+#pragma unroll
     for (int i = 0; i < 6; ++i) { xi[i] = damping * xi[i]; has_nan = has_nan || (xi[i] != xi[i]); nrm += xi[i] * xi[i]; }
     if (nrm < thr_sq) return 1;
     if (!has_nan) {

@@ -75,7 +75,8 @@ gsdf_status gsdf_compute_normals(gsdf_handle h, float* nx, float* ny, float* nz)
 /* -- the depth frame (cv::Mat depth, CV_32FC1 metres, 0 = invalid, img_loader/ImageLoader.h:159-175) ------- */
 /* Host buffer -> device (async on the handle's stream, complete before the next call that uses it). */
 gsdf_status gsdf_upload_frame(gsdf_handle h, const float* depth_host);
-/* Frame already resident in HBM (device pointer, width*height floats, must stay valid while it is current). */
+/* Frame already resident in HBM (device pointer, 16-byte aligned, width*height floats, must stay valid while it
+ * is current). */
 gsdf_status gsdf_set_frame_device(gsdf_handle h, const float* depth_dev);
 
 /* -- Sdf::update / Sdf::setup (sdf_tracker/Sdf.h:117-121; MapGradPixelSdfOmp.cpp:44-130,
@@ -175,7 +176,8 @@ gsdf_status gsdf_track_stats(gsdf_handle h, int64_t* iterations, int64_t* valid_
 /* Per-kernel device timing (the reference's only metrics are Timer tic/toc prints, Timer.h:59-78): when
  * enabled, a CUDA-event pair brackets every launch of that kind on the handle's stream; gsdf_profile_read
  * synchronises and returns the launches and their summed duration since gsdf_profile_enable(h, 1). */
-enum { GSDF_PROF_NORMALS = 0, GSDF_PROF_FUSE = 1, GSDF_PROF_ACCUMULATE = 2, GSDF_PROF_KINDS = 3 };
+enum { GSDF_PROF_NORMALS = 0, GSDF_PROF_FUSE = 1, GSDF_PROF_ACCUMULATE = 2 /* tracker */, GSDF_PROF_PREPARE = 3,
+       GSDF_PROF_KINDS = 4 };
 gsdf_status gsdf_profile_enable(gsdf_handle h, int32_t on);
 gsdf_status gsdf_profile_read(gsdf_handle h, int32_t kind, int64_t* launches, double* total_ms);
 /* Multi-GPU: rank 0 calls gsdf_comm_unique_id, the 128 bytes are distributed by the caller (any transport),

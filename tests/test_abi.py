@@ -11,7 +11,7 @@ ROOT = Path(__file__).resolve().parents[1]
 
 def test_exports_match_header(pkg):
     header = (ROOT / "include" / "gsdf_b200.h").read_text()
-    declared = set(re.findall(r"^(?:gsdf_status|const char\*|void\*?|int64_t)\s+(gsdf_[a-z0-9_]+)\s*\(", header, re.M))
+    declared = set(re.findall(r"^(?:gsdf_status|const char\*|void\*?|int64_t|int32_t)\s+(gsdf_[a-z0-9_]+)\s*\(", header, re.M))
     L = pkg.lib()
     for sym in sorted(declared):
         assert hasattr(L, sym), f"{sym} declared in include/gsdf_b200.h but not exported"

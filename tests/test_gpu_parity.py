@@ -252,7 +252,9 @@ def test_scan_pipeline_matches_synchronous_calls(pkg, po, synth, variant):
     import torch
 
     W, H = 320, 240
-    frames, poses, K, _ = synth.make_sequence(300, W, H)
+    # grad-sdf: noise-free frames and small motion, where its tracker converges with margin (on noisy data its
+    # 1e-3 stopping rule is borderline and two runs of the REFERENCE disagree with each other)
+    frames, poses, K, _ = synth.make_sequence(300, W, H) if variant == 1 else synth.make_sequence(800, W, H, noise=False)
     frames = frames[:10]
     ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
     a, _ = make_pair(pkg, po, variant, 0.01, 5, W, H, K, log2cap=16)
@@ -287,19 +289,20 @@ def test_scan_pipeline_matches_synchronous_calls(pkg, po, synth, variant):
     first, got = got[0], got[1:]
     assert first.converged == 1 and first.fused == 1 and first.updates > 0 and first.iters == 0
     assert len(got) == len(ref)
-    # Fusion is an atomic reduction, so two runs differ in the last bits of the map; the base-sdf tracker is
-    # insensitive to that, the grad-sdf tracker (nearest-voxel Taylor model, borderline 1e-3 stopping rule) is not:
-    # same flags and iteration counts are required for base-sdf, poses within 1 mm for both.
+    # Fusion is an atomic reduction, so two runs differ in the last bits of the map: same flags and iteration
+    # counts, poses within a fraction of the stopping threshold.
     mismatches = 0
     for r, (conv, iters, pose, st) in zip(got, ref):
         assert bool(r.fused) == bool(r.converged)
         assert r.track_iterations == (r.iters + 1 if r.converged else 25)
-        assert np.abs(np.array(r.pose7[:]) - pose).max() < (2e-5 if variant == 1 else 1e-3)
+        # the grad-sdf tracker stops at |xi| < 1e-3: two runs over maps that differ in the last bits agree to a
+        # fraction of that threshold, not better
+        assert np.abs(np.array(r.pose7[:]) - pose).max() < (5e-4 if variant == 0 else 5e-5)
         if bool(r.converged) != conv or r.iters != iters:
             mismatches += 1
         elif conv:
             assert abs(r.updates - st[1]) <= 1e-3 * st[1] and abs(r.points - st[0]) <= 1e-3 * st[0]
-    assert mismatches == 0 if variant == 1 else mismatches <= 2
+    assert mismatches == 0
     ka, kb = a.download()[0], b.download()[0]
     sa, sb = {tuple(x) for x in ka}, {tuple(x) for x in kb}
     assert len(sa & sb) / len(sa | sb) > 0.999
