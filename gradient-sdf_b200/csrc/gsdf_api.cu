@@ -78,8 +78,9 @@ struct gsdf_map {
     bool normals_valid = false, prepared = false;
     int2* d_vlist[2] = {nullptr, nullptr};  // compacted valid pixels, double-buffered like the normals
     int* d_nvalid = nullptr;                // [2] counts of the two lists
-    int* d_seg_counts = nullptr;            // [2][nseg]
-    int nseg = 0;
+    unsigned int* d_compact_flags = nullptr;  // [nseg] look-back flags {epoch, count} of compact_tiles_kernel
+    unsigned int compact_epoch = 0;
+    int nseg = 0;                           // CTAs of the compaction (64 tiles of 8x4 pixels each)
     FrameState* d_state = nullptr;
     Counters* d_ctr = nullptr;
     float* d_partials = nullptr;      // v1 accumulate / accumulate_list: [acc_blocks][32]
@@ -239,17 +240,14 @@ gsdf_status launch_normals(gsdf_map* h, const float* depth, int buf, cudaStream_
     return check_launch(h, "normals_tile_kernel");
 }
 
-// compaction of a frame's z-valid pixels (deterministic, ascending order) into d_vlist[buf], count into d_nvalid[buf]
+// compaction of a frame's z-valid pixels (deterministic, tile order) into d_vlist[buf], count into d_nvalid[buf]
 gsdf_status launch_prepare(gsdf_map* h, const float* depth, int buf, cudaStream_t stream) {
-    const int n = h->cfg.width * h->cfg.height;
-    int* counts = h->d_seg_counts + (size_t)buf * h->nseg;
     ProfScope prof(h, GSDF_PROF_PREPARE, stream);
-    valid_count_kernel<<<h->nseg, 256, 0, stream>>>(depth, n, h->geom.z_min, h->geom.z_max, counts);
-    gsdf_status s = check_launch(h, "valid_count_kernel");
-    if (s != GSDF_OK) return s;
-    valid_write_kernel<<<h->nseg, 256, 0, stream>>>(depth, n, h->geom.z_min, h->geom.z_max, counts, h->d_vlist[buf],
-                                                    h->d_nvalid + buf);
-    return check_launch(h, "valid_write_kernel");
+    h->compact_epoch = (h->compact_epoch + 1) & 0xFFFFFu;
+    compact_tiles_kernel<<<h->nseg, kCompactThreads, 0, stream>>>(depth, h->cfg.width, h->cfg.height, h->geom.z_min,
+                                                                  h->geom.z_max, h->d_compact_flags, h->compact_epoch,
+                                                                  h->d_vlist[buf], h->d_nvalid + buf);
+    return check_launch(h, "compact_tiles_kernel");
 }
 
 gsdf_status ensure_frame(gsdf_map* h) {
@@ -275,8 +273,7 @@ gsdf_status ensure_normals(gsdf_map* h) {
 
 gsdf_status launch_fuse(gsdf_map* h, const Pose& pose, int pose_src, int nbuf, cudaStream_t stream) {
     const size_t np = (size_t)h->cfg.width * h->cfg.height;
-    int blocks = (int)((np + 255) / 256);
-    if (blocks > h->sm_count * 8) blocks = h->sm_count * 8;
+    const int blocks = h->sm_count * 8;  // warps stride over (32-pixel chunk, sample group) work items
     const float* nrm = h->d_normals[nbuf];
     return by_variant(h, [&](auto V) {
         ProfScope prof(h, GSDF_PROF_FUSE, stream);
@@ -339,6 +336,11 @@ gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream
     return GSDF_OK;
 }
 
+void sum_counters(const Counters& c, unsigned long long& points, unsigned long long& updates) {
+    points = updates = 0;
+    for (int i = 0; i < kCounterSlots; ++i) { points += c.slot[i].points; updates += c.slot[i].updates; }
+}
+
 gsdf_status clear_map(gsdf_map* h) {
     CUDA_TRY(h, cudaMemsetAsync(h->view.keys, 0xFF, sizeof(unsigned long long) * h->cap, h->stream));
     if (h->cfg.variant == GSDF_GRAD_SDF) {
@@ -366,7 +368,7 @@ void free_all(gsdf_map* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
     cudaFree(h->d_planes); cudaFree(h->d_normals[0]); cudaFree(h->d_normals[1]); cudaFree(h->d_ctr);
-    cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_seg_counts); cudaFree(h->d_state); cudaFree(h->d_track_partials);
+    cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_state); cudaFree(h->d_track_partials);
     cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
     cudaFreeHost(h->h_state);
@@ -413,8 +415,10 @@ gsdf_status create_impl(gsdf_map* h) {
     CUDA_TRY(h, cudaMalloc(&h->d_vlist[1], sizeof(int2) * n));
     CUDA_TRY(h, cudaMalloc(&h->d_nvalid, sizeof(int) * 2));
     CUDA_TRY(h, cudaMemset(h->d_nvalid, 0, sizeof(int) * 2));
-    h->nseg = (int)((n + kSegPixels - 1) / kSegPixels);
-    CUDA_TRY(h, cudaMalloc(&h->d_seg_counts, sizeof(int) * 2 * h->nseg));
+    const int ntiles = ((c.width + kTileW - 1) / kTileW) * ((c.height + kTileH - 1) / kTileH);
+    h->nseg = (ntiles + kTilesPerBlock - 1) / kTilesPerBlock;
+    CUDA_TRY(h, cudaMalloc(&h->d_compact_flags, sizeof(unsigned int) * h->nseg));
+    CUDA_TRY(h, cudaMemset(h->d_compact_flags, 0, sizeof(unsigned int) * h->nseg));
     CUDA_TRY(h, cudaMalloc(&h->d_state, sizeof(FrameState)));
     CUDA_TRY(h, cudaMalloc(&h->d_ctr, sizeof(Counters)));
     h->acc_blocks = h->sm_count * 2;
@@ -524,8 +528,13 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     if ((c.variant != GSDF_GRAD_SDF && c.variant != GSDF_BASE_SDF) || !(c.voxel_size > 0.f) || !(c.truncation > 0.f) ||
         c.width <= 0 || c.height <= 0 || c.normal_window < 1 || !(c.normal_window & 1) || c.normal_window / 2 > N_MAXR ||
         c.normal_window / 2 >= c.width || c.normal_window / 2 >= c.height || c.log2_capacity < 4 || c.log2_capacity > 26 ||
-        c.rank < 0 || c.rank >= c.world_size || !(c.K[0] != 0.f) || !(c.K[4] != 0.f)) {
+        c.rank < 0 || c.rank >= c.world_size || !(c.K[0] != 0.f) || !(c.K[4] != 0.f) || c.width > 65535 ||
+        c.height > 32767) {
         g_create_error = "invalid gsdf_config";
+        return GSDF_ERR_INVALID;
+    }
+    if (c.world_size > 1 && c.variant == GSDF_BASE_SDF) {
+        g_create_error = "base-sdf maps cannot be sharded yet (trilinear corners straddle shard boundaries)";
         return GSDF_ERR_INVALID;
     }
     int ndev = 0;
@@ -634,11 +643,13 @@ gsdf_status gsdf_integrate(gsdf_handle h, const float* R9, const float* t3, gsdf
     if (stats) {
         CUDA_TRY(h, cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(h, cudaStreamSynchronize(h->stream));
-        stats->points = (int64_t)(h->h_ctr->points - h->last_points);
-        stats->updates = (int64_t)(h->h_ctr->updates - h->last_updates);
+        unsigned long long pts, upd;
+        sum_counters(*h->h_ctr, pts, upd);
+        stats->points = (int64_t)(pts - h->last_points);
+        stats->updates = (int64_t)(upd - h->last_updates);
         stats->blocks = (int64_t)h->h_ctr->blocks;
-        h->last_points = h->h_ctr->points;
-        h->last_updates = h->h_ctr->updates;
+        h->last_points = pts;
+        h->last_updates = upd;
         if (h->h_ctr->overflow) {
             h->err = "voxel-block hash full: samples dropped; raise gsdf_config.log2_capacity";
             return GSDF_ERR_CAPACITY;
@@ -872,13 +883,15 @@ gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
     out->iters = tracked ? st.iters : 0;
     out->fused = out->converged;
     out->n_valid = st.n_valid;
-    out->points = (int64_t)(c.points - h->last_points);
-    out->updates = (int64_t)(c.updates - h->last_updates);
+    unsigned long long pts, upd;
+    sum_counters(c, pts, upd);
+    out->points = (int64_t)(pts - h->last_points);
+    out->updates = (int64_t)(upd - h->last_updates);
     out->blocks = (int64_t)c.blocks;
     out->track_iterations = (int64_t)st.track_iters - h->track_iterations;
     out->track_valid = (int64_t)st.track_valid - h->track_valid;
-    h->last_points = c.points;
-    h->last_updates = c.updates;
+    h->last_points = pts;
+    h->last_updates = upd;
     h->track_iterations = (int64_t)st.track_iters;
     h->track_valid = (int64_t)st.track_valid;
     if (c.overflow) {

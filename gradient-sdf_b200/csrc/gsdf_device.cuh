@@ -36,13 +36,19 @@ struct MapView {
     int32_t world, rank;
 };
 
+// Statistics and tickets.  The per-frame counters are spread over kCounterSlots slots (one per CTA modulo the
+// slot count, after a CTA-level sum): measured on B200 (profiles/micro/red_single.cu), ~10 k warps each adding to
+// the SAME two words cost 11 us of serialised L2 atomics — as much as the whole fusion kernel should take.
+constexpr int kCounterSlots = 64;
 struct Counters {
-    unsigned long long points;    // pixels that passed every validity test
-    unsigned long long updates;   // committed (pixel,k) samples
     unsigned int blocks;          // allocated blocks
     unsigned int overflow;        // find-or-insert gave up: GSDF_ERR_CAPACITY
     unsigned int ticket;          // last-block-done ticket of the reduction
     unsigned int pad;
+    struct Slot {
+        unsigned long long points;   // pixels that passed every validity test
+        unsigned long long updates;  // committed (pixel,k) samples
+    } slot[kCounterSlots];
 };
 
 __device__ __forceinline__ unsigned long long mix64(unsigned long long x) {

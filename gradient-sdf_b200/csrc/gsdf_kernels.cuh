@@ -168,8 +168,9 @@ fuse_kernel(MapView m, FrameGeom g, Pose pose, const float* __restrict__ depth, 
     const unsigned int pts = __popc(__ballot_sync(0xffffffffu, valid));
     n_upd = __reduce_add_sync(0xffffffffu, n_upd);
     if ((threadIdx.x & 31) == 0 && (pts | n_upd)) {
-        atomicAdd(&ctr->points, (unsigned long long)pts);
-        atomicAdd(&ctr->updates, (unsigned long long)n_upd);
+        Counters::Slot* sl = ctr->slot + (blockIdx.x & (kCounterSlots - 1));
+        atomicAdd(&sl->points, (unsigned long long)pts);
+        atomicAdd(&sl->updates, (unsigned long long)n_upd);
     }
 }
 
@@ -197,10 +198,12 @@ struct Lookup<0> {  // MapGradPixelSdf.h:109-125
         const float W = m.accW[addr];
         if (!(W > 0.f)) return 0.f;
         const float4 a = m.acc4[addr];
-        const float dist = a.x / W;
+        // phi and grad are tolerance-level quantities (sums of them are compared at 1e-4), not key-determining:
+        // approximate reciprocal / rsqrt (<= 2 ulp) instead of IEEE division on the tracker's critical path
+        const float dist = __fdividef(a.x, W);
         const float sq = dot3_rn(a.y, a.z, a.w, a.y, a.z, a.w);
         float n0 = a.y, n1 = a.z, n2 = a.w;
-        if (sq > 0.f) { const float l = __fsqrt_rn(sq); n0 = __fdiv_rn(n0, l); n1 = __fdiv_rn(n1, l); n2 = __fdiv_rn(n2, l); }
+        if (sq > 0.f) { const float il = rsqrtf(sq); n0 *= il; n1 *= il; n2 *= il; }
         const float dx = __fsub_rn(__fmul_rn(g.vs, (float)vx), px);
         const float dy = __fsub_rn(__fmul_rn(g.vs, (float)vy), py);
         const float dz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pz);
@@ -223,27 +226,38 @@ struct Lookup<1> {  // MapPixelSdf.h:107-143 + interp3, MapPixelSdfOmp.cpp:44-11
         const int rx = (int)roundf(fx) - im, ry = (int)roundf(fy) - jm, rz = (int)roundf(fz) - km;  // nearest corner
         // resolve the (at most 8, usually 1) blocks first, then issue all 8 voxel loads before looking at any of
         // them: one memory round trip instead of eight dependent ones
-        size_t addr[8];
-        unsigned long long last_key = ck;
-        int slot = cs;
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            const int vx = im + (c & 1), vy = jm + ((c >> 1) & 1), vz = km + (c >> 2);
-            const unsigned long long key = block_key_of(vx, vy, vz);
-            if (key != last_key) { last_key = key; slot = map_find(m, key); }
-            if (c == 0) { ck = last_key; cs = slot; }
-            if (slot < 0) return 0.f;  // weights(): all 8 corners must exist (MapPixelSdf.h:127-136)
-            addr[c] = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
-        }
+        const int cn = rx | (ry << 1) | (rz << 2);
         float2 v[8];
+        const int lx = im & 7, ly = jm & 7, lz = km & 7;
+        if (lx < 7 && ly < 7 && lz < 7) {  // (7/8)^3 = 67 % of the cells lie inside one block: one probe, fixed offsets
+            const unsigned long long key = block_key_of(im, jm, km);
+            if (key != ck) { ck = key; cs = map_find(m, key); }
+            if (cs < 0) return 0.f;
+            const float2* base = m.acc2 + (size_t)cs * kBlockVoxels + (lx | (ly << 3) | (lz << 6));
 #pragma unroll
-        for (int c = 0; c < 8; ++c) v[c] = m.acc2[addr[c]];
+            for (int c = 0; c < 8; ++c) v[c] = base[(c & 1) + ((c >> 1) & 1) * 8 + (c >> 2) * 64];
+        } else {
+            size_t addr[8];
+            unsigned long long last_key = ck;
+            int slot = cs;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int vx = im + (c & 1), vy = jm + ((c >> 1) & 1), vz = km + (c >> 2);
+                const unsigned long long key = block_key_of(vx, vy, vz);
+                if (key != last_key) { last_key = key; slot = map_find(m, key); }
+                if (c == 0) { ck = last_key; cs = slot; }
+                if (slot < 0) return 0.f;  // weights(): all 8 corners must exist (MapPixelSdf.h:127-136)
+                addr[c] = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) v[c] = m.acc2[addr[c]];
+        }
         bool all = true;
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
             all = all && (v[c].x > 0.f);
-            d[c] = v[c].y / v[c].x;
-            if ((c & 1) == rx && ((c >> 1) & 1) == ry && (c >> 2) == rz) Wn = v[c].x;
+            d[c] = __fdividef(v[c].y, v[c].x);  // tolerance-level quantity, see Lookup<0>
+            Wn = (c == cn) ? v[c].x : Wn;
         }
         if (!all) return 0.f;
         const float dx = fx - (float)im, dy = fy - (float)jm, dz = fz - (float)km;

@@ -1,10 +1,10 @@
 // Frame pipeline kernels (v2): everything a frame needs runs on the stream without a host round trip.
 //
-//   valid_count_kernel / valid_write_kernel   deterministic compaction of the z-valid pixels of the frame into
-//                                             vlist = {pixel index, z} (ascending pixel order), so that every
-//                                             lane of every warp downstream has work (the sphere scenes have
-//                                             ~20 % valid pixels, spatially clustered: a per-pixel grid leaves
-//                                             most warps idle and a few with all the work);
+//   compact_tiles_kernel                      deterministic single-pass compaction of the z-valid pixels of the frame
+//                                             into vlist = {(y<<16)|x, z} in 8x4-tile order, so that every lane of
+//                                             every warp downstream has work (the sphere scenes have ~20 % valid
+//                                             pixels, spatially clustered: a per-pixel grid leaves most warps idle
+//                                             and a few with all the work) and a warp's pixels are neighbours;
 //   track_kernel<V>                           the WHOLE Gauss-Newton loop of RigidPointOptimizer::optimize_sampled
 //                                             (RigidPointOptimizerOmp.cpp:44-106) as one persistent cooperative
 //                                             kernel: per-pixel lookup + Jacobian, warp -> block -> grid tree
@@ -40,86 +40,80 @@ struct FrameState {
     float sums[32];             // last reduced sums
 };
 
-constexpr int kSegPixels = 2048;  // pixels per compaction segment (256 threads x 8)
+constexpr int kTileW = 8, kTileH = 4;           // one warp <-> one 8x4 pixel tile
+constexpr int kTilesPerWarp = 8;
+constexpr int kCompactThreads = 256;
+constexpr int kTilesPerBlock = (kCompactThreads / 32) * kTilesPerWarp;  // 64 tiles = 2048 pixels per CTA
 
 __device__ __forceinline__ bool z_valid(float z, float z_min, float z_max) { return !(z <= z_min || z >= z_max); }
 
-// Each thread owns 8 CONSECUTIVE pixels (two 16-byte loads), so ascending pixel order is thread order and one
-// block-wide exclusive scan of the per-thread counts places everything.
-__device__ __forceinline__ void load8(const float* __restrict__ depth, int i0, int n, float* z) {
-    if (i0 + 8 <= n) {
-        const float4 a = __ldg(reinterpret_cast<const float4*>(depth + i0));
-        const float4 b = __ldg(reinterpret_cast<const float4*>(depth + i0 + 4));
-        z[0] = a.x; z[1] = a.y; z[2] = a.z; z[3] = a.w; z[4] = b.x; z[5] = b.y; z[6] = b.z; z[7] = b.w;
-    } else {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) z[k] = (i0 + k < n) ? depth[i0 + k] : 0.f;
-    }
-}
-
-__global__ void __launch_bounds__(256)
-valid_count_kernel(const float* __restrict__ depth, int n, float z_min, float z_max, int* __restrict__ seg_counts) {
-    const int i0 = blockIdx.x * kSegPixels + threadIdx.x * 8;
-    float z[8];
-    load8(depth, i0, n, z);
-    int c = 0;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) c += (i0 + k < n && z_valid(z[k], z_min, z_max)) ? 1 : 0;
-    c = __reduce_add_sync(0xffffffffu, c);
-    __shared__ int sm[8];
-    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = c;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int s = 0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) s += sm[w];
-        seg_counts[blockIdx.x] = s;
-    }
-}
-
-__global__ void __launch_bounds__(256)
-valid_write_kernel(const float* __restrict__ depth, int n, float z_min, float z_max, const int* __restrict__ seg_counts,
-                   int2* __restrict__ vlist, int* __restrict__ n_valid_out) {
-    __shared__ int s_base;
-    __shared__ int s_warp[8];
+// Single-pass, deterministic compaction of the z-valid pixels into vlist = {(y << 16) | x, z}, in TILE order:
+// 32 consecutive entries come from (at most a few) 8x4 pixel tiles, so the lanes of a warp downstream look at a
+// compact 3-D neighbourhood — nearby voxels for the tracker's gathers, and many lanes hitting the SAME voxel in
+// fusion, which the warp then merges into one reduction.
+// The exclusive prefix over CTAs is a chained look-back: CTA b publishes {epoch, count} in flags[b] and sums the
+// flags of all CTAs < b, spinning until they carry this launch's epoch (lower-numbered CTAs are dispatched first and
+// wait only on even lower ones, so the chain always makes progress; flags need no clearing between launches).
+__global__ void __launch_bounds__(kCompactThreads)
+compact_tiles_kernel(const float* __restrict__ depth, int w, int h, float z_min, float z_max,
+                     unsigned int* __restrict__ flags, unsigned int epoch, int2* __restrict__ vlist,
+                     int* __restrict__ n_valid_out) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int i0 = blockIdx.x * kSegPixels + threadIdx.x * 8;
-    float z[8];
-    load8(depth, i0, n, z);
-    if (warp == 0) {  // exclusive prefix of the segment counts before this block
+    const int tiles_x = (w + kTileW - 1) / kTileW, tiles_y = (h + kTileH - 1) / kTileH, ntiles = tiles_x * tiles_y;
+    const int tx = lane & 7, ty = lane >> 3;
+    __shared__ int s_warp[kCompactThreads / 32];
+    __shared__ int s_base;
+    float z[kTilesPerWarp];
+    int yx[kTilesPerWarp];
+    unsigned int mask[kTilesPerWarp];
+    int wtot = 0;
+#pragma unroll
+    for (int i = 0; i < kTilesPerWarp; ++i) {
+        const int tile = blockIdx.x * kTilesPerBlock + warp * kTilesPerWarp + i;
+        const int tyi = tile / tiles_x, txi = tile - tyi * tiles_x;
+        const int x = txi * kTileW + tx, y = tyi * kTileH + ty;
+        const bool in = tile < ntiles && x < w && y < h;
+        z[i] = in ? __ldg(depth + (size_t)y * w + x) : 0.f;
+        yx[i] = (y << 16) | x;
+        mask[i] = __ballot_sync(0xffffffffu, in && z_valid(z[i], z_min, z_max));
+        wtot += __popc(mask[i]);
+    }
+    if (lane == 0) s_warp[warp] = wtot;
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int q = 0; q < kCompactThreads / 32; ++q) { const int c = s_warp[q]; before += q < warp ? c : 0; total += c; }
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicExch(flags + blockIdx.x, (epoch << 12) | (unsigned)total);  // total <= 2048 < 2^12
+    }
+    if (warp == 0) {
         int s = 0;
-        for (int b = lane; b < (int)blockIdx.x; b += 32) s += seg_counts[b];
+        for (int b = lane; b < (int)blockIdx.x; b += 32) {
+            unsigned int f;
+            do { f = *reinterpret_cast<volatile unsigned int*>(flags + b); } while ((f >> 12) != (epoch & 0xFFFFFu));
+            s += (int)(f & 0xFFFu);
+        }
         s = __reduce_add_sync(0xffffffffu, s);
         if (lane == 0) s_base = s;
     }
-    unsigned int flags = 0;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) flags |= (i0 + k < n && z_valid(z[k], z_min, z_max)) ? (1u << k) : 0u;
-    const int c = __popc(flags);
-    int incl = c;  // warp inclusive scan
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, off);
-        if (lane >= off) incl += v;
-    }
-    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    int off = s_base + incl - c, tot = 0;
+    int off = s_base + before;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) { const int cw = s_warp[w]; off += w < warp ? cw : 0; tot += cw; }
-#pragma unroll
-    for (int k = 0; k < 8; ++k)
-        if (flags & (1u << k)) vlist[off++] = make_int2(i0 + k, __float_as_int(z[k]));
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) *n_valid_out = s_base + tot;
+    for (int i = 0; i < kTilesPerWarp; ++i) {
+        if (mask[i] & (1u << lane)) vlist[off + __popc(mask[i] & ((1u << lane) - 1))] = make_int2(yx[i], __float_as_int(z[i]));
+        off += __popc(mask[i]);
+    }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) *n_valid_out = s_base + total;
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // Per-pixel tracker term: residual, Jacobian, 29 accumulations (RigidPointOptimizerOmp.cpp:72-90).
 template <int VARIANT>
 __device__ __forceinline__ void track_pixel(const MapView& m, const FrameGeom& g, const TrackIntr& ti, const float* R,
-                                            const float* t, int idx, float z, float* acc, unsigned long long& ck,
+                                            const float* t, int yx, float z, float* acc, unsigned long long& ck,
                                             int& cs) {
-    const int y = idx / g.w, x = idx - y * g.w;
+    const int y = yx >> 16, x = yx & 0xFFFF;
     const float x0 = ((float)x - ti.cx) * ti.fx_inv, y0 = ((float)y - ti.cy) * ti.fy_inv;
     const float cx_ = x0 * z, cy_ = y0 * z;
     const float px = dot3_rn(R[0], R[1], R[2], cx_, cy_, z) + t[0];
@@ -333,14 +327,45 @@ __global__ void track_begin_kernel(FrameState* st) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Fusion over the compacted list.  pose_src: 0 = pose by value, 1 = pose from the device state (any), 2 = pose from
-// the device state and only if the last optimize converged (main_scan_3d.cpp:261).
+// Fusion over the compacted list: one lane per pixel walks its 2*factor+1 ray samples (MapGradPixelSdfOmp.cpp:103);
+// at every sample the warp merges the lanes that hit the SAME voxel (list entries of a warp come from the same
+// 8x4-pixel tiles, and a 1 cm voxel spans 3-5 pixels) and only the group leader issues the vector reductions.
+// Measured on B200 (profiles/micro/red_bench.cu): global RED throughput is ~100 G ops/s regardless of how the
+// duplicates are spread, so the number of REDs — not the bytes — bounds this kernel; merging cuts them 3-6x.
+// pose_src: 0 = pose by value, 1 = pose from the device state, 2 = pose from the device state and only if the last
+// optimize converged (main_scan_3d.cpp:261).
+template <int NV>
+__device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool has, float* v, bool& leader) {
+    // lanes without a sample get a key no one else has
+    const int lane = threadIdx.x & 31;
+    const unsigned long long k = has ? key : (0xFFFFFFFF00000000ull | (unsigned)lane);
+    const unsigned int peers = __match_any_sync(0xffffffffu, k);
+    leader = has && ((int)__ffs(peers) - 1 == lane);
+    unsigned int rest = peers & (peers - 1);  // the group without its leader (identical on every member)
+    while (__any_sync(0xffffffffu, rest != 0)) {
+        const int src = rest ? __ffs(rest) - 1 : lane;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const float o = __shfl_sync(0xffffffffu, v[i], src);
+            if (leader && rest) v[i] += o;
+        }
+        rest &= rest - 1;
+    }
+}
+
+// Work decomposition: a work item is (chunk of 32 consecutive list entries, group of kFuseKPerWarp ray samples) and
+// belongs to one warp; the 2*factor+1 samples of a pixel are therefore spread over several warps (of the same
+// CTA, so the per-pixel planes come from L1) instead of forming one long dependent instruction stream per lane —
+// with ~2 k warps of 11 serial samples each the kernel was latency-bound at 25 us; with ~6x more, shorter warps the
+// SMs have something to switch to.
+constexpr int kFuseKPerWarp = 2;
+
 template <int VARIANT>
 __global__ void __launch_bounds__(256)
 fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2* __restrict__ vlist,
-                 const int* __restrict__ n_valid_ptr, FrameState* st, const float* __restrict__ nx, const float* __restrict__ ny,
-                 const float* __restrict__ nz, const float* __restrict__ x0, const float* __restrict__ y0,
-                 const float* __restrict__ hom_inv, Counters* ctr) {
+                 const int* __restrict__ n_valid_ptr, FrameState* st, const float* __restrict__ nx,
+                 const float* __restrict__ ny, const float* __restrict__ nz, const float* __restrict__ x0,
+                 const float* __restrict__ y0, const float* __restrict__ hom_inv, Counters* ctr) {
     if (pose_src == 2 && !st->converged) return;
     __shared__ Pose pose;
     if (threadIdx.x == 0) {
@@ -356,69 +381,105 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
     const int n_valid = *n_valid_ptr;
     if (blockIdx.x == 0 && threadIdx.x == 0) st->n_valid = n_valid;  // reported with the frame result
     unsigned int n_upd = 0, n_pts = 0;
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += gridDim.x * blockDim.x) {
-        const int2 e = __ldg(vlist + j);
-        const int idx = e.x;
-        const float z = __int_as_float(e.y);
-        const float hx = x0[idx], hy = y0[idx];
-        const float a = nx[idx], b = ny[idx], c = nz[idx];
-        const float hi = hom_inv[idx];
-        const float nsq = dot3_rn(a, b, c, a, b, c);
-        const float d = dot3_rn(a, b, c, hx, hy, 1.f);
-        if ((double)nsq < .1) continue;                                       // MapGradPixelSdfOmp.cpp:97
-        if ((double)__fmul_rn(__fmul_rn(d, d), hi) < .25) continue;           // :100
-        ++n_pts;
-        const float Rxy0 = dot3_rn(R[0], R[1], R[2], hx, hy, 1.f);            // :93
-        const float Rxy1 = dot3_rn(R[3], R[4], R[5], hx, hy, 1.f);
-        const float Rxy2 = dot3_rn(R[6], R[7], R[8], hx, hy, 1.f);
-        float Rn0 = 0.f, Rn1 = 0.f, Rn2 = 0.f;
-        if (VARIANT == 0) {
-            Rn0 = dot3_rn(R[0], R[1], R[2], a, b, c);                         // :95
-            Rn1 = dot3_rn(R[3], R[4], R[5], a, b, c);
-            Rn2 = dot3_rn(R[6], R[7], R[8], a, b, c);
+    const int lane = threadIdx.x & 31;
+    const int S = 2 * g.factor + 1;
+    const int kgroups = (S + kFuseKPerWarp - 1) / kFuseKPerWarp;
+    const int nchunks = (n_valid + 31) >> 5;
+    const int items = nchunks * kgroups;
+    const int warps_total = (gridDim.x * blockDim.x) >> 5;
+    for (int it = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; it < items; it += warps_total) {
+        const int chunk = it / kgroups, kg = it - chunk * kgroups;
+        const int j = chunk * 32 + lane;
+        bool valid = j < n_valid;
+        float z = 0.f, Rxy0 = 0.f, Rxy1 = 0.f, Rxy2 = 0.f, Rn0 = 0.f, Rn1 = 0.f, Rn2 = 0.f;
+        if (valid) {
+            const int2 e = __ldg(vlist + j);
+            const int idx = (e.x >> 16) * g.w + (e.x & 0xFFFF);
+            z = __int_as_float(e.y);
+            const float hx = x0[idx], hy = y0[idx];
+            const float a = nx[idx], b = ny[idx], c = nz[idx];
+            const float hi = hom_inv[idx];
+            const float nsq = dot3_rn(a, b, c, a, b, c);
+            const float d = dot3_rn(a, b, c, hx, hy, 1.f);
+            if ((double)nsq < .1) valid = false;                                       // MapGradPixelSdfOmp.cpp:97
+            else if ((double)__fmul_rn(__fmul_rn(d, d), hi) < .25) valid = false;      // :100
+            Rxy0 = dot3_rn(R[0], R[1], R[2], hx, hy, 1.f);                             // :93
+            Rxy1 = dot3_rn(R[3], R[4], R[5], hx, hy, 1.f);
+            Rxy2 = dot3_rn(R[6], R[7], R[8], hx, hy, 1.f);
+            if (VARIANT == 0) {
+                Rn0 = dot3_rn(R[0], R[1], R[2], a, b, c);                              // :95
+                Rn1 = dot3_rn(R[3], R[4], R[5], a, b, c);
+                Rn2 = dot3_rn(R[6], R[7], R[8], a, b, c);
+            }
         }
+        n_pts += (valid && kg == 0) ? 1u : 0u;
         unsigned long long last_key = kEmptyKey;
         int slot = -1;
-        for (int kk = -g.factor; kk <= g.factor; ++kk) {                      // :103
-            const float s = __fadd_rn(z, __fmul_rn((float)kk, g.vs));
-            const float px = __fadd_rn(__fmul_rn(s, Rxy0), pose.t[0]);        // :105
-            const float py = __fadd_rn(__fmul_rn(s, Rxy1), pose.t[1]);
-            const float pz = __fadd_rn(__fmul_rn(s, Rxy2), pose.t[2]);
-            const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
-            const float qx = __fsub_rn(__fmul_rn(g.vs, (float)vx), pose.t[0]);  // :107
-            const float qy = __fsub_rn(__fmul_rn(g.vs, (float)vy), pose.t[1]);
-            const float qz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pose.t[2]);
-            const float sdf = __fsub_rn(dot3_rn(R[2], R[5], R[8], qx, qy, qz), z);  // :107-108
-            const float wgt = sdf_weight(sdf, g.T, g.inv_T);
-            if (wgt > 0.f) {
-                const unsigned long long key = block_key_of(vx, vy, vz);
-                if (key != last_key) {
-                    last_key = key;
-                    if (m.world > 1 && block_owner(key, m.world) != m.rank) slot = -2;
-                    else {
-                        slot = map_find_or_insert(m, key, ctr);
-                        if (slot < 0) atomicAdd(&ctr->overflow, 1u);
+        const int k_lo = kg * kFuseKPerWarp - g.factor;
+        const int k_hi = min(k_lo + kFuseKPerWarp - 1, g.factor);
+        for (int kk = k_lo; kk <= k_hi; ++kk) {                                        // :103
+            bool has = false;
+            unsigned long long vaddr = 0;
+            float v[VARIANT == 0 ? 5 : 2];
+            if (valid) {
+                const float s = __fadd_rn(z, __fmul_rn((float)kk, g.vs));
+                const float px = __fadd_rn(__fmul_rn(s, Rxy0), pose.t[0]);             // :105
+                const float py = __fadd_rn(__fmul_rn(s, Rxy1), pose.t[1]);
+                const float pz = __fadd_rn(__fmul_rn(s, Rxy2), pose.t[2]);
+                const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
+                const float qx = __fsub_rn(__fmul_rn(g.vs, (float)vx), pose.t[0]);     // :107
+                const float qy = __fsub_rn(__fmul_rn(g.vs, (float)vy), pose.t[1]);
+                const float qz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pose.t[2]);
+                const float sdf = __fsub_rn(dot3_rn(R[2], R[5], R[8], qx, qy, qz), z); // :107-108
+                const float wgt = sdf_weight(sdf, g.T, g.inv_T);
+                if (wgt > 0.f) {                                                       // :110-111
+                    const unsigned long long key = block_key_of(vx, vy, vz);
+                    if (key != last_key) {
+                        last_key = key;
+                        if (m.world > 1 && block_owner(key, m.world) != m.rank) slot = -2;  // another rank's block
+                        else {
+                            slot = map_find_or_insert(m, key, ctr);
+                            if (slot < 0) atomicAdd(&ctr->overflow, 1u);
+                        }
+                    }
+                    if (slot >= 0) {
+                        has = true;
+                        vaddr = (unsigned long long)slot * kBlockVoxels + local_index(vx, vy, vz);
+                        const float ws = wgt * sdf_truncate(sdf, g.T);
+                        if (VARIANT == 0) { v[0] = ws; v[1] = wgt * Rn0; v[2] = wgt * Rn1; v[3] = wgt * Rn2; v[4] = wgt; }
+                        else { v[0] = wgt; v[1] = ws; }
+                        ++n_upd;
                     }
                 }
-                if (slot >= 0) {
-                    const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
-                    const float ws = wgt * sdf_truncate(sdf, g.T);
-                    if (VARIANT == 0) {
-                        atomicAdd(m.acc4 + addr, make_float4(ws, wgt * Rn0, wgt * Rn1, wgt * Rn2));  // :115-117
-                        atomicAdd(m.accW + addr, wgt);
-                    } else {
-                        atomicAdd(m.acc2 + addr, make_float2(wgt, ws));
-                    }
-                    ++n_upd;
+            }
+            if (!has) {
+#pragma unroll
+                for (int i = 0; i < (VARIANT == 0 ? 5 : 2); ++i) v[i] = 0.f;
+            }
+            bool leader;
+            warp_merge_by_key<(VARIANT == 0 ? 5 : 2)>(vaddr, has, v, leader);
+            if (leader) {
+                if (VARIANT == 0) {
+                    atomicAdd(m.acc4 + vaddr, make_float4(v[0], v[1], v[2], v[3]));    // :115-117
+                    atomicAdd(m.accW + vaddr, v[4]);
+                } else {
+                    atomicAdd(m.acc2 + vaddr, make_float2(v[0], v[1]));                // MapPixelSdfOmp.cpp:183-185
                 }
             }
         }
     }
+    // statistics: warp -> CTA (shared-memory atomics) -> one slot per CTA; never thousands of warps on one word
+    __shared__ unsigned int s_pts, s_upd;
+    if (threadIdx.x == 0) { s_pts = 0; s_upd = 0; }
+    __syncthreads();
     n_pts = __reduce_add_sync(0xffffffffu, n_pts);
     n_upd = __reduce_add_sync(0xffffffffu, n_upd);
-    if ((threadIdx.x & 31) == 0 && (n_pts | n_upd)) {
-        atomicAdd(&ctr->points, (unsigned long long)n_pts);
-        atomicAdd(&ctr->updates, (unsigned long long)n_upd);
+    if (lane == 0 && (n_pts | n_upd)) { atomicAdd(&s_pts, n_pts); atomicAdd(&s_upd, n_upd); }
+    __syncthreads();
+    if (threadIdx.x == 0 && (s_pts | s_upd)) {
+        Counters::Slot* sl = ctr->slot + (blockIdx.x & (kCounterSlots - 1));
+        atomicAdd(&sl->points, (unsigned long long)s_pts);
+        atomicAdd(&sl->updates, (unsigned long long)s_upd);
     }
 }
 
