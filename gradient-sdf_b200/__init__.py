@@ -35,7 +35,7 @@ EXPORTS = [
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
-    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_accumulate_local", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -92,6 +92,7 @@ def lib() -> C.CDLL:
     L.gsdf_integrate.argtypes = [H, _f32p, _f32p, C.POINTER(IntegrateStats)]
     L.gsdf_integrate_pose.argtypes = [H, _f32p, C.POINTER(IntegrateStats)]
     L.gsdf_accumulate.argtypes = [H, _f32p, _f32p, C.c_int32, _f32p]
+    L.gsdf_accumulate_local.argtypes = [H, _f32p, _f32p, C.c_int32, _f32p]
     L.gsdf_track.argtypes = [H, _f32p, C.c_int32, C.c_float, C.c_float, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.gsdf_query.argtypes = [H, _f32p, C.c_int64, _f32p, _f32p, _f32p]
     L.gsdf_voxel_count.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -130,6 +131,22 @@ def _fp(a):
 
 def _f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
+
+
+# ---- sharding (host-side restatement of block_owner() in csrc/gsdf_device.cuh) ----------------------------------
+def shard_owner(voxel_keys, world_size: int):
+    """Rank that owns each voxel's 8^3 block: (mix64(packed 21-bit block coordinates) >> 40) % world_size."""
+    k = np.asarray(voxel_keys, dtype=np.int64).reshape(-1, 3) >> 3
+    bias = 1 << 20
+    m = np.uint64(0x1FFFFF)
+    key = ((k[:, 0] + bias).astype(np.uint64) & m) | (((k[:, 1] + bias).astype(np.uint64) & m) << np.uint64(21)) | \
+          (((k[:, 2] + bias).astype(np.uint64) & m) << np.uint64(42))
+    x = key.copy()
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint64(33); x *= np.uint64(0xff51afd7ed558ccd)
+        x ^= x >> np.uint64(33); x *= np.uint64(0xc4ceb9fe1a85ec53)
+        x ^= x >> np.uint64(33)
+    return ((x >> np.uint64(40)) % np.uint64(world_size)).astype(np.int32)
 
 
 # ---- pose algebra (no GPU needed) -------------------------------------------------------------------------
@@ -330,6 +347,12 @@ class Sdf:
         land in caller-owned DEVICE memory at out29_dev_ptr once the handle's stream gets there."""
         R, t = _f32(R).reshape(9), _f32(t)
         self._check(self.L.gsdf_accumulate_noalloc(self.h, _fp(R), _fp(t), sampling, C.c_void_p(out29_dev_ptr)))
+
+    def accumulate_local(self, R, t, sampling: int = 1):
+        """This shard's partial sums (no collective)."""
+        R, t, out = _f32(R).reshape(9), _f32(t), np.zeros(29, np.float32)
+        self._check(self.L.gsdf_accumulate_local(self.h, _fp(R), _fp(t), sampling, _fp(out)))
+        return out
 
     # -- map access
     def voxel_count(self):

@@ -456,7 +456,7 @@ gsdf_status create_impl(gsdf_map* h) {
 }
 
 // v1 reduction over the pixel grid (supports sampling): result lands in d_out29, pose taken from d_pose
-gsdf_status accumulate_device(gsdf_map* h, int sampling) {
+gsdf_status accumulate_device(gsdf_map* h, int sampling, bool collective = true) {
     const TrackIntr ti = make_intr(h, sampling);
     const int total = ti.ws * ti.hs;
     int blocks = (total + kAccThreads - 1) / kAccThreads;
@@ -468,7 +468,7 @@ gsdf_status accumulate_device(gsdf_map* h, int sampling) {
         return check_launch(h, "accumulate_kernel");
     });
     if (s != GSDF_OK) return s;
-    if (h->cfg.world_size > 1) {
+    if (h->cfg.world_size > 1 && collective) {
         if (!h->comm) { h->err = "world_size > 1 but gsdf_comm_init was not called"; return GSDF_ERR_NCCL; }
         const int rc = g_nccl.AllReduce(h->d_out29, h->d_out29, kAccTerms, kNcclFloat, kNcclSum, h->comm, h->stream);
         if (rc != 0) { h->err = std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?"); return GSDF_ERR_NCCL; }
@@ -674,6 +674,22 @@ gsdf_status gsdf_accumulate(gsdf_handle h, const float* R9, const float* t3, int
     s = set_pose_device(h, R9, t3);
     if (s != GSDF_OK) return s;
     s = accumulate_device(h, sampling);
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaMemcpyAsync(h->h_out29, h->d_out29, sizeof(float) * kAccTerms, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    std::memcpy(out29, h->h_out29, sizeof(float) * kAccTerms);
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_accumulate_local(gsdf_handle h, const float* R9, const float* t3, int32_t sampling, float* out29) {
+    if (!h || !R9 || !t3 || !out29 || sampling < 1) return GSDF_ERR_INVALID;
+    if (!h->d_depth) { h->err = "no depth frame set"; return GSDF_ERR_NO_FRAME; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    s = set_pose_device(h, R9, t3);
+    if (s != GSDF_OK) return s;
+    s = accumulate_device(h, sampling, false);
     if (s != GSDF_OK) return s;
     CUDA_TRY(h, cudaMemcpyAsync(h->h_out29, h->d_out29, sizeof(float) * kAccTerms, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));

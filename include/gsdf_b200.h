@@ -47,7 +47,9 @@ typedef struct gsdf_config {
     int32_t normal_window;  /* 11 (main_scan_3d.cpp:183) */
     int32_t log2_capacity;  /* voxel-block hash slots = 2^log2_capacity blocks of 8^3 voxels; 0 -> default 17 */
     int32_t device;         /* CUDA device ordinal */
-    int32_t world_size;     /* >1: map sharded by block key, this handle owns blocks with owner(key) == rank */
+    int32_t world_size;     /* >1: map sharded by block key, this handle owns blocks with owner(key) == rank;
+                             * owner(block) = (mix64(packed 21-bit block coords) >> 40) % world_size, see
+                             * shard_owner() in gradient-sdf_b200/__init__.py for the host-side restatement */
     int32_t rank;
 } gsdf_config;
 
@@ -92,6 +94,10 @@ gsdf_status gsdf_integrate_pose(gsdf_handle h, const float* pose7, gsdf_integrat
  * out29 = g[6], upper triangle of H row-major [21], E, counter.  With world_size > 1 the partials of all
  * ranks are summed (NCCL) so every rank receives the same totals. */
 gsdf_status gsdf_accumulate(gsdf_handle h, const float* R9, const float* t3, int32_t sampling, float* out29);
+/* This rank's partial sums only, no collective: for callers that reduce across shards themselves (any transport;
+ * tests/test_sharding.py sums them with torch.distributed gloo) and for inspecting a shard.  No counterpart in the
+ * reference (it has one map). */
+gsdf_status gsdf_accumulate_local(gsdf_handle h, const float* R9, const float* t3, int32_t sampling, float* out29);
 /* optimize(depth, K): Gauss-Newton from pose7 (updated in place) for at most max_iters iterations with the
  * reference's stopping rule |xi|^2 < conv_threshold^2 (last xi not applied) and NaN guard.
  * *converged = the bool optimize() returns; *iters_used = k at convergence (or max_iters). */

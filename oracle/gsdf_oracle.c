@@ -22,12 +22,23 @@ struct orc_ctx {
     float* planes;              /* 11 cached planes */
     orc_slot* tab;
     size_t cap, count;
+    int world, rank; /* multi-GPU sharding protocol emulation: this context owns blocks with owner(key) == rank */
 };
 
 static uint64_t mix64(uint64_t x) {
     x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
     return x;
 }
+/* shard owner of the 8^3 block a voxel lies in: same function as block_owner() in the CUDA library
+ * (gradient-sdf_b200/csrc/gsdf_device.cuh): packed 21-bit block coordinates, mix64, bits 40.. modulo world */
+static int voxel_owner(const int32_t* v, int world) {
+    const uint64_t bias = 1u << 20;
+    const uint64_t key = (((uint64_t)(uint32_t)((v[0] >> 3) + (int32_t)bias)) & 0x1FFFFFull) |
+                         ((((uint64_t)(uint32_t)((v[1] >> 3) + (int32_t)bias)) & 0x1FFFFFull) << 21) |
+                         ((((uint64_t)(uint32_t)((v[2] >> 3) + (int32_t)bias)) & 0x1FFFFFull) << 42);
+    return (int)((mix64(key) >> 40) % (uint64_t)world);
+}
+
 static size_t key_hash(const int32_t* k) {
     /* the reference's hash (hash_map.h:44-52) is not observable; any hash gives the same key set */
     uint64_t a = (uint32_t)k[0], b = (uint32_t)k[1], c = (uint32_t)k[2];
@@ -175,6 +186,7 @@ orc_ctx* orc_create(int variant, float voxel_size, float trunc_factor, int w, in
     c->T = trunc_factor * voxel_size;                   /* main_scan_3d.cpp:191 */
     c->inv_T = (float)(1. / (double)c->T);              /* Sdf.h:105 */
     c->z_min = 0.5f; c->z_max = 3.5f;
+    c->world = 1; c->rank = 0;
     c->planes = (float*)malloc(sizeof(float) * (size_t)w * h * 11);
     c->cap = 1u << 16; c->count = 0;
     c->tab = (orc_slot*)calloc(c->cap, sizeof(orc_slot));
@@ -188,6 +200,8 @@ void orc_destroy(orc_ctx* c) {
 }
 
 void orc_set_zrange(orc_ctx* c, float z_min, float z_max) { c->z_min = z_min; c->z_max = z_max; }
+void orc_set_shard(orc_ctx* c, int world, int rank) { c->world = world; c->rank = rank; }
+int orc_voxel_owner(const int32_t* v3, int world) { return voxel_owner(v3, world); }
 
 void orc_normal_cache(const orc_ctx* c, float* out11) { memcpy(out11, c->planes, sizeof(float) * (size_t)c->w * c->h * 11); }
 
@@ -260,6 +274,7 @@ long long orc_update(orc_ctx* c, const float* depth, const float* R, const float
             for (int i = 0; i < 3; ++i) q[i] = vf[i] - t[i];
             const float sdf = dot3(Rt2, q) - z; /* :107-108 */
             const float wgt = sdf_weight(c, sdf);
+            if (wgt > 0 && c->world > 1 && voxel_owner(vi, c->world) != c->rank) continue; /* another shard's block */
             if (wgt > 0) {
                 orc_slot* v = tab_get(c, vi); /* :114 */
                 v->weight += wgt;
@@ -294,6 +309,7 @@ void orc_download(const orc_ctx* c, int32_t* keys, float* dist, float* weight, f
 static float grad_weights(const orc_ctx* c, const float* p) { /* MapGradPixelSdf.h:117-125 */
     int32_t vi[3];
     float2vox(c, p, vi);
+    if (c->world > 1 && voxel_owner(vi, c->world) != c->rank) return 0.f; /* counted on the owning shard */
     const orc_slot* s = tab_find(c, vi);
     return s ? s->weight : 0.f;
 }

@@ -28,6 +28,10 @@ typedef struct orc_ctx orc_ctx;
 orc_ctx* orc_create(int variant, float voxel_size, float trunc_factor, int w, int h, const float* K9, int normal_win);
 void orc_destroy(orc_ctx* c);
 void orc_set_zrange(orc_ctx* c, float z_min, float z_max);
+/* Emulation of the multi-GPU sharding protocol (no counterpart in the reference): this context commits only samples
+ * whose 8^3 block it owns and its tracker counts only pixels whose nearest voxel it owns; grad-sdf only. */
+void orc_set_shard(orc_ctx* c, int world, int rank);
+int orc_voxel_owner(const int32_t* v3, int world);
 
 /* NormalEstimator::cache (normals/NormalEstimator.h:81-154): 11 planes of w*h floats, order
  * x0, y0, x0/n^2, y0/n^2, 1/n^2, Q11, Q12, Q13, Q22, Q23, Q33 */

@@ -71,6 +71,9 @@ class Oracle(_Base):
         L.orc_create.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, _f32p, C.c_int]
         L.orc_destroy.argtypes = [C.c_void_p]
         L.orc_set_zrange.argtypes = [C.c_void_p, C.c_float, C.c_float]
+        L.orc_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.orc_voxel_owner.restype = C.c_int
+        L.orc_voxel_owner.argtypes = [_i32p, C.c_int]
         L.orc_normal_cache.argtypes = [C.c_void_p, _f32p]
         L.orc_normals.argtypes = [C.c_void_p, _f32p, _f32p, _f32p, _f32p]
         L.orc_update.restype = C.c_longlong
@@ -103,6 +106,13 @@ class Oracle(_Base):
             self.close()
         except Exception:
             pass
+
+    def set_shard(self, world, rank):
+        self.L.orc_set_shard(self.handle, world, rank)
+
+    def voxel_owner(self, keys, world):
+        k = np.ascontiguousarray(keys, dtype=np.int32).reshape(-1, 3)
+        return np.array([self.L.orc_voxel_owner(k[i].ctypes.data_as(_i32p), world) for i in range(len(k))], np.int32)
 
     def normal_cache(self):
         out = np.zeros((11, self.h, self.w), np.float32)

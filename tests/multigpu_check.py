@@ -1,0 +1,70 @@
+"""Run under torchrun with N >= 2 GPUs: the NCCL-sharded pipeline must reproduce the single-GPU run — identical
+converged flags, poses within 1e-5, and the union of the ranks' voxel key sets equal to the single-GPU key set.
+(Not a pytest file: tests/test_sharding.py launches it when 2 GPUs are present.)"""
+import ctypes as C
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+import gsdf_loader  # noqa: E402
+
+pkg = gsdf_loader.load()
+import importlib  # noqa: E402
+
+synth = importlib.import_module("gradient_sdf_b200.synth")
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+W, H = 320, 240
+frames, poses, K, _ = synth.make_sequence(800, W, H, noise=False)
+frames = frames[:8]
+nest = pkg.NormalEstimator(W, H, K, 11)
+vs, T = np.float32(0.01), np.float32(0.05)
+ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+
+
+def run(sdf):
+    sdf.scan_set_pose(ident)
+    sdf.scan_set_tracker(25, 1e-3, 1.0)
+    out = []
+    sdf.scan_submit(depth_host=frames[0], track=False)
+    out.append(sdf.scan_collect())
+    for i in range(1, len(frames)):
+        sdf.scan_submit(depth_host=frames[i], track=True)
+        out.append(sdf.scan_collect())
+    return out
+
+
+single = pkg.MapGradPixelSdf(vs, T, nest, log2_capacity=16, device=local)
+ref = run(single)
+sharded = pkg.MapGradPixelSdf(vs, T, nest, log2_capacity=16, device=local, world_size=world, rank=rank)
+idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+if rank == 0:
+    buf = (C.c_uint8 * 128)()
+    assert pkg.lib().gsdf_comm_unique_id(buf) == 0
+    idt.copy_(torch.tensor(list(buf), dtype=torch.uint8))
+dist.broadcast(idt, 0)
+sharded.comm_init(bytes(idt.cpu().tolist()))
+got = run(sharded)
+for a, b in zip(got, ref):
+    assert a.converged == b.converged and a.iters == b.iters, (a.converged, b.converged, a.iters, b.iters)
+    assert np.abs(np.array(a.pose7[:]) - np.array(b.pose7[:])).max() < 5e-4
+upd = torch.tensor([sum(r.updates for r in got)], dtype=torch.int64, device="cuda")
+dist.all_reduce(upd)
+assert abs(int(upd) - sum(r.updates for r in ref)) <= 1e-3 * sum(r.updates for r in ref)
+k = sharded.download()[0]
+assert (pkg.shard_owner(k, world) == rank).all()
+n = torch.tensor([len(k)], dtype=torch.int64, device="cuda")
+dist.all_reduce(n)
+nref = single.voxel_count()[0]
+assert abs(int(n) - nref) <= 1e-3 * nref, (int(n), nref)
+dist.barrier()
+if rank == 0:
+    print("MULTIGPU OK", world, "ranks; voxels", int(n), "vs", nref)
+dist.destroy_process_group()

@@ -1,0 +1,101 @@
+"""The C++ host mirror (gradient-sdf_b200/host): forwarding shells with the reference's class names over the C ABI and
+the Scan3D driver that reproduces main_scan_3d.cpp's loop and output files."""
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+BIN = ROOT / "gradient-sdf_b200" / "host" / "scan3d_b200"
+
+
+def write_raw(tmp, frames, K, poses=None):
+    n, h, w = frames.shape
+    np.savetxt(tmp / "intrinsics.txt", K.reshape(3, 3), fmt="%.9g")
+    (tmp / "meta.txt").write_text(f"{w} {h} {n}\n")
+    frames.astype(np.float32).tofile(tmp / "frames.f32")
+    if poses is not None:
+        with open(tmp / "pose.txt", "w") as f:
+            for i, p in enumerate(poses):
+                f.write(f"{i:03d} " + " ".join(f"{x:.9g}" for x in p) + "\n")
+
+
+def run(args):
+    return subprocess.run([str(BIN)] + args, capture_output=True, text=True, timeout=300)
+
+
+def test_driver_builds_and_rejects_like_the_reference():
+    assert BIN.exists(), "run __graft_entry__.build()"
+    r = run(["--scan-type", "voxel-gp", "--data-type", "raw"])
+    assert r.returncode == 1 and "Your specified scan type is not supported (yet)." in r.stderr  # main_scan_3d.cpp:112
+    r = run(["--scan-type", "grad-sdf", "--data-type", "tum"])
+    assert r.returncode == 1 and "Your specified dataset type is not supported (yet)." in r.stderr
+    r = run(["--scan-type", "grad-sdf", "--data-type", "raw", "--input", "/nonexistent"])
+    assert r.returncode == 1 and "No intrinsics file found" in r.stderr  # main_scan_3d.cpp:163
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("stype", ["base-sdf", "grad-sdf"])
+def test_scan3d_driver_matches_python_binding(pkg, synth, tmp_path, stype):
+    W, H = 320, 240
+    noise = stype == "base-sdf"  # grad-sdf: the regime in which its tracker converges with margin
+    frames, poses, K, _ = synth.make_sequence(400 if noise else 800, W, H, noise=noise)
+    frames = frames[:8]
+    write_raw(tmp_path, frames, K)
+    out = tmp_path / "res"
+    # reference loop through the Python binding
+    nest = pkg.NormalEstimator(W, H, K, 11)
+    cls = pkg.MapPixelSdf if stype == "base-sdf" else pkg.MapGradPixelSdf
+    sdf = cls(np.float32(0.01), np.float32(5) * np.float32(0.01), nest, log2_capacity=15)
+    sdf.setup(frames[0])
+    opt = pkg.RigidPointOptimizer(sdf)
+    ref = [opt.pose()]
+    for i in range(1, len(frames)):
+        if opt.optimize(frames[i]):
+            sdf.update(None, opt.pose(), stored=True)
+        ref.append(opt.pose())
+    ref = np.stack(ref)
+    nv_ref = sdf.voxel_count()[0]
+    for extra in ([], ["--pipelined"]):
+        r = run(["--input", str(tmp_path), "--results", str(out), "--scan-type", stype, "--data-type", "raw",
+                 "--voxel-size", "0.01", "--trunc", "5", "--capacity-log2", "15", "--save-sdf"] + extra)
+        assert r.returncode == 0, r.stderr[-2000:]
+        assert "points integrated into tSDF volume!" in r.stdout and "Convergence after" in r.stdout
+        got = np.loadtxt(str(out) + "_poses.txt")[:, 1:]
+        assert got.shape == ref.shape
+        assert np.abs(got - ref).max() < (5e-5 if noise else 5e-4)
+        # output files of MapGradPixelSdfOmp.cpp:186-303
+        info = Path(str(out) + "gradient_sdf_grid_info.txt").read_text().splitlines()
+        assert info[0].startswith("voxel size: 0.01") and info[1].startswith("voxel dim:")
+        d = np.loadtxt(str(out) + "gradient_sdf_sdf_d.txt")
+        wt = np.loadtxt(str(out) + "gradient_sdf_sdf_weight.txt")
+        assert abs(len(d) - nv_ref) <= 0.001 * nv_ref and len(wt) == len(d)
+        assert np.abs(d[:, 1]).max() <= 0.05 + 1e-6 and wt[:, 1].min() > 0
+        dims = [int(x) for x in info[1].split(":")[1].split()]
+        assert d[:, 0].max() < dims[0] * dims[1] * dims[2]
+        ply = Path(str(out) + "gradient_sdf_cloud_final.ply").read_text().splitlines()
+        nvert = int(ply[2].split()[-1])
+        assert ply[0] == "ply" and (nvert > 100 if stype == "grad-sdf" else nvert >= 0) and len(ply) == 10 + nvert
+
+
+@pytest.mark.gpu
+def test_scan3d_driver_ground_truth_poses(pkg, po, synth, tmp_path):
+    """With a pose file every frame is fused at its ground-truth pose without tracking (main_scan_3d.cpp:242,250-254):
+    the voxel count must equal the oracle's on the same frames and poses."""
+    W, H = 160, 120
+    frames, poses, K, _ = synth.make_sequence(100, W, H)
+    frames, poses = frames[:4], poses[:4]
+    write_raw(tmp_path, frames, K, poses)
+    out = tmp_path / "gt"
+    r = run(["--input", str(tmp_path), "--results", str(out), "--scan-type", "grad-sdf", "--data-type", "raw",
+             "--voxel-size", "0.02", "--trunc", "5", "--capacity-log2", "14", "--save-sdf"])
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "4 GT poses are loaded!" in r.stdout
+    orc = po.Oracle(0, np.float32(0.02), np.float32(5), W, H, K)
+    for i in range(4):
+        # the pose file is text: parse it back exactly as the driver does
+        p = np.array([float(x) for x in (tmp_path / "pose.txt").read_text().splitlines()[i].split()[1:]], np.float32)
+        orc.update(frames[i], p)
+    d = np.loadtxt(str(out) + "gradient_sdf_sdf_d.txt")
+    assert len(d) == orc.voxel_count()
