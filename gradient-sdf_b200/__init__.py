@@ -35,7 +35,7 @@ EXPORTS = [
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
-    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_accumulate_local", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -115,6 +115,9 @@ def lib() -> C.CDLL:
     L.gsdf_scan_pending.restype = C.c_int32
     L.gsdf_scan_pending.argtypes = [H]
     L.gsdf_accumulate_noalloc.argtypes = [H, _f32p, _f32p, C.c_int32, C.c_void_p]
+    L.gsdf_trace_enable.argtypes = [H, C.c_int32]
+    L.gsdf_trace_dump.restype = C.c_int64
+    L.gsdf_trace_dump.argtypes = [H, C.c_char_p, C.c_int64]
     L.gsdf_track_stats.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gsdf_profile_enable.argtypes = [H, C.c_int32]
     L.gsdf_profile_read.argtypes = [H, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
@@ -235,6 +238,16 @@ class Sdf:
     @property
     def launch_count(self) -> int:
         return int(self.L.gsdf_launch_count(self.h))
+
+    def trace_enable(self, on: bool = True):
+        self._check(self.L.gsdf_trace_enable(self.h, 1 if on else 0))
+
+    def trace_dump(self):
+        """[(label, microseconds since the first mark)] of the frames submitted since trace_enable."""
+        n = self.L.gsdf_trace_dump(self.h, None, 0)
+        buf = C.create_string_buffer(int(n))
+        self.L.gsdf_trace_dump(self.h, buf, n)
+        return [(l.rsplit(" ", 1)[0], float(l.rsplit(" ", 1)[1])) for l in buf.value.decode().splitlines()]
 
     def track_stats(self):
         """(cumulative Gauss-Newton iterations, cumulative contributing pixels) of gsdf_track on this handle."""

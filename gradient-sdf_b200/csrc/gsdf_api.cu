@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -54,11 +55,16 @@ std::string g_create_error;
 constexpr int kRing = 4;  // frames in flight in the submit/collect pipeline
 }  // namespace
 
+// tracker state and statistics live side by side on the device so that a frame's result is ONE small copy
+struct DeviceResult {
+    FrameState st;
+    Counters ctr;
+};
+
 struct FrameSlot {
     float* d_depth = nullptr;              // landing buffer for host uploads
     cudaEvent_t ev_up = nullptr, ev_norm = nullptr, ev_fused = nullptr, ev_done = nullptr;
-    FrameState* h_state = nullptr;         // pinned result staging
-    Counters* h_ctr = nullptr;
+    ResultSnapshot* h_snap = nullptr;      // pinned + mapped: the frame's last kernel writes the result here
     int mode = 0;
 };
 
@@ -81,6 +87,8 @@ struct gsdf_map {
     unsigned int* d_compact_flags = nullptr;  // [nseg] look-back flags {epoch, count} of compact_tiles_kernel
     unsigned int compact_epoch = 0;
     int nseg = 0;                           // CTAs of the compaction (64 tiles of 8x4 pixels each)
+    int nseg_frame = 0;                     // segments of the frame kernel's compaction (128 tiles each)
+    DeviceResult* d_res = nullptr;    // owns d_state and d_ctr
     FrameState* d_state = nullptr;
     Counters* d_ctr = nullptr;
     float* d_partials = nullptr;      // v1 accumulate / accumulate_list: [acc_blocks][32]
@@ -110,6 +118,10 @@ struct gsdf_map {
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[GSDF_PROF_KINDS];
     size_t prof_used[GSDF_PROF_KINDS] = {0, 0, 0, 0};
+    // timeline tracing (off by default): labelled events on whichever stream the step runs on
+    bool frame_kernel = false;  // GSDF_FRAME_KERNEL=1: whole frame in one cooperative launch (experimental)
+    bool tracing = false;
+    std::vector<std::pair<std::string, cudaEvent_t>> trace;
     ncclComm_t comm = nullptr;
     std::string err;
 };
@@ -213,6 +225,14 @@ struct ProfScope {
     ~ProfScope() { if (stop) cudaEventRecord(stop, st); }
 };
 
+void trace_mark(gsdf_map* h, const char* label, cudaStream_t stream) {
+    if (!h->tracing) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, stream);
+    h->trace.push_back({label, e});
+}
+
 TrackIntr make_intr(const gsdf_map* h, int sampling) {
     TrackIntr ti;
     ti.fx_inv = 1.f / h->cfg.K[0]; ti.fy_inv = 1.f / h->cfg.K[4]; ti.cx = h->cfg.K[2]; ti.cy = h->cfg.K[5];
@@ -243,7 +263,7 @@ gsdf_status launch_normals(gsdf_map* h, const float* depth, int buf, cudaStream_
 // compaction of a frame's z-valid pixels (deterministic, tile order) into d_vlist[buf], count into d_nvalid[buf]
 gsdf_status launch_prepare(gsdf_map* h, const float* depth, int buf, cudaStream_t stream) {
     ProfScope prof(h, GSDF_PROF_PREPARE, stream);
-    h->compact_epoch = (h->compact_epoch + 1) & 0xFFFFFu;
+    h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu;  // 19 bits: flags hold {epoch, count < 2^13}
     compact_tiles_kernel<<<h->nseg, kCompactThreads, 0, stream>>>(depth, h->cfg.width, h->cfg.height, h->geom.z_min,
                                                                   h->geom.z_max, h->d_compact_flags, h->compact_epoch,
                                                                   h->d_vlist[buf], h->d_nvalid + buf);
@@ -286,7 +306,11 @@ gsdf_status launch_fuse(gsdf_map* h, const Pose& pose, int pose_src, int nbuf, c
 }
 
 // the Gauss-Newton loop from the pose in d_state; result (pose, converged, iters) stays in d_state
-gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream_t stream) {
+// fuse_after: integrate the frame in the same launch if the optimisation converged (single-GPU path only)
+// fuse_mode 0/1/2 (never / always / iff converged) integrates the frame in the same launch; frame != null also runs
+// compaction and normals at the head of the launch (single-GPU path only)
+gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream_t stream, int fuse_mode = 0,
+                         ResultSnapshot* snap_out = nullptr, const float* frame = nullptr) {
     const TrackIntr ti = make_intr(h, 1);
     if (h->cfg.world_size == 1) {
         return by_variant(h, [&](auto V) {
@@ -294,14 +318,22 @@ gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream
             MapView view = h->view;
             FrameGeom geom = h->geom;
             TrackIntr ti_ = ti;
-            const int2* vlist = h->d_vlist[buf];
-            const int* nvalid = h->d_nvalid + buf;
+            int2* vlist = h->d_vlist[buf];
+            int* nvalid = h->d_nvalid + buf;
             FrameState* st = h->d_state;
             float* partials = h->d_track_partials;
             TrackParams tp_ = tp;
-            void* args[] = {&view, &geom, &ti_, &vlist, &nvalid, &st, &partials, &tp_};
+            float* fuse_normals = fuse_mode ? h->d_normals[buf] : nullptr;
+            const float* planes = h->d_planes;
+            Counters* ctr = h->d_ctr;
+            ResultSnapshot* snap = snap_out;
+            FramePhases ph;
+            ph.depth = frame; ph.flags = h->d_compact_flags; ph.epoch = 0; ph.nseg = h->nseg_frame;
+            ph.r = h->cfg.normal_window / 2; ph.fuse_mode = fuse_mode;
+            if (frame) { h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu; ph.epoch = h->compact_epoch; }
+            void* args[] = {&view, &geom, &ti_, &vlist, &nvalid, &st, &partials, &tp_, &fuse_normals, &planes, &ctr, &snap, &ph};
             cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_kernel<decltype(V)::value>, dim3(h->track_blocks),
-                                                        dim3(kTrackThreads), args, 0, stream);
+                                                        dim3(kTrackThreads), args, frame ? normals_smem(h) : 0, stream);
             if (e != cudaSuccess) { h->err = std::string("cudaLaunchCooperativeKernel(track_kernel): ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
             return check_launch(h, "track_kernel");
         });
@@ -367,13 +399,13 @@ void free_all(gsdf_map* h) {
     cudaSetDevice(h->cfg.device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
-    cudaFree(h->d_planes); cudaFree(h->d_normals[0]); cudaFree(h->d_normals[1]); cudaFree(h->d_ctr);
-    cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_state); cudaFree(h->d_track_partials);
+    cudaFree(h->d_planes); cudaFree(h->d_normals[0]); cudaFree(h->d_normals[1]); cudaFree(h->d_res);
+    cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_track_partials);
     cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
     cudaFreeHost(h->h_state);
     for (auto& sl : h->ring) {
-        cudaFree(sl.d_depth); cudaFreeHost(sl.h_state); cudaFreeHost(sl.h_ctr);
+        cudaFree(sl.d_depth); cudaFreeHost(sl.h_snap);
         if (sl.ev_up) cudaEventDestroy(sl.ev_up);
         if (sl.ev_norm) cudaEventDestroy(sl.ev_norm);
         if (sl.ev_fused) cudaEventDestroy(sl.ev_fused);
@@ -394,9 +426,13 @@ gsdf_status create_impl(gsdf_map* h) {
     CUDA_TRY(h, cudaGetDeviceProperties(&prop, c.device));
     h->sm_count = prop.multiProcessorCount;
     if (!prop.cooperativeLaunch) { h->err = "device lacks cooperative launch"; return GSDF_ERR_CUDA; }
-    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream_n, cudaStreamNonBlocking));
-    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream_c, cudaStreamNonBlocking));
+    // the main stream carries the sequentially dependent work (track -> fuse -> next track): highest priority, so
+    // that the frame-only work of the NEXT frame on the side stream fills the gaps instead of delaying it
+    int prio_lo = 0, prio_hi = 0;
+    CUDA_TRY(h, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CUDA_TRY(h, cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, prio_hi));
+    CUDA_TRY(h, cudaStreamCreateWithPriority(&h->stream_n, cudaStreamNonBlocking, prio_lo));
+    CUDA_TRY(h, cudaStreamCreateWithPriority(&h->stream_c, cudaStreamNonBlocking, prio_lo));
     const size_t n = (size_t)c.width * c.height;
     h->cap = (size_t)1 << c.log2_capacity;
     h->view.cap_mask = (uint32_t)(h->cap - 1);
@@ -417,16 +453,23 @@ gsdf_status create_impl(gsdf_map* h) {
     CUDA_TRY(h, cudaMemset(h->d_nvalid, 0, sizeof(int) * 2));
     const int ntiles = ((c.width + kTileW - 1) / kTileW) * ((c.height + kTileH - 1) / kTileH);
     h->nseg = (ntiles + kTilesPerBlock - 1) / kTilesPerBlock;
+    h->nseg_frame = (ntiles + kTrackWarps * kTilesPerWarp - 1) / (kTrackWarps * kTilesPerWarp);
     CUDA_TRY(h, cudaMalloc(&h->d_compact_flags, sizeof(unsigned int) * h->nseg));
     CUDA_TRY(h, cudaMemset(h->d_compact_flags, 0, sizeof(unsigned int) * h->nseg));
-    CUDA_TRY(h, cudaMalloc(&h->d_state, sizeof(FrameState)));
-    CUDA_TRY(h, cudaMalloc(&h->d_ctr, sizeof(Counters)));
+    CUDA_TRY(h, cudaMalloc(&h->d_res, sizeof(DeviceResult)));
+    h->d_state = &h->d_res->st;
+    h->d_ctr = &h->d_res->ctr;
     h->acc_blocks = h->sm_count * 2;
     CUDA_TRY(h, cudaMalloc(&h->d_partials, sizeof(float) * kAccStride * h->sm_count * 4));
     // persistent tracker: one CTA per SM (all co-resident, as grid.sync requires)
     int per_sm = 0;
-    if (c.variant == GSDF_GRAD_SDF) CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<0>, kTrackThreads, 0));
-    else CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<1>, kTrackThreads, 0));
+    if (c.variant == GSDF_GRAD_SDF) {
+        CUDA_TRY(h, cudaFuncSetAttribute(track_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<0>, kTrackThreads, normals_smem(h)));
+    } else {
+        CUDA_TRY(h, cudaFuncSetAttribute(track_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<1>, kTrackThreads, normals_smem(h)));
+    }
     if (per_sm < 1) { h->err = "track_kernel does not fit on an SM"; return GSDF_ERR_CUDA; }
     h->track_blocks = h->sm_count;
     CUDA_TRY(h, cudaMalloc(&h->d_track_partials, sizeof(float) * 2 * kAccStride * h->track_blocks));
@@ -440,8 +483,7 @@ gsdf_status create_impl(gsdf_map* h) {
     CUDA_TRY(h, cudaHostAlloc(&h->h_count2, sizeof(unsigned long long) * 4, cudaHostAllocDefault));
     for (auto& sl : h->ring) {
         CUDA_TRY(h, cudaMalloc(&sl.d_depth, sizeof(float) * n));
-        CUDA_TRY(h, cudaHostAlloc(&sl.h_state, sizeof(FrameState), cudaHostAllocDefault));
-        CUDA_TRY(h, cudaHostAlloc(&sl.h_ctr, sizeof(Counters), cudaHostAllocDefault));
+        CUDA_TRY(h, cudaHostAlloc(&sl.h_snap, sizeof(ResultSnapshot), cudaHostAllocMapped));
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_up, cudaEventDisableTiming));
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_norm, cudaEventDisableTiming));
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_fused, cudaEventDisableTiming));
@@ -545,6 +587,7 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     }
     gsdf_map* h = new gsdf_map();
     h->cfg = c;
+    if (const char* e = std::getenv("GSDF_FRAME_KERNEL")) h->frame_kernel = e[0] == '1';
     h->geom.w = c.width; h->geom.h = c.height;
     h->geom.vs = c.voxel_size;
     h->geom.vs_inv = (float)(1. / (double)c.voxel_size);  // MapGradPixelSdf.h:102
@@ -851,29 +894,55 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
         CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, sl.ev_up, 0));
         frame = sl.d_depth;
     }
-    // Pixel compaction and normals depend only on the frame, not on the map or the pose: they run on the side
-    // stream and, with two or more frames in flight, overlap the previous frame's tracking and fusion.  Their
-    // buffers (index seq & 1) were last read by the tracker/fusion of frame seq-2.
     const int nbuf = (int)(seq & 1);
-    if (seq >= 2) CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, h->ring[(seq - 2) % kRing].ev_fused, 0));
-    gsdf_status s = launch_prepare(h, frame, nbuf, h->stream_n);
-    if (s != GSDF_OK) return s;
-    s = launch_normals(h, frame, nbuf, h->stream_n, true);
-    if (s != GSDF_OK) return s;
-    CUDA_TRY(h, cudaEventRecord(sl.ev_norm, h->stream_n));
-    CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_norm, 0));
-    if (mode == GSDF_SCAN_TRACK_FUSE) {
-        s = launch_track(h, h->scan_tp, nbuf, h->stream);
+    gsdf_status s = GSDF_OK;
+    const bool single = h->cfg.world_size == 1 && !h->profiling;
+    if (single && h->frame_kernel) {
+        // ONE cooperative launch per frame: compaction + normals, the Gauss-Newton loop, fusion, result snapshot.
+        // Measured slower than the split below (95 vs 73 us per frame at 640x480: with one 512-thread CTA per SM the
+        // frame-only phases run at a quarter of their stand-alone occupancy), kept behind GSDF_FRAME_KERNEL=1.
+        trace_mark(h, "main:begin", h->stream);
+        TrackParams tp = h->scan_tp;
+        if (mode == GSDF_SCAN_FUSE) tp.max_iters = 0;
+        s = launch_track(h, tp, nbuf, h->stream, mode == GSDF_SCAN_FUSE ? 1 : 2, sl.h_snap, frame);
         if (s != GSDF_OK) return s;
+    } else {
+        // Pixel compaction and normals depend only on the frame, not on the map or the pose: they run on the side
+        // stream (overlapping the previous frame's main-stream work when several frames are in flight); their
+        // buffers (index seq & 1) were last read by the tracker/fusion of frame seq-2.
+        if (seq >= 2) CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, h->ring[(seq - 2) % kRing].ev_fused, 0));
+        trace_mark(h, "side:begin", h->stream_n);
+        s = launch_prepare(h, frame, nbuf, h->stream_n);
+        if (s != GSDF_OK) return s;
+        s = launch_normals(h, frame, nbuf, h->stream_n, true);
+        if (s != GSDF_OK) return s;
+        trace_mark(h, "side:normals", h->stream_n);
+        CUDA_TRY(h, cudaEventRecord(sl.ev_norm, h->stream_n));
+        CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_norm, 0));
+        trace_mark(h, "main:begin", h->stream);
+        if (single && mode == GSDF_SCAN_TRACK_FUSE) {
+            // main stream: track, fuse iff converged and publish the result in ONE cooperative launch
+            s = launch_track(h, h->scan_tp, nbuf, h->stream, 2, sl.h_snap);
+            if (s != GSDF_OK) return s;
+        } else {
+            // separate kernels: per-kernel profiling, sharded maps, frames fused without tracking
+            if (mode == GSDF_SCAN_TRACK_FUSE) {
+                s = launch_track(h, h->scan_tp, nbuf, h->stream);
+                if (s != GSDF_OK) return s;
+            }
+            Pose unused;
+            std::memset(&unused, 0, sizeof(unused));
+            s = launch_fuse(h, unused, mode == GSDF_SCAN_TRACK_FUSE ? 2 : 1, nbuf, h->stream);
+            if (s != GSDF_OK) return s;
+            snapshot_kernel<<<1, 64, 0, h->stream>>>(h->d_state, h->d_ctr, sl.h_snap);
+            s = check_launch(h, "snapshot_kernel");
+            if (s != GSDF_OK) return s;
+        }
     }
-    Pose unused;
-    std::memset(&unused, 0, sizeof(unused));
-    s = launch_fuse(h, unused, mode == GSDF_SCAN_TRACK_FUSE ? 2 : 1, nbuf, h->stream);
-    if (s != GSDF_OK) return s;
     CUDA_TRY(h, cudaEventRecord(sl.ev_fused, h->stream));
-    CUDA_TRY(h, cudaMemcpyAsync(sl.h_state, h->d_state, sizeof(FrameState), cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(h, cudaMemcpyAsync(sl.h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+    trace_mark(h, "main:tracked+fused", h->stream);
     CUDA_TRY(h, cudaEventRecord(sl.ev_done, h->stream));
+    trace_mark(h, "main:result", h->stream);
     sl.mode = mode;
     h->seq_submitted++;
     // the synchronous entry points see this frame as current once the pipeline has drained
@@ -891,16 +960,15 @@ gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
     FrameSlot& sl = h->ring[h->seq_collected % kRing];
     CUDA_TRY(h, cudaEventSynchronize(sl.ev_done));
     h->seq_collected++;
-    const FrameState& st = *sl.h_state;
-    const Counters& c = *sl.h_ctr;
+    const FrameState& st = sl.h_snap->st;
+    const ResultSnapshot& c = *sl.h_snap;
     std::memcpy(out->pose7, st.pose7, sizeof(float) * 7);
     const bool tracked = sl.mode == GSDF_SCAN_TRACK_FUSE;
     out->converged = tracked ? st.converged : 1;
     out->iters = tracked ? st.iters : 0;
     out->fused = out->converged;
     out->n_valid = st.n_valid;
-    unsigned long long pts, upd;
-    sum_counters(c, pts, upd);
+    const unsigned long long pts = c.points, upd = c.updates;
     out->points = (int64_t)(pts - h->last_points);
     out->updates = (int64_t)(upd - h->last_updates);
     out->blocks = (int64_t)c.blocks;
@@ -1016,6 +1084,35 @@ extern "C" gsdf_status gsdf_accumulate_noalloc(gsdf_handle h, const float* R9, c
 }
 
 extern "C" {
+
+gsdf_status gsdf_trace_enable(gsdf_handle h, int32_t on) {
+    if (!h) return GSDF_ERR_INVALID;
+    for (auto& t : h->trace) cudaEventDestroy(t.second);
+    h->trace.clear();
+    h->tracing = on != 0;
+    return GSDF_OK;
+}
+
+// "label microseconds-since-first-mark" per line; returns the number of bytes needed (including the final NUL)
+int64_t gsdf_trace_dump(gsdf_handle h, char* buf, int64_t size) {
+    if (!h) return 0;
+    cudaSetDevice(h->cfg.device);
+    cudaDeviceSynchronize();
+    std::string out;
+    for (size_t i = 0; i < h->trace.size(); ++i) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->trace[0].second, h->trace[i].second);
+        char line[96];
+        std::snprintf(line, sizeof(line), "%s %.2f\n", h->trace[i].first.c_str(), ms * 1e3);
+        out += line;
+    }
+    if (buf && size > 0) {
+        const size_t n = std::min((size_t)size - 1, out.size());
+        std::memcpy(buf, out.data(), n);
+        buf[n] = 0;
+    }
+    return (int64_t)out.size() + 1;
+}
 
 gsdf_status gsdf_track_stats(gsdf_handle h, int64_t* iterations, int64_t* valid_pixels) {
     if (!h) return GSDF_ERR_INVALID;

@@ -44,7 +44,7 @@ struct Counters {
     unsigned int blocks;          // allocated blocks
     unsigned int overflow;        // find-or-insert gave up: GSDF_ERR_CAPACITY
     unsigned int ticket;          // last-block-done ticket of the reduction
-    unsigned int pad;
+    unsigned int ticket_snap;     // last-block-done ticket of the frame-result snapshot
     struct Slot {
         unsigned long long points;   // pixels that passed every validity test
         unsigned long long updates;  // committed (pixel,k) samples

@@ -40,6 +40,37 @@ struct FrameState {
     float sums[32];             // last reduced sums
 };
 
+// What gsdf_scan_collect reports for a frame.  Written by the LAST CTA of the frame's last kernel straight into pinned
+// host memory (mapped), so that no copy operation sits on the main stream between one frame's fusion and the next
+// frame's tracking (a 1 KB cudaMemcpyAsync there measured 8 us, 10 % of a frame).
+struct ResultSnapshot {
+    FrameState st;
+    unsigned long long points, updates;  // cumulative
+    unsigned int blocks, overflow;
+};
+
+// executed by one whole CTA (>= 64 threads) after every other CTA's writes are visible
+__device__ __forceinline__ void write_snapshot(const FrameState* st, const Counters* ctr, ResultSnapshot* out) {
+    __shared__ unsigned long long s_p[kCounterSlots], s_u[kCounterSlots];
+    const int t = threadIdx.x;
+    if (t < kCounterSlots) {
+        s_p[t] = __ldcg(&ctr->slot[t].points);
+        s_u[t] = __ldcg(&ctr->slot[t].updates);
+    }
+    constexpr int kWords = (int)(sizeof(FrameState) / sizeof(int));
+    if (t < kWords) reinterpret_cast<int*>(&out->st)[t] = __ldcg(reinterpret_cast<const int*>(st) + t);
+    __syncthreads();
+    if (t == 0) {
+        unsigned long long p = 0, u = 0;
+        for (int i = 0; i < kCounterSlots; ++i) { p += s_p[i]; u += s_u[i]; }
+        out->points = p; out->updates = u;
+        out->blocks = __ldcg(&ctr->blocks); out->overflow = __ldcg(&ctr->overflow);
+        __threadfence_system();
+    }
+}
+
+__global__ void snapshot_kernel(const FrameState* st, const Counters* ctr, ResultSnapshot* out) { write_snapshot(st, ctr, out); }
+
 constexpr int kTileW = 8, kTileH = 4;           // one warp <-> one 8x4 pixel tile
 constexpr int kTilesPerWarp = 8;
 constexpr int kCompactThreads = 256;
@@ -54,22 +85,24 @@ __device__ __forceinline__ bool z_valid(float z, float z_min, float z_max) { ret
 // The exclusive prefix over CTAs is a chained look-back: CTA b publishes {epoch, count} in flags[b] and sums the
 // flags of all CTAs < b, spinning until they carry this launch's epoch (lower-numbered CTAs are dispatched first and
 // wait only on even lower ones, so the chain always makes progress; flags need no clearing between launches).
-__global__ void __launch_bounds__(kCompactThreads)
-compact_tiles_kernel(const float* __restrict__ depth, int w, int h, float z_min, float z_max,
-                     unsigned int* __restrict__ flags, unsigned int epoch, int2* __restrict__ vlist,
-                     int* __restrict__ n_valid_out) {
+// One segment = (NWARPS * kTilesPerWarp) tiles handled by one CTA of NWARPS warps.  The list order is the global tile
+// order whatever the segment size, so the stand-alone kernel (8 warps) and the frame kernel (16 warps) agree.
+constexpr int kFlagShift = 13;  // a segment holds at most 16 warps * 8 tiles * 32 = 4096 < 2^13 pixels
+template <int NWARPS>
+__device__ __forceinline__ void compact_segment(const float* __restrict__ depth, int w, int h, float z_min, float z_max,
+                                                unsigned int* __restrict__ flags, unsigned int epoch,
+                                                int2* __restrict__ vlist, int* __restrict__ n_valid_out, int seg,
+                                                int nseg, int* s_warp /* [NWARPS] */, int* s_base) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tiles_x = (w + kTileW - 1) / kTileW, tiles_y = (h + kTileH - 1) / kTileH, ntiles = tiles_x * tiles_y;
     const int tx = lane & 7, ty = lane >> 3;
-    __shared__ int s_warp[kCompactThreads / 32];
-    __shared__ int s_base;
     float z[kTilesPerWarp];
     int yx[kTilesPerWarp];
     unsigned int mask[kTilesPerWarp];
     int wtot = 0;
 #pragma unroll
     for (int i = 0; i < kTilesPerWarp; ++i) {
-        const int tile = blockIdx.x * kTilesPerBlock + warp * kTilesPerWarp + i;
+        const int tile = (seg * NWARPS + warp) * kTilesPerWarp + i;
         const int tyi = tile / tiles_x, txi = tile - tyi * tiles_x;
         const int x = txi * kTileW + tx, y = tyi * kTileH + ty;
         const bool in = tile < ntiles && x < w && y < h;
@@ -82,29 +115,40 @@ compact_tiles_kernel(const float* __restrict__ depth, int w, int h, float z_min,
     __syncthreads();
     int before = 0, total = 0;
 #pragma unroll
-    for (int q = 0; q < kCompactThreads / 32; ++q) { const int c = s_warp[q]; before += q < warp ? c : 0; total += c; }
+    for (int q = 0; q < NWARPS; ++q) { const int c = s_warp[q]; before += q < warp ? c : 0; total += c; }
     if (threadIdx.x == 0) {
         __threadfence();
-        atomicExch(flags + blockIdx.x, (epoch << 12) | (unsigned)total);  // total <= 2048 < 2^12
+        atomicExch(flags + seg, (epoch << kFlagShift) | (unsigned)total);
     }
     if (warp == 0) {
         int s = 0;
-        for (int b = lane; b < (int)blockIdx.x; b += 32) {
+        for (int b = lane; b < seg; b += 32) {
             unsigned int f;
-            do { f = *reinterpret_cast<volatile unsigned int*>(flags + b); } while ((f >> 12) != (epoch & 0xFFFFFu));
-            s += (int)(f & 0xFFFu);
+            do { f = *reinterpret_cast<volatile unsigned int*>(flags + b); } while ((f >> kFlagShift) != epoch);
+            s += (int)(f & ((1u << kFlagShift) - 1));
         }
         s = __reduce_add_sync(0xffffffffu, s);
-        if (lane == 0) s_base = s;
+        if (lane == 0) *s_base = s;
     }
     __syncthreads();
-    int off = s_base + before;
+    int off = *s_base + before;
 #pragma unroll
     for (int i = 0; i < kTilesPerWarp; ++i) {
         if (mask[i] & (1u << lane)) vlist[off + __popc(mask[i] & ((1u << lane) - 1))] = make_int2(yx[i], __float_as_int(z[i]));
         off += __popc(mask[i]);
     }
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) *n_valid_out = s_base + total;
+    if (seg == nseg - 1 && threadIdx.x == 0) *n_valid_out = *s_base + total;
+    __syncthreads();  // s_warp / s_base are reused by the caller's next segment
+}
+
+__global__ void __launch_bounds__(kCompactThreads)
+compact_tiles_kernel(const float* __restrict__ depth, int w, int h, float z_min, float z_max,
+                     unsigned int* __restrict__ flags, unsigned int epoch, int2* __restrict__ vlist,
+                     int* __restrict__ n_valid_out) {
+    __shared__ int s_warp[kCompactThreads / 32];
+    __shared__ int s_base;
+    compact_segment<kCompactThreads / 32>(depth, w, h, z_min, z_max, flags, epoch, vlist, n_valid_out, blockIdx.x,
+                                          gridDim.x, s_warp, &s_base);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -214,118 +258,6 @@ __device__ __forceinline__ void grid_reduce_29(const float* partials, int nblock
     }
 }
 
-template <int VARIANT>
-__global__ void __launch_bounds__(kTrackThreads, 1)
-track_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist, const int* __restrict__ n_valid_ptr,
-             FrameState* st, float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp) {
-    cg::grid_group grid = cg::this_grid();
-    __shared__ float s_pose7[8];
-    __shared__ Pose s_pose;
-    __shared__ float s_tot[kAccStride];
-    __shared__ float s_warp[kTrackWarps][kAccStride];
-    __shared__ int s_conv;
-    if (threadIdx.x < 7) s_pose7[threadIdx.x] = st->pose7[threadIdx.x];
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
-        s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
-    }
-    __syncthreads();
-    const int n_valid = *n_valid_ptr;
-    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
-    int converged = 0, k = 0;
-    float valid_sum = 0.f;
-    unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
-    int cs = -1;
-    for (k = 0; k < tp.max_iters; ++k) {
-        float acc[kAccTerms];
-#pragma unroll
-        for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
-        for (int j = gtid; j < n_valid; j += nthreads) {
-            const int2 e = __ldg(vlist + j);
-            track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
-        }
-        float* mine = partials + ((size_t)(k & 1) * gridDim.x + blockIdx.x) * kAccStride;
-        block_reduce_29<kTrackWarps>(acc, s_warp, mine);
-        grid.sync();
-        grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            valid_sum += s_tot[28];
-            s_conv = gauss_newton_step(s_tot, tp.damping, tp.thr_sq, s_pose7);
-            quat_to_R(s_pose7 + 3, s_pose.R);
-            s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
-        }
-        __syncthreads();
-        if (s_conv) { converged = 1; break; }
-    }
-    if (blockIdx.x == 0) {
-        if (threadIdx.x < 7) st->pose7[threadIdx.x] = s_pose7[threadIdx.x];
-        if (threadIdx.x < kAccTerms) st->sums[threadIdx.x] = s_tot[threadIdx.x];
-        if (threadIdx.x == 0) {
-            st->n_valid = n_valid;
-            st->converged = converged;
-            st->iters = converged ? k : tp.max_iters;
-            st->track_iters += (unsigned long long)(converged ? k + 1 : tp.max_iters);
-            st->track_valid += (unsigned long long)valid_sum;
-        }
-    }
-}
-
-// Per-iteration variant (sharded maps): sums of this rank's pixels -> out29 (last-block-done), the caller
-// all-reduces out29 across ranks and then runs solve_kernel.  Exits at once when the loop is already done.
-template <int VARIANT>
-__global__ void __launch_bounds__(kAccThreads)
-accumulate_list_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist,
-                       const int* __restrict__ n_valid_ptr, const FrameState* st, float* __restrict__ partials,
-                       Counters* ctr, float* __restrict__ out29) {
-    if (st->done) return;
-    __shared__ Pose s_pose;
-    __shared__ float sm[kAccThreads / 32][kAccStride];
-    if (threadIdx.x == 0) {
-        float q[4] = {st->pose7[3], st->pose7[4], st->pose7[5], st->pose7[6]};
-        quat_to_R(q, s_pose.R);
-        s_pose.t[0] = st->pose7[0]; s_pose.t[1] = st->pose7[1]; s_pose.t[2] = st->pose7[2];
-    }
-    __syncthreads();
-    float acc[kAccTerms];
-#pragma unroll
-    for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
-    const int n_valid = *n_valid_ptr;
-    unsigned long long ck = kEmptyKey;
-    int cs = -1;
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += gridDim.x * blockDim.x) {
-        const int2 e = __ldg(vlist + j);
-        track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
-    }
-    block_reduce_29<kAccThreads / 32>(acc, sm, partials + (size_t)blockIdx.x * kAccStride);
-    __shared__ bool is_last;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) is_last = (atomicInc(&ctr->ticket, gridDim.x - 1) == gridDim.x - 1);
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    grid_reduce_29<kAccThreads / 32>(partials, gridDim.x, sm, out29);
-}
-
-__global__ void solve_kernel(FrameState* st, const float* __restrict__ sums29, TrackParams tp) {
-    if (threadIdx.x != 0 || st->done) return;
-    float pose7[7], sums[kAccTerms];
-    for (int i = 0; i < 7; ++i) pose7[i] = st->pose7[i];
-    for (int i = 0; i < kAccTerms; ++i) { sums[i] = sums29[i]; st->sums[i] = sums[i]; }
-    const int conv = gauss_newton_step(sums, tp.damping, tp.thr_sq, pose7);
-    for (int i = 0; i < 7; ++i) st->pose7[i] = pose7[i];
-    st->track_iters += 1;
-    st->track_valid += (unsigned long long)sums[28];
-    if (conv) { st->converged = 1; st->iters = st->k; st->done = 1; }
-    else if (++st->k >= tp.max_iters) { st->converged = 0; st->iters = tp.max_iters; st->done = 1; }
-}
-
-__global__ void track_begin_kernel(FrameState* st) {
-    if (threadIdx.x == 0) { st->done = 0; st->k = 0; st->converged = 0; st->iters = 0; }
-}
-
 // ---------------------------------------------------------------------------------------------------------
 // Fusion over the compacted list: one lane per pixel walks its 2*factor+1 ray samples (MapGradPixelSdfOmp.cpp:103);
 // at every sample the warp merges the lanes that hit the SAME voxel (list entries of a warp come from the same
@@ -360,27 +292,18 @@ __device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool h
 // SMs have something to switch to.
 constexpr int kFuseKPerWarp = 2;
 
-template <int VARIANT>
-__global__ void __launch_bounds__(256)
-fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2* __restrict__ vlist,
-                 const int* __restrict__ n_valid_ptr, FrameState* st, const float* __restrict__ nx,
-                 const float* __restrict__ ny, const float* __restrict__ nz, const float* __restrict__ x0,
-                 const float* __restrict__ y0, const float* __restrict__ hom_inv, Counters* ctr) {
-    if (pose_src == 2 && !st->converged) return;
-    __shared__ Pose pose;
-    if (threadIdx.x == 0) {
-        if (pose_src == 0) pose = pose_arg;
-        else {
-            float q[4] = {st->pose7[3], st->pose7[4], st->pose7[5], st->pose7[6]};
-            quat_to_R(q, pose.R);  // pose.rotationMatrix() of the stored SE3
-            pose.t[0] = st->pose7[0]; pose.t[1] = st->pose7[1]; pose.t[2] = st->pose7[2];
-        }
-    }
-    __syncthreads();
+// The fusion work of one CTA: warps stride over the (chunk, sample group) items.  Called by fuse_list_kernel and by
+// the tail of track_kernel (fused track+fuse launch).
+// COHERENT: the list and the normals were produced earlier in the SAME launch (frame kernel) -> L2 loads, not the
+// non-coherent read-only path.
+template <int VARIANT, bool COHERENT>
+__device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, const Pose& pose,
+                                          const int2* __restrict__ vlist, int n_valid, const float* __restrict__ nx,
+                                          const float* __restrict__ ny, const float* __restrict__ nz,
+                                          const float* __restrict__ x0, const float* __restrict__ y0,
+                                          const float* __restrict__ hom_inv, Counters* ctr, unsigned int& n_pts,
+                                          unsigned int& n_upd) {
     const float* R = pose.R;
-    const int n_valid = *n_valid_ptr;
-    if (blockIdx.x == 0 && threadIdx.x == 0) st->n_valid = n_valid;  // reported with the frame result
-    unsigned int n_upd = 0, n_pts = 0;
     const int lane = threadIdx.x & 31;
     const int S = 2 * g.factor + 1;
     const int kgroups = (S + kFuseKPerWarp - 1) / kFuseKPerWarp;
@@ -393,11 +316,12 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
         bool valid = j < n_valid;
         float z = 0.f, Rxy0 = 0.f, Rxy1 = 0.f, Rxy2 = 0.f, Rn0 = 0.f, Rn1 = 0.f, Rn2 = 0.f;
         if (valid) {
-            const int2 e = __ldg(vlist + j);
+            const int2 e = COHERENT ? __ldcg(vlist + j) : __ldg(vlist + j);
             const int idx = (e.x >> 16) * g.w + (e.x & 0xFFFF);
             z = __int_as_float(e.y);
             const float hx = x0[idx], hy = y0[idx];
-            const float a = nx[idx], b = ny[idx], c = nz[idx];
+            const float a = COHERENT ? __ldcg(nx + idx) : nx[idx], b = COHERENT ? __ldcg(ny + idx) : ny[idx],
+                        c = COHERENT ? __ldcg(nz + idx) : nz[idx];
             const float hi = hom_inv[idx];
             const float nsq = dot3_rn(a, b, c, a, b, c);
             const float d = dot3_rn(a, b, c, hx, hy, 1.f);
@@ -468,8 +392,12 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
             }
         }
     }
-    // statistics: warp -> CTA (shared-memory atomics) -> one slot per CTA; never thousands of warps on one word
+}
+
+// statistics: warp -> CTA (shared-memory atomics) -> one slot per CTA; never thousands of warps on one word
+__device__ __forceinline__ void fuse_stats_flush(Counters* ctr, unsigned int n_pts, unsigned int n_upd) {
     __shared__ unsigned int s_pts, s_upd;
+    const int lane = threadIdx.x & 31;
     if (threadIdx.x == 0) { s_pts = 0; s_upd = 0; }
     __syncthreads();
     n_pts = __reduce_add_sync(0xffffffffu, n_pts);
@@ -483,29 +411,54 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
     }
 }
 
+template <int VARIANT>
+__global__ void __launch_bounds__(256)
+fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2* __restrict__ vlist,
+                 const int* __restrict__ n_valid_ptr, FrameState* st, const float* __restrict__ nx,
+                 const float* __restrict__ ny, const float* __restrict__ nz, const float* __restrict__ x0,
+                 const float* __restrict__ y0, const float* __restrict__ hom_inv, Counters* ctr) {
+    if (pose_src == 2 && !st->converged) return;
+    __shared__ Pose pose;
+    if (threadIdx.x == 0) {
+        if (pose_src == 0) pose = pose_arg;
+        else {
+            float q[4] = {st->pose7[3], st->pose7[4], st->pose7[5], st->pose7[6]};
+            quat_to_R(q, pose.R);  // pose.rotationMatrix() of the stored SE3
+            pose.t[0] = st->pose7[0]; pose.t[1] = st->pose7[1]; pose.t[2] = st->pose7[2];
+        }
+    }
+    __syncthreads();
+    const int n_valid = *n_valid_ptr;
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->n_valid = n_valid;  // reported with the frame result
+    unsigned int n_upd = 0, n_pts = 0;
+    fuse_work<VARIANT, false>(m, g, pose, vlist, n_valid, nx, ny, nz, x0, y0, hom_inv, ctr, n_pts, n_upd);
+    fuse_stats_flush(ctr, n_pts, n_upd);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // FALS normals per 32x16 tile (same arithmetic and summation order as normals_kernel, so bit-identical), but
 //   * tiles whose interior holds no z-valid pixel are skipped (fusion never reads normals of invalid pixels);
 //   * the z_inv products are widened to double once, when staged, instead of once per window tap.
-__global__ void __launch_bounds__(NT_W* NT_H)
-normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x0n, const float* __restrict__ y0n,
-                    const float* __restrict__ nsi, const float* __restrict__ Q, float* __restrict__ nx,
-                    float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r, float z_min, float z_max) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+__device__ __forceinline__ void normals_tile(const float* __restrict__ depth, const float* __restrict__ x0n,
+                                             const float* __restrict__ y0n, const float* __restrict__ nsi,
+                                             const float* __restrict__ Q, float* __restrict__ nx,
+                                             float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r,
+                                             float z_min, float z_max, int tile_x, int tile_y, int tix, int tiy,
+                                             unsigned char* smem_raw) {
     const int tw = NT_W + 2 * r, th = NT_H + 2 * r;
     double* a = reinterpret_cast<double*>(smem_raw);   // [3][th][tw] products, widened
     double* rs = a + 3 * tw * th;                      // [3][th][NT_W] row sums
-    const int tid = threadIdx.y * NT_W + threadIdx.x;
-    const int x_base = blockIdx.x * NT_W, y_base = blockIdx.y * NT_H;
-    const int x = x_base + threadIdx.x, y = y_base + threadIdx.y;
+    const int tid = tiy * NT_W + tix;
+    const int x_base = tile_x * NT_W, y_base = tile_y * NT_H;
+    const int x = x_base + tix, y = y_base + tiy;
     const size_t n = (size_t)w * h;
     const bool inside = x < w && y < h;
     const float zc = inside ? depth[(size_t)y * w + x] : 0.f;
     if (!__syncthreads_or(inside && z_valid(zc, z_min, z_max))) return;
 
-    for (int ly = threadIdx.y; ly < th; ly += NT_H) {
+    for (int ly = tiy; ly < th; ly += NT_H) {
         const int gy = reflect101(min(y_base + ly - r, h - 1 + r), h);
-        for (int lx = threadIdx.x; lx < tw; lx += NT_W) {
+        for (int lx = tix; lx < tw; lx += NT_W) {
             const int gx = reflect101(min(x_base + lx - r, w - 1 + r), w);
             const size_t gi = (size_t)gy * w + gx;
             const float z = depth[gi];
@@ -518,17 +471,17 @@ normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x
     }
     __syncthreads();
     for (int p = 0; p < 3; ++p)
-        for (int ly = threadIdx.y; ly < th; ly += NT_H) {
-            const double* row = a + p * tw * th + ly * tw + threadIdx.x;
+        for (int ly = tiy; ly < th; ly += NT_H) {
+            const double* row = a + p * tw * th + ly * tw + tix;
             double s = 0.0;
             for (int d = 0; d <= 2 * r; ++d) s = __dadd_rn(s, row[d]);      // left -> right
-            rs[(p * th + ly) * NT_W + threadIdx.x] = s;
+            rs[(p * th + ly) * NT_W + tix] = s;
         }
     __syncthreads();
     if (!inside) return;
     double s1 = 0.0, s2 = 0.0, s3 = 0.0;
     for (int d = 0; d <= 2 * r; ++d) {                                      // top -> bottom
-        const int j = (threadIdx.y + d) * NT_W + threadIdx.x;
+        const int j = (tiy + d) * NT_W + tix;
         s1 = __dadd_rn(s1, rs[j]);
         s2 = __dadd_rn(s2, rs[th * NT_W + j]);
         s3 = __dadd_rn(s3, rs[2 * th * NT_W + j]);
@@ -544,5 +497,178 @@ normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x
     ny[gi] = __fdiv_rn(vy, nn);
     nz[gi] = __fdiv_rn(vz, nn);
 }
+
+__global__ void __launch_bounds__(NT_W* NT_H)
+normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x0n, const float* __restrict__ y0n,
+                    const float* __restrict__ nsi, const float* __restrict__ Q, float* __restrict__ nx,
+                    float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r, float z_min, float z_max) {
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
+    normals_tile(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
+                 threadIdx.y, smem_dyn);
+}
+
+// Optional frame-only phases run at the head of track_kernel (the "frame kernel": ONE cooperative launch per frame
+// does compaction, normals, the Gauss-Newton loop, fusion and the result snapshot — no side streams, no events, no
+// launch gaps between dependent kernels inside a frame).
+struct FramePhases {
+    const float* depth;      // null: the list and the normals were prepared by earlier launches
+    unsigned int* flags;     // look-back flags of the compaction
+    unsigned int epoch;
+    int nseg;                // segments of kTrackWarps * kTilesPerWarp tiles
+    int r;                   // normal window radius
+    int fuse_mode;           // 0 = never, 1 = always (setup / ground-truth pose), 2 = iff the optimisation converged
+};
+
+template <int VARIANT>
+__global__ void __launch_bounds__(kTrackThreads, 1)
+track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr,
+             FrameState* st, float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp,
+             float* fuse_normals /* null: track only; else 3 planes used by the fusion at the end */,
+             const float* __restrict__ planes /* the 11 cached FALS planes */, Counters* ctr,
+             ResultSnapshot* snap /* null, or pinned host memory for the frame result */, FramePhases ph) {
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
+    __shared__ float s_pose7[8];
+    __shared__ Pose s_pose;
+    __shared__ float s_tot[kAccStride];
+    __shared__ float s_warp[kTrackWarps][kAccStride];
+    __shared__ int s_conv;
+    if (ph.depth != nullptr) {
+        // compaction (look-back over segments) and normals (tiles) both depend only on the depth frame
+        __shared__ int s_cw[kTrackWarps];
+        __shared__ int s_cb;
+        for (int seg = blockIdx.x; seg < ph.nseg; seg += gridDim.x)
+            compact_segment<kTrackWarps>(ph.depth, g.w, g.h, g.z_min, g.z_max, ph.flags, ph.epoch, vlist, n_valid_ptr, seg,
+                                         ph.nseg, s_cw, &s_cb);
+        const size_t np = (size_t)g.w * g.h;
+        const int ntx = (g.w + NT_W - 1) / NT_W, nty = (g.h + NT_H - 1) / NT_H;
+        for (int tile = blockIdx.x; tile < ntx * nty; tile += gridDim.x) {
+            const int ty = tile / ntx, tx = tile - ty * ntx;
+            normals_tile(ph.depth, planes + 2 * np, planes + 3 * np, planes + 4 * np, planes + 5 * np, fuse_normals,
+                         fuse_normals + np, fuse_normals + 2 * np, g.w, g.h, ph.r, g.z_min, g.z_max, tx, ty,
+                         threadIdx.x & (NT_W - 1), threadIdx.x / NT_W, smem_dyn);
+            __syncthreads();
+        }
+        grid.sync();
+    }
+    if (threadIdx.x < 7) s_pose7[threadIdx.x] = st->pose7[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
+        s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+    }
+    __syncthreads();
+    const int n_valid = __ldcg(n_valid_ptr);
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+    int converged = 0, k = 0;
+    float valid_sum = 0.f;
+    unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
+    int cs = -1;
+    for (k = 0; k < tp.max_iters; ++k) {
+        float acc[kAccTerms];
+#pragma unroll
+        for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
+        for (int j = gtid; j < n_valid; j += nthreads) {
+            const int2 e = __ldcg(vlist + j);
+            track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
+        }
+        float* mine = partials + ((size_t)(k & 1) * gridDim.x + blockIdx.x) * kAccStride;
+        block_reduce_29<kTrackWarps>(acc, s_warp, mine);
+        grid.sync();
+        grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            valid_sum += s_tot[28];
+            s_conv = gauss_newton_step(s_tot, tp.damping, tp.thr_sq, s_pose7);
+            quat_to_R(s_pose7 + 3, s_pose.R);
+            s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+        }
+        __syncthreads();
+        if (s_conv) { converged = 1; break; }
+    }
+    if (blockIdx.x == 0) {
+        if (threadIdx.x < 7) st->pose7[threadIdx.x] = s_pose7[threadIdx.x];
+        if (threadIdx.x < kAccTerms) st->sums[threadIdx.x] = s_tot[threadIdx.x];
+        if (threadIdx.x == 0) {
+            st->n_valid = n_valid;
+            st->converged = converged;
+            st->iters = converged ? k : tp.max_iters;
+            st->track_iters += (unsigned long long)(converged ? k + 1 : tp.max_iters);
+            st->track_valid += (unsigned long long)valid_sum;
+        }
+    }
+    // main_scan_3d.cpp:261-264: integrate the frame at the pose just found, iff the optimisation converged — in the
+    // same launch (every CTA holds the final pose in shared memory; the map is not read by anyone else meanwhile)
+    if (fuse_normals != nullptr && (ph.fuse_mode == 1 || (ph.fuse_mode == 2 && converged))) {
+        const size_t np = (size_t)g.w * g.h;
+        unsigned int n_upd = 0, n_pts = 0;
+        fuse_work<VARIANT, true>(m, g, s_pose, vlist, n_valid, fuse_normals, fuse_normals + np, fuse_normals + 2 * np,
+                                 planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd);
+        fuse_stats_flush(ctr, n_pts, n_upd);
+    }
+    if (snap != nullptr) {  // the last CTA to get here publishes the frame result
+        __shared__ bool s_last;
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicInc(&ctr->ticket_snap, gridDim.x - 1) == gridDim.x - 1;
+        __syncthreads();
+        if (s_last) { __threadfence(); write_snapshot(st, ctr, snap); }
+    }
+}
+
+// Per-iteration variant (sharded maps): sums of this rank's pixels -> out29 (last-block-done), the caller
+// all-reduces out29 across ranks and then runs solve_kernel.  Exits at once when the loop is already done.
+template <int VARIANT>
+__global__ void __launch_bounds__(kAccThreads)
+accumulate_list_kernel(MapView m, FrameGeom g, TrackIntr ti, const int2* __restrict__ vlist,
+                       const int* __restrict__ n_valid_ptr, const FrameState* st, float* __restrict__ partials,
+                       Counters* ctr, float* __restrict__ out29) {
+    if (st->done) return;
+    __shared__ Pose s_pose;
+    __shared__ float sm[kAccThreads / 32][kAccStride];
+    if (threadIdx.x == 0) {
+        float q[4] = {st->pose7[3], st->pose7[4], st->pose7[5], st->pose7[6]};
+        quat_to_R(q, s_pose.R);
+        s_pose.t[0] = st->pose7[0]; s_pose.t[1] = st->pose7[1]; s_pose.t[2] = st->pose7[2];
+    }
+    __syncthreads();
+    float acc[kAccTerms];
+#pragma unroll
+    for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
+    const int n_valid = *n_valid_ptr;
+    unsigned long long ck = kEmptyKey;
+    int cs = -1;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += gridDim.x * blockDim.x) {
+        const int2 e = __ldg(vlist + j);
+        track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
+    }
+    block_reduce_29<kAccThreads / 32>(acc, sm, partials + (size_t)blockIdx.x * kAccStride);
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicInc(&ctr->ticket, gridDim.x - 1) == gridDim.x - 1);
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    grid_reduce_29<kAccThreads / 32>(partials, gridDim.x, sm, out29);
+}
+
+__global__ void solve_kernel(FrameState* st, const float* __restrict__ sums29, TrackParams tp) {
+    if (threadIdx.x != 0 || st->done) return;
+    float pose7[7], sums[kAccTerms];
+    for (int i = 0; i < 7; ++i) pose7[i] = st->pose7[i];
+    for (int i = 0; i < kAccTerms; ++i) { sums[i] = sums29[i]; st->sums[i] = sums[i]; }
+    const int conv = gauss_newton_step(sums, tp.damping, tp.thr_sq, pose7);
+    for (int i = 0; i < 7; ++i) st->pose7[i] = pose7[i];
+    st->track_iters += 1;
+    st->track_valid += (unsigned long long)sums[28];
+    if (conv) { st->converged = 1; st->iters = st->k; st->done = 1; }
+    else if (++st->k >= tp.max_iters) { st->converged = 0; st->iters = tp.max_iters; st->done = 1; }
+}
+
+__global__ void track_begin_kernel(FrameState* st) {
+    if (threadIdx.x == 0) { st->done = 0; st->k = 0; st->converged = 0; st->iters = 0; }
+}
+
 
 }  // namespace gsdf

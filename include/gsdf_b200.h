@@ -186,6 +186,11 @@ enum { GSDF_PROF_NORMALS = 0, GSDF_PROF_FUSE = 1, GSDF_PROF_ACCUMULATE = 2 /* tr
        GSDF_PROF_KINDS = 4 };
 gsdf_status gsdf_profile_enable(gsdf_handle h, int32_t on);
 gsdf_status gsdf_profile_read(gsdf_handle h, int32_t kind, int64_t* launches, double* total_ms);
+/* Timeline tracing of the frame pipeline (the reference prints Timer tic/toc lines, Timer.h:59-78): when enabled,
+ * gsdf_scan_submit drops labelled CUDA events on its streams; gsdf_trace_dump synchronises the device and writes
+ * "label microseconds" lines (time since the first mark) into buf, returning the size needed. */
+gsdf_status gsdf_trace_enable(gsdf_handle h, int32_t on);
+int64_t gsdf_trace_dump(gsdf_handle h, char* buf, int64_t size);
 /* Multi-GPU: rank 0 calls gsdf_comm_unique_id, the 128 bytes are distributed by the caller (any transport),
  * then every rank calls gsdf_comm_init on its handle (cfg.world_size/rank).  Needed only for world_size > 1. */
 gsdf_status gsdf_comm_unique_id(uint8_t id128[128]);
