@@ -416,8 +416,12 @@ __global__ void __launch_bounds__(256)
 fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2* __restrict__ vlist,
                  const int* __restrict__ n_valid_ptr, FrameState* st, const float* __restrict__ nx,
                  const float* __restrict__ ny, const float* __restrict__ nz, const float* __restrict__ x0,
-                 const float* __restrict__ y0, const float* __restrict__ hom_inv, Counters* ctr) {
-    if (pose_src == 2 && !st->converged) return;
+                 const float* __restrict__ y0, const float* __restrict__ hom_inv, Counters* ctr,
+                 ResultSnapshot* snap /* null, or pinned host memory: the last CTA publishes the frame result */) {
+    if (pose_src == 2 && !st->converged) {  // nothing to integrate (main_scan_3d.cpp:261): only the result is published
+        if (snap != nullptr && blockIdx.x == 0) write_snapshot(st, ctr, snap);
+        return;
+    }
     __shared__ Pose pose;
     if (threadIdx.x == 0) {
         if (pose_src == 0) pose = pose_arg;
@@ -433,6 +437,14 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
     unsigned int n_upd = 0, n_pts = 0;
     fuse_work<VARIANT, false>(m, g, pose, vlist, n_valid, nx, ny, nz, x0, y0, hom_inv, ctr, n_pts, n_upd);
     fuse_stats_flush(ctr, n_pts, n_upd);
+    if (snap != nullptr) {
+        __shared__ bool s_last;
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicInc(&ctr->ticket_snap, gridDim.x - 1) == gridDim.x - 1;
+        __syncthreads();
+        if (s_last) { __threadfence(); write_snapshot(st, ctr, snap); }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -520,7 +532,7 @@ struct FramePhases {
 };
 
 template <int VARIANT>
-__global__ void __launch_bounds__(kTrackThreads, 1)
+__global__ void __launch_bounds__(kTrackThreads, 2)
 track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr,
              FrameState* st, float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp,
              float* fuse_normals /* null: track only; else 3 planes used by the fusion at the end */,
