@@ -35,7 +35,7 @@ EXPORTS = [
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
-    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -115,6 +115,7 @@ def lib() -> C.CDLL:
     L.gsdf_scan_pending.restype = C.c_int32
     L.gsdf_scan_pending.argtypes = [H]
     L.gsdf_accumulate_noalloc.argtypes = [H, _f32p, _f32p, C.c_int32, C.c_void_p]
+    L.gsdf_debug_track_timers.argtypes = [H, C.c_void_p, C.POINTER(C.c_int32)]
     L.gsdf_trace_enable.argtypes = [H, C.c_int32]
     L.gsdf_trace_dump.restype = C.c_int64
     L.gsdf_trace_dump.argtypes = [H, C.c_char_p, C.c_int64]

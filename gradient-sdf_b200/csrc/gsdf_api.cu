@@ -85,6 +85,7 @@ struct gsdf_map {
     int2* d_vlist[2] = {nullptr, nullptr};  // compacted valid pixels, double-buffered like the normals
     int* d_nvalid = nullptr;                // [2] counts of the two lists
     unsigned int* d_compact_flags = nullptr;  // [nseg] look-back flags {epoch, count} of compact_tiles_kernel
+    unsigned int* d_compact_flags2 = nullptr; // [normals tiles] same for normals_compact_kernel
     unsigned int compact_epoch = 0;
     int nseg = 0;                           // CTAs of the compaction (64 tiles of 8x4 pixels each)
     int nseg_frame = 0;                     // segments of the frame kernel's compaction (128 tiles each)
@@ -120,8 +121,10 @@ struct gsdf_map {
     size_t prof_used[GSDF_PROF_KINDS] = {0, 0, 0, 0};
     // timeline tracing (off by default): labelled events on whichever stream the step runs on
     bool fuse_in_track = true;  // GSDF_FUSE_IN_TRACK=0: separate fusion launch instead of the tracker launch's tail
+    bool merged_side = true;    // GSDF_MERGED_SIDE=0: compaction and normals as two launches
     bool serial = false;        // GSDF_SERIAL=1: frame-only kernels on the main stream instead of the side stream
     bool frame_kernel = false;  // GSDF_FRAME_KERNEL=1: whole frame in one cooperative launch (experimental)
+    unsigned long long* d_dbg = nullptr;  // tracker phase stamps (gsdf_debug_track_timers)
     bool tracing = false;
     std::vector<std::pair<std::string, cudaEvent_t>> trace;
     ncclComm_t comm = nullptr;
@@ -272,6 +275,20 @@ gsdf_status launch_prepare(gsdf_map* h, const float* depth, int buf, cudaStream_
     return check_launch(h, "compact_tiles_kernel");
 }
 
+// compaction + normals of a frame in one launch (the pipeline's frame-only work)
+gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cudaStream_t stream) {
+    const int w = h->cfg.width, ht = h->cfg.height, r = h->cfg.normal_window / 2;
+    const size_t n = (size_t)w * ht;
+    dim3 grid((w + NT_W - 1) / NT_W, (ht + NT_H - 1) / NT_H), block(NT_W, NT_H);
+    float* nrm = h->d_normals[buf];
+    h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu;
+    normals_compact_kernel<<<grid, block, normals_smem(h), stream>>>(
+        depth, h->d_planes + 2 * n, h->d_planes + 3 * n, h->d_planes + 4 * n, h->d_planes + 5 * n, nrm, nrm + n,
+        nrm + 2 * n, w, ht, r, h->geom.z_min, h->geom.z_max, h->d_compact_flags2, h->compact_epoch, h->d_vlist[buf],
+        h->d_nvalid + buf);
+    return check_launch(h, "normals_compact_kernel");
+}
+
 gsdf_status ensure_frame(gsdf_map* h) {
     if (!h->d_depth) { h->err = "no depth frame set"; return GSDF_ERR_NO_FRAME; }
     return GSDF_OK;
@@ -332,7 +349,7 @@ gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream
             ResultSnapshot* snap = snap_out;
             FramePhases ph;
             ph.depth = frame; ph.flags = h->d_compact_flags; ph.epoch = 0; ph.nseg = h->nseg_frame;
-            ph.r = h->cfg.normal_window / 2; ph.fuse_mode = fuse_mode;
+            ph.r = h->cfg.normal_window / 2; ph.fuse_mode = fuse_mode; ph.dbg = h->d_dbg;
             if (frame) { h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu; ph.epoch = h->compact_epoch; }
             void* args[] = {&view, &geom, &ti_, &vlist, &nvalid, &st, &partials, &tp_, &fuse_normals, &planes, &ctr, &snap, &ph};
             cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_kernel<decltype(V)::value>, dim3(h->track_blocks),
@@ -403,7 +420,8 @@ void free_all(gsdf_map* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
     cudaFree(h->d_planes); cudaFree(h->d_normals[0]); cudaFree(h->d_normals[1]); cudaFree(h->d_res);
-    cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_track_partials);
+    cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_compact_flags2); cudaFree(h->d_track_partials);
+    cudaFree(h->d_dbg);
     cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
     cudaFreeHost(h->h_state);
@@ -459,6 +477,9 @@ gsdf_status create_impl(gsdf_map* h) {
     h->nseg_frame = (ntiles + kTrackWarps * kTilesPerWarp - 1) / (kTrackWarps * kTilesPerWarp);
     CUDA_TRY(h, cudaMalloc(&h->d_compact_flags, sizeof(unsigned int) * h->nseg));
     CUDA_TRY(h, cudaMemset(h->d_compact_flags, 0, sizeof(unsigned int) * h->nseg));
+    const int n_ntiles = ((c.width + NT_W - 1) / NT_W) * ((c.height + NT_H - 1) / NT_H);
+    CUDA_TRY(h, cudaMalloc(&h->d_compact_flags2, sizeof(unsigned int) * n_ntiles));
+    CUDA_TRY(h, cudaMemset(h->d_compact_flags2, 0, sizeof(unsigned int) * n_ntiles));
     CUDA_TRY(h, cudaMalloc(&h->d_res, sizeof(DeviceResult)));
     h->d_state = &h->d_res->st;
     h->d_ctr = &h->d_res->ctr;
@@ -494,8 +515,10 @@ gsdf_status create_impl(gsdf_map* h) {
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
     }
     CUDA_TRY(h, cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
-    if (normals_smem(h) > 48 * 1024)
+    if (normals_smem(h) > 48 * 1024) {
         CUDA_TRY(h, cudaFuncSetAttribute(normals_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
+        CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
+    }
     build_normal_cache(c, h->h_planes);
     CUDA_TRY(h, cudaMemcpyAsync(h->d_planes, h->h_planes.data(), sizeof(float) * n * 11, cudaMemcpyHostToDevice, h->stream));
     return clear_map(h);
@@ -593,6 +616,7 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     h->cfg = c;
     if (const char* e = std::getenv("GSDF_FRAME_KERNEL")) h->frame_kernel = e[0] == '1';
     if (const char* e = std::getenv("GSDF_SERIAL")) h->serial = e[0] == '1';
+    if (const char* e = std::getenv("GSDF_MERGED_SIDE")) h->merged_side = e[0] == '1';
     if (const char* e = std::getenv("GSDF_FUSE_IN_TRACK")) h->fuse_in_track = e[0] == '1';
     h->geom.w = c.width; h->geom.h = c.height;
     h->geom.vs = c.voxel_size;
@@ -916,15 +940,21 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
         // Pixel compaction and normals depend only on the frame, not on the map or the pose: they run on the side
         // stream (overlapping the previous frame's main-stream work when several frames are in flight); their
         // buffers (index seq & 1) were last read by the tracker/fusion of frame seq-2.
-        cudaStream_t side = h->serial ? h->stream : h->stream_n;
-        if (seq >= 2 && !h->serial) CUDA_TRY(h, cudaStreamWaitEvent(side, h->ring[(seq - 2) % kRing].ev_fused, 0));
+        // per-kernel profiling runs everything on one stream so that the event brackets do not overlap
+        const bool serial = h->serial || h->profiling;
+        cudaStream_t side = serial ? h->stream : h->stream_n;
+        if (seq >= 2 && !serial) CUDA_TRY(h, cudaStreamWaitEvent(side, h->ring[(seq - 2) % kRing].ev_fused, 0));
         trace_mark(h, "side:begin", side);
-        s = launch_prepare(h, frame, nbuf, side);
-        if (s != GSDF_OK) return s;
-        s = launch_normals(h, frame, nbuf, side, true);
+        if (h->profiling || !h->merged_side) {  // separate launches (also keeps the per-kernel brackets meaningful)
+            s = launch_prepare(h, frame, nbuf, side);
+            if (s != GSDF_OK) return s;
+            s = launch_normals(h, frame, nbuf, side, true);
+        } else {
+            s = launch_normals_compact(h, frame, nbuf, side);
+        }
         if (s != GSDF_OK) return s;
         trace_mark(h, "side:normals", side);
-        if (!h->serial) {
+        if (!serial) {
             CUDA_TRY(h, cudaEventRecord(sl.ev_norm, side));
             CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_norm, 0));
         }
@@ -1092,6 +1122,27 @@ extern "C" gsdf_status gsdf_accumulate_noalloc(gsdf_handle h, const float* R9, c
 }
 
 extern "C" {
+
+// Debug: %globaltimer stamps of the next gsdf_track's phases per CTA and pass: out[n_ctas][4][6] nanoseconds
+// (0 lookups begin, 1 lookups end, 2 CTA reduce end, 3 grid barrier passed, 4 grid reduce end, 5 solve end).
+// Call once with out = NULL to arm (allocates), run gsdf_track, then call with a buffer of *n_ctas * 24 values.
+gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int32_t* n_ctas) {
+    if (!h || !n_ctas) return GSDF_ERR_INVALID;
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    *n_ctas = h->track_blocks;
+    const size_t bytes = sizeof(unsigned long long) * h->track_blocks * 24;
+    if (!h->d_dbg) {
+        CUDA_TRY(h, cudaMalloc(&h->d_dbg, bytes));
+        CUDA_TRY(h, cudaMemset(h->d_dbg, 0, bytes));
+    }
+    if (out) {
+        CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+        CUDA_TRY(h, cudaMemcpy(out, h->d_dbg, bytes, cudaMemcpyDeviceToHost));
+        CUDA_TRY(h, cudaFree(h->d_dbg));
+        h->d_dbg = nullptr;
+    }
+    return GSDF_OK;
+}
 
 gsdf_status gsdf_trace_enable(gsdf_handle h, int32_t on) {
     if (!h) return GSDF_ERR_INVALID;

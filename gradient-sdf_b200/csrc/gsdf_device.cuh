@@ -99,6 +99,22 @@ __device__ __forceinline__ int map_find(const MapView& m, unsigned long long key
     return -1;
 }
 
+// Probe that continues from a first slot whose key has already been loaded (lets a caller issue the first loads of
+// several independent lookups together and resolve them afterwards).
+__device__ __forceinline__ int map_find_resume(const MapView& m, unsigned long long key, uint32_t slot,
+                                               unsigned long long first) {
+    if (first == key) return (int)slot;
+    if (first == kEmptyKey) return -1;
+#pragma unroll 1
+    for (int probe = 1; probe < kMaxProbe; ++probe) {
+        slot = (slot + 1) & m.cap_mask;
+        const unsigned long long k = __ldcg(m.keys + slot);
+        if (k == key) return (int)slot;
+        if (k == kEmptyKey) return -1;
+    }
+    return -1;
+}
+
 // Find-or-insert (the reference's tsdf_[vi], MapGradPixelSdfOmp.cpp:114, at block granularity).
 // Returns the slot, or -1 if kMaxProbe slots were all taken by other keys (caller raises overflow).
 __device__ __forceinline__ int map_find_or_insert(const MapView& m, unsigned long long key, Counters* ctr) {

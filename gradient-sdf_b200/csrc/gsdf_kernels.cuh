@@ -237,20 +237,44 @@ struct Lookup<1> {  // MapPixelSdf.h:107-143 + interp3, MapPixelSdfOmp.cpp:44-11
 #pragma unroll
             for (int c = 0; c < 8; ++c) v[c] = base[(c & 1) + ((c >> 1) & 1) * 8 + (c >> 2) * 64];
         } else {
-            size_t addr[8];
-            unsigned long long last_key = ck;
-            int slot = cs;
+            // the cell straddles 2, 4 or 8 blocks: a corner (i0, j0, k0) lies in block base + (i0 & qx, j0 & qy, k0 & qz)
+            // where q* tells whether that axis crosses; only those block combinations are probed (29 % of all cells
+            // need 2 probes, 4 % need 4, 0.2 % need 8)
+            const int qx = lx == 7, qy = ly == 7, qz = lz == 7;
+            const int bx = im >> kBlockLog2, by = jm >> kBlockLog2, bz = km >> kBlockLog2;
+            // first issue the key loads of ALL needed blocks, then resolve them: the probes are independent, and a
+            // lane that needs 8 of them would otherwise pay 8 dependent L2 round trips (the slowest warp of a CTA sets
+            // the length of every Gauss-Newton pass: measured 9 us against 3 us for grad-sdf before this change)
+            int slots[8];
+            uint32_t hs[8];
+            unsigned long long want[8], got[8];
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int vx = im + (c & 1), vy = jm + ((c >> 1) & 1), vz = km + (c >> 2);
-                const unsigned long long key = block_key_of(vx, vy, vz);
-                if (key != last_key) { last_key = key; slot = map_find(m, key); }
-                if (c == 0) { ck = last_key; cs = slot; }
-                if (slot < 0) return 0.f;  // weights(): all 8 corners must exist (MapPixelSdf.h:127-136)
-                addr[c] = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
+            for (int e = 0; e < 8; ++e) {
+                const int ex = e & 1, ey = (e >> 1) & 1, ez = e >> 2;
+                const bool need = (ex <= qx) && (ey <= qy) && (ez <= qz);
+                want[e] = pack_block(bx + ex, by + ey, bz + ez);
+                hs[e] = hash_key(want[e]) & m.cap_mask;
+                got[e] = kEmptyKey;
+                if (need && !(e == 0 && want[0] == ck)) got[e] = __ldcg(m.keys + hs[e]);
             }
 #pragma unroll
-            for (int c = 0; c < 8; ++c) v[c] = m.acc2[addr[c]];
+            for (int e = 0; e < 8; ++e) {
+                const int ex = e & 1, ey = (e >> 1) & 1, ez = e >> 2;
+                const bool need = (ex <= qx) && (ey <= qy) && (ez <= qz);
+                slots[e] = 0;
+                if (need) {
+                    if (e == 0 && want[0] == ck) slots[0] = cs;
+                    else slots[e] = map_find_resume(m, want[e], hs[e], got[e]);
+                    if (e == 0) { ck = want[0]; cs = slots[0]; }
+                    if (slots[e] < 0) return 0.f;  // weights(): all 8 corners must exist (MapPixelSdf.h:127-136)
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int i0 = c & 1, j0 = (c >> 1) & 1, k0 = c >> 2;
+                const int e = (i0 & qx) | ((j0 & qy) << 1) | ((k0 & qz) << 2);
+                v[c] = m.acc2[(size_t)slots[e] * kBlockVoxels + local_index(im + i0, jm + j0, km + k0)];
+            }
         }
         bool all = true;
 #pragma unroll

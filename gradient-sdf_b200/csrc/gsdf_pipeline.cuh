@@ -529,7 +529,61 @@ struct FramePhases {
     int nseg;                // segments of kTrackWarps * kTilesPerWarp tiles
     int r;                   // normal window radius
     int fuse_mode;           // 0 = never, 1 = always (setup / ground-truth pose), 2 = iff the optimisation converged
+    unsigned long long* dbg; // null, or [gridDim.x][4 passes][6] %globaltimer stamps of the tracker's phases
 };
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define GSDF_STAMP(i) do { if (ph.dbg && threadIdx.x == 0 && k < 4) ph.dbg[((size_t)blockIdx.x * 4 + k) * 6 + (i)] = global_ns(); } while (0)
+
+// Frame-only work of the pipeline in ONE launch: each CTA compacts the z-valid pixels of its 32x16 tile (16 warps <->
+// its sixteen 8x4 sub-tiles, chained look-back over the CTAs for the exclusive prefix) and then computes the tile's
+// normals.  List order: 32x16 tiles row-major, 8x4 sub-tiles row-major inside, pixels row-major inside.
+__global__ void __launch_bounds__(NT_W* NT_H)
+normals_compact_kernel(const float* __restrict__ depth, const float* __restrict__ x0n, const float* __restrict__ y0n,
+                       const float* __restrict__ nsi, const float* __restrict__ Q, float* __restrict__ nx,
+                       float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r, float z_min, float z_max,
+                       unsigned int* __restrict__ flags, unsigned int epoch, int2* __restrict__ vlist,
+                       int* __restrict__ n_valid_out) {
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
+    __shared__ int s_warp[NT_W * NT_H / 32];
+    __shared__ int s_base;
+    const int tid = threadIdx.y * NT_W + threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int cta = blockIdx.y * gridDim.x + blockIdx.x, ncta = gridDim.x * gridDim.y;
+    const int px = blockIdx.x * NT_W + (warp & 3) * kTileW + (lane & 7);
+    const int py = blockIdx.y * NT_H + (warp >> 2) * kTileH + (lane >> 3);
+    const bool in = px < w && py < h;
+    const float z = in ? __ldg(depth + (size_t)py * w + px) : 0.f;
+    const unsigned int mask = __ballot_sync(0xffffffffu, in && z_valid(z, z_min, z_max));
+    if (lane == 0) s_warp[warp] = __popc(mask);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int q = 0; q < NT_W * NT_H / 32; ++q) { const int c = s_warp[q]; before += q < warp ? c : 0; total += c; }
+    if (tid == 0) atomicExch(flags + cta, (epoch << kFlagShift) | (unsigned)total);
+    if (total > 0 || cta == ncta - 1) {
+        if (warp == 0) {
+            int s = 0;
+            for (int b = lane; b < cta; b += 32) {
+                unsigned int f;
+                do { f = *reinterpret_cast<volatile unsigned int*>(flags + b); } while ((f >> kFlagShift) != epoch);
+                s += (int)(f & ((1u << kFlagShift) - 1));
+            }
+            s = __reduce_add_sync(0xffffffffu, s);
+            if (lane == 0) s_base = s;
+        }
+        __syncthreads();
+        if (mask & (1u << lane))
+            vlist[s_base + before + __popc(mask & ((1u << lane) - 1))] = make_int2((py << 16) | px, __float_as_int(z));
+        if (cta == ncta - 1 && tid == 0) *n_valid_out = s_base + total;
+    }
+    if (total == 0) return;  // no valid pixel in the tile: fusion never reads its normals
+    normals_tile(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
+                 threadIdx.y, smem_dyn);
+}
 
 template <int VARIANT>
 __global__ void __launch_bounds__(kTrackThreads, 2)
@@ -580,15 +634,20 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
         float acc[kAccTerms];
 #pragma unroll
         for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
+        GSDF_STAMP(0);
         for (int j = gtid; j < n_valid; j += nthreads) {
             const int2 e = __ldcg(vlist + j);
             track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
         }
+        GSDF_STAMP(1);
         float* mine = partials + ((size_t)(k & 1) * gridDim.x + blockIdx.x) * kAccStride;
         block_reduce_29<kTrackWarps>(acc, s_warp, mine);
+        GSDF_STAMP(2);
         grid.sync();
+        GSDF_STAMP(3);
         grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
         __syncthreads();
+        GSDF_STAMP(4);
         if (threadIdx.x == 0) {
             valid_sum += s_tot[28];
             s_conv = gauss_newton_step(s_tot, tp.damping, tp.thr_sq, s_pose7);
@@ -596,6 +655,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
             s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
         }
         __syncthreads();
+        GSDF_STAMP(5);
         if (s_conv) { converged = 1; break; }
     }
     if (blockIdx.x == 0) {

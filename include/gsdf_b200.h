@@ -191,6 +191,8 @@ gsdf_status gsdf_profile_read(gsdf_handle h, int32_t kind, int64_t* launches, do
  * "label microseconds" lines (time since the first mark) into buf, returning the size needed. */
 gsdf_status gsdf_trace_enable(gsdf_handle h, int32_t on);
 int64_t gsdf_trace_dump(gsdf_handle h, char* buf, int64_t size);
+/* Debug aid: per-CTA %globaltimer stamps of the tracker's phases (see gsdf_api.cu); not for production use. */
+gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int32_t* n_ctas);
 /* Multi-GPU: rank 0 calls gsdf_comm_unique_id, the 128 bytes are distributed by the caller (any transport),
  * then every rank calls gsdf_comm_init on its handle (cfg.world_size/rank).  Needed only for world_size > 1. */
 gsdf_status gsdf_comm_unique_id(uint8_t id128[128]);

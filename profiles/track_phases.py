@@ -1,0 +1,43 @@
+"""Phase timing of the persistent tracker from in-kernel %globaltimer stamps: python profiles/track_phases.py [grad|base]"""
+import ctypes as C
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+import gsdf_loader  # noqa: E402
+
+pkg = gsdf_loader.load()
+import importlib  # noqa: E402
+
+synth = importlib.import_module("gradient_sdf_b200.synth")
+variant = sys.argv[1] if len(sys.argv) > 1 else "grad"
+W, H = 640, 480
+frames, poses, K, _ = synth.make_sequence(100, W, H)
+nest = pkg.NormalEstimator(W, H, K, 11)
+cls = pkg.MapGradPixelSdf if variant == "grad" else pkg.MapPixelSdf
+sdf = cls(np.float32(0.01), np.float32(0.05), nest, log2_capacity=17)
+for i in range(6):
+    sdf.update(frames[i], poses[i])
+opt = pkg.RigidPointOptimizer(sdf)
+opt.set_pose(poses[5])
+opt.optimize(frames[6])  # warm
+n = C.c_int32(0)
+sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, None, C.byref(n)))
+opt.set_pose(poses[5])
+conv = opt.optimize(frames[6])
+buf = np.zeros((n.value, 4, 6), np.uint64)
+sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, buf.ctypes.data, C.byref(n)))
+t = buf.astype(np.int64)
+print(variant, "ctas", n.value, "converged", conv, "iters", opt.last_iterations)
+names = ["lookups", "cta reduce", "grid barrier", "grid reduce", "solve"]
+for k in range(min(4, opt.last_iterations + 1)):
+    tk = t[:, k, :]
+    ok = tk[:, 0] > 0
+    t0 = tk[ok, 0].min()
+    print(f" pass {k}: begin spread {(tk[ok, 0].max() - t0) / 1e3:.2f} us; pass length {(tk[ok, 5].max() - t0) / 1e3:.2f} us")
+    for i, nm in enumerate(names):
+        d = (tk[ok, i + 1] - tk[ok, i]) / 1e3
+        print(f"   {nm:12s} mean {d.mean():6.2f}  max {d.max():6.2f} us   (phase ends at {(tk[ok, i + 1].max() - t0) / 1e3:6.2f} us)")
