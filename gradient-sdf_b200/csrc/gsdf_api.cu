@@ -625,6 +625,8 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     h->geom.inv_T = (float)(1. / (double)c.truncation);   // Sdf.h:105
     h->geom.z_min = c.z_min; h->geom.z_max = c.z_max;
     h->geom.factor = (int)std::floor(c.truncation / c.voxel_size);  // MapGradPixelSdfOmp.cpp:78
+    h->geom.fuse_kpw = 2;
+    if (const char* e = std::getenv("GSDF_FUSE_KPW")) h->geom.fuse_kpw = std::max(1, std::atoi(e));
     gsdf_status s = create_impl(h);
     if (s != GSDF_OK) { g_create_error = h->err; free_all(h); return s; }
     *out = h;

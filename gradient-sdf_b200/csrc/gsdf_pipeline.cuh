@@ -285,12 +285,11 @@ __device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool h
     }
 }
 
-// Work decomposition: a work item is (chunk of 32 consecutive list entries, group of kFuseKPerWarp ray samples) and
+// Work decomposition: a work item is (chunk of 32 consecutive list entries, group of g.fuse_kpw ray samples) and
 // belongs to one warp; the 2*factor+1 samples of a pixel are therefore spread over several warps (of the same
 // CTA, so the per-pixel planes come from L1) instead of forming one long dependent instruction stream per lane —
 // with ~2 k warps of 11 serial samples each the kernel was latency-bound at 25 us; with ~6x more, shorter warps the
 // SMs have something to switch to.
-constexpr int kFuseKPerWarp = 2;
 
 // The fusion work of one CTA: warps stride over the (chunk, sample group) items.  Called by fuse_list_kernel and by
 // the tail of track_kernel (fused track+fuse launch).
@@ -306,7 +305,8 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
     const float* R = pose.R;
     const int lane = threadIdx.x & 31;
     const int S = 2 * g.factor + 1;
-    const int kgroups = (S + kFuseKPerWarp - 1) / kFuseKPerWarp;
+    const int kpw = g.fuse_kpw;
+    const int kgroups = (S + kpw - 1) / kpw;
     const int nchunks = (n_valid + 31) >> 5;
     const int items = nchunks * kgroups;
     const int warps_total = (gridDim.x * blockDim.x) >> 5;
@@ -339,8 +339,8 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
         n_pts += (valid && kg == 0) ? 1u : 0u;
         unsigned long long last_key = kEmptyKey;
         int slot = -1;
-        const int k_lo = kg * kFuseKPerWarp - g.factor;
-        const int k_hi = min(k_lo + kFuseKPerWarp - 1, g.factor);
+        const int k_lo = kg * kpw - g.factor;
+        const int k_hi = min(k_lo + kpw - 1, g.factor);
         for (int kk = k_lo; kk <= k_hi; ++kk) {                                        // :103
             bool has = false;
             unsigned long long vaddr = 0;

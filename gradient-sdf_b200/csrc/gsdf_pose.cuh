@@ -113,10 +113,13 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
     // critical path of every Gauss-Newton pass)
     // (loops run over the full fixed range with a predicate instead of triangular bounds: nvcc keeps A in
     // registers only then)
-    float A[36], y[6], x6[6];
+    float A[36], y[6], x6[6], inv[6];
 #pragma unroll
     for (int i = 0; i < 36; ++i) A[i] = H36[i];
     bool ok = true;  // false once a pivot was non-positive: Eigen stops there and leaves the remaining columns as is
+    // Divisions by a pivot are done as one reciprocal per column and multiplications (<= 1 ulp away from Eigen's
+    // divisions, far inside the solve's tolerance): the 12 dependent IEEE divisions of the two substitutions were
+    // a third of the single-thread critical path that every Gauss-Newton pass of the persistent tracker waits for.
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
         float x = A[6 * k + k];
@@ -125,7 +128,9 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
             if (j < k) x -= A[6 * k + j] * A[6 * k + j];
         const bool good = ok && !(x <= 0.f);
         const float r = sqrtf(x);
+        const float ir = 1.f / r;
         A[6 * k + k] = good ? r : A[6 * k + k];
+        inv[k] = good ? ir : 1.f / A[6 * k + k];
 #pragma unroll
         for (int i = 0; i < 6; ++i)
             if (i > k) {
@@ -133,7 +138,7 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
 #pragma unroll
                 for (int j = 0; j < 6; ++j)
                     if (j < k) s -= A[6 * i + j] * A[6 * k + j];
-                A[6 * i + k] = good ? s / r : A[6 * i + k];
+                A[6 * i + k] = good ? s * ir : A[6 * i + k];
             }
         ok = good;
     }
@@ -143,7 +148,7 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
 #pragma unroll
         for (int j = 0; j < 6; ++j)
             if (j < i) s -= A[6 * i + j] * y[j];
-        y[i] = s / A[6 * i + i];
+        y[i] = s * inv[i];
     }
 #pragma unroll
     for (int ii = 0; ii < 6; ++ii) {
@@ -152,7 +157,7 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
 #pragma unroll
         for (int j = 0; j < 6; ++j)
             if (j > i) s -= A[6 * j + i] * x6[j];
-        x6[i] = s / A[6 * i + i];
+        x6[i] = s * inv[i];
     }
 #pragma unroll
     for (int i = 0; i < 6; ++i) xi6[i] = x6[i];
