@@ -35,7 +35,7 @@ EXPORTS = [
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
-    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_p2p_export", "gsdf_p2p_connect", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -122,6 +122,8 @@ def lib() -> C.CDLL:
     L.gsdf_track_stats.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gsdf_profile_enable.argtypes = [H, C.c_int32]
     L.gsdf_profile_read.argtypes = [H, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+    L.gsdf_p2p_export.argtypes = [H, C.POINTER(C.c_uint8)]
+    L.gsdf_p2p_connect.argtypes = [H, C.POINTER(C.c_uint8)]
     L.gsdf_comm_unique_id.argtypes = [C.POINTER(C.c_uint8)]
     L.gsdf_comm_init.argtypes = [H, C.POINTER(C.c_uint8)]
     L.gsdf_version.restype = C.c_char_p
@@ -264,6 +266,16 @@ class Sdf:
         n, ms = C.c_int64(0), C.c_double(0.0)
         self._check(self.L.gsdf_profile_read(self.h, kind, C.byref(n), C.byref(ms)))
         return int(n.value), float(ms.value)
+
+    def p2p_export(self) -> bytes:
+        buf = (C.c_uint8 * 64)()
+        self._check(self.L.gsdf_p2p_export(self.h, buf))
+        return bytes(buf)
+
+    def p2p_connect(self, handles: bytes):
+        """handles: world_size * 64 bytes, the ranks' p2p_export() results in rank order."""
+        buf = (C.c_uint8 * len(handles)).from_buffer_copy(handles)
+        self._check(self.L.gsdf_p2p_connect(self.h, buf))
 
     def comm_init(self, id128: bytes):
         buf = (C.c_uint8 * 128).from_buffer_copy(id128)

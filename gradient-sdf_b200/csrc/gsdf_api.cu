@@ -125,6 +125,12 @@ struct gsdf_map {
     bool serial = false;        // GSDF_SERIAL=1: frame-only kernels on the main stream instead of the side stream
     bool frame_kernel = false;  // GSDF_FRAME_KERNEL=1: whole frame in one cooperative launch (experimental)
     unsigned long long* d_dbg = nullptr;  // tracker phase stamps (gsdf_debug_track_timers)
+    // NVLink peer exchange of the sharded tracker (gsdf_p2p_export / gsdf_p2p_connect)
+    void* d_p2p = nullptr;            // [2][world][32] 64-bit {tag, float} words, then one error word
+    PeerExchange px{};
+    bool p2p_connected = false;
+    unsigned int p2p_launches = 0;
+    void* p2p_peer_base[kMaxPeers] = {};
     bool tracing = false;
     std::vector<std::pair<std::string, cudaEvent_t>> trace;
     ncclComm_t comm = nullptr;
@@ -332,7 +338,7 @@ gsdf_status launch_fuse(gsdf_map* h, const Pose& pose, int pose_src, int nbuf, c
 gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream_t stream, int fuse_mode = 0,
                          ResultSnapshot* snap_out = nullptr, const float* frame = nullptr) {
     const TrackIntr ti = make_intr(h, 1);
-    if (h->cfg.world_size == 1) {
+    if (h->cfg.world_size == 1 || h->p2p_connected) {
         return by_variant(h, [&](auto V) {
             ProfScope prof(h, GSDF_PROF_ACCUMULATE, stream);
             MapView view = h->view;
@@ -351,7 +357,10 @@ gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream
             ph.depth = frame; ph.flags = h->d_compact_flags; ph.epoch = 0; ph.nseg = h->nseg_frame;
             ph.r = h->cfg.normal_window / 2; ph.fuse_mode = fuse_mode; ph.dbg = h->d_dbg;
             if (frame) { h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu; ph.epoch = h->compact_epoch; }
-            void* args[] = {&view, &geom, &ti_, &vlist, &nvalid, &st, &partials, &tp_, &fuse_normals, &planes, &ctr, &snap, &ph};
+            PeerExchange px = h->px;  // world <= 1 unless gsdf_p2p_connect succeeded
+            if (px.world > 1 && tp.max_iters > 63) { h->err = "sharded tracking over NVLink supports at most 63 iterations"; return GSDF_ERR_INVALID; }
+            if (px.world > 1) px.epoch0 = (++h->p2p_launches) * 64u;  // max_iters <= 63 passes per launch
+            void* args[] = {&view, &geom, &ti_, &vlist, &nvalid, &st, &partials, &tp_, &fuse_normals, &planes, &ctr, &snap, &ph, &px};
             cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_kernel<decltype(V)::value>, dim3(h->track_blocks),
                                                         dim3(kTrackThreads), args, frame ? normals_smem(h) : 0, stream);
             if (e != cudaSuccess) { h->err = std::string("cudaLaunchCooperativeKernel(track_kernel): ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
@@ -418,6 +427,9 @@ void free_all(gsdf_map* h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    for (int r = 0; r < kMaxPeers; ++r)
+        if (h->p2p_peer_base[r] && r != h->cfg.rank) cudaIpcCloseMemHandle(h->p2p_peer_base[r]);
+    cudaFree(h->d_p2p);
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
     cudaFree(h->d_planes); cudaFree(h->d_normals[0]); cudaFree(h->d_normals[1]); cudaFree(h->d_res);
     cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_compact_flags2); cudaFree(h->d_track_partials);
@@ -793,6 +805,11 @@ gsdf_status gsdf_track(gsdf_handle h, float* pose7, int32_t max_iters, float con
     if (s != GSDF_OK) return s;
     CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->d_state, sizeof(FrameState), cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    if (h->p2p_connected) {
+        int perr = 0;
+        CUDA_TRY(h, cudaMemcpy(&perr, h->px.error, sizeof(int), cudaMemcpyDeviceToHost));
+        if (perr) { h->err = "sharded tracker: a peer rank did not reach the NVLink exchange within 0.5 s"; return GSDF_ERR_NCCL; }
+    }
     std::memcpy(pose7, h->h_state->pose7, sizeof(float) * 7);
     *converged = h->h_state->converged;
     if (iters_used) *iters_used = h->h_state->iters;
@@ -928,7 +945,8 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
     }
     const int nbuf = (int)(seq & 1);
     gsdf_status s = GSDF_OK;
-    const bool single = h->cfg.world_size == 1 && !h->profiling;
+    // single cooperative launch for track + fuse: one GPU, or a sharded map whose ranks are connected over NVLink
+    const bool single = (h->cfg.world_size == 1 || h->p2p_connected) && !h->profiling;
     if (single && h->frame_kernel) {
         // ONE cooperative launch per frame: compaction + normals, the Gauss-Newton loop, fusion, result snapshot.
         // Measured slower than the split below (95 vs 73 us per frame at 640x480: with one 512-thread CTA per SM the
@@ -1021,6 +1039,10 @@ gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
     if (c.overflow) {
         h->err = "voxel-block hash full: samples dropped; raise gsdf_config.log2_capacity";
         return GSDF_ERR_CAPACITY;
+    }
+    if (c.peer_error) {
+        h->err = "sharded tracker: a peer rank did not reach the NVLink exchange within 0.5 s";
+        return GSDF_ERR_NCCL;
     }
     return GSDF_OK;
 }
@@ -1208,6 +1230,47 @@ gsdf_status gsdf_profile_read(gsdf_handle h, int32_t kind, int64_t* launches, do
 void* gsdf_stream(gsdf_handle h) { return h ? (void*)h->stream : nullptr; }
 
 int64_t gsdf_launch_count(gsdf_handle h) { return h ? h->launches : 0; }
+
+// ---- NVLink peer exchange: the sharded tracker's all-reduce inside the cooperative launch --------------------------
+static size_t p2p_bytes(int world) { return sizeof(unsigned long long) * 2 * world * kAccStride + 64; }
+
+gsdf_status gsdf_p2p_export(gsdf_handle h, uint8_t handle64[64]) {
+    if (!h || !handle64) return GSDF_ERR_INVALID;
+    if (h->cfg.world_size < 2 || h->cfg.world_size > kMaxPeers) { h->err = "gsdf_p2p_export: world_size must be 2..8"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    if (!h->d_p2p) {
+        CUDA_TRY(h, cudaMalloc(&h->d_p2p, p2p_bytes(h->cfg.world_size)));
+        CUDA_TRY(h, cudaMemset(h->d_p2p, 0, p2p_bytes(h->cfg.world_size)));
+        CUDA_TRY(h, cudaDeviceSynchronize());
+    }
+    cudaIpcMemHandle_t mh;
+    CUDA_TRY(h, cudaIpcGetMemHandle(&mh, h->d_p2p));
+    static_assert(sizeof(mh) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    std::memcpy(handle64, &mh, 64);
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_p2p_connect(gsdf_handle h, const uint8_t* handles /* world_size * 64 bytes, in rank order */) {
+    if (!h || !handles) return GSDF_ERR_INVALID;
+    const int world = h->cfg.world_size, rank = h->cfg.rank;
+    if (world < 2 || world > kMaxPeers || !h->d_p2p) { h->err = "gsdf_p2p_connect: call gsdf_p2p_export on every rank first"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    for (int r = 0; r < world; ++r) {
+        void* base = h->d_p2p;
+        if (r != rank) {
+            cudaIpcMemHandle_t mh;
+            std::memcpy(&mh, handles + 64 * r, 64);
+            CUDA_TRY(h, cudaIpcOpenMemHandle(&base, mh, cudaIpcMemLazyEnablePeerAccess));
+        }
+        h->p2p_peer_base[r] = base;
+        h->px.data[r] = reinterpret_cast<unsigned long long*>(base);
+    }
+    h->px.world = world;
+    h->px.rank = rank;
+    h->px.error = reinterpret_cast<int*>(reinterpret_cast<char*>(h->d_p2p) + sizeof(unsigned long long) * 2 * world * kAccStride);
+    h->p2p_connected = true;
+    return GSDF_OK;
+}
 
 gsdf_status gsdf_comm_unique_id(uint8_t id128[128]) {
     std::string err;

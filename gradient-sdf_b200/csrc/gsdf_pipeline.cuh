@@ -47,10 +47,12 @@ struct ResultSnapshot {
     FrameState st;
     unsigned long long points, updates;  // cumulative
     unsigned int blocks, overflow;
+    unsigned int peer_error, pad;        // sharded tracker: a peer did not show up in the exchange
 };
 
 // executed by one whole CTA (>= 64 threads) after every other CTA's writes are visible
-__device__ __forceinline__ void write_snapshot(const FrameState* st, const Counters* ctr, ResultSnapshot* out) {
+__device__ __forceinline__ void write_snapshot(const FrameState* st, const Counters* ctr, ResultSnapshot* out,
+                                               const int* peer_error = nullptr) {
     __shared__ unsigned long long s_p[kCounterSlots], s_u[kCounterSlots];
     const int t = threadIdx.x;
     if (t < kCounterSlots) {
@@ -65,6 +67,7 @@ __device__ __forceinline__ void write_snapshot(const FrameState* st, const Count
         for (int i = 0; i < kCounterSlots; ++i) { p += s_p[i]; u += s_u[i]; }
         out->points = p; out->updates = u;
         out->blocks = __ldcg(&ctr->blocks); out->overflow = __ldcg(&ctr->overflow);
+        out->peer_error = peer_error ? (unsigned int)__ldcg(peer_error) : 0u;
         __threadfence_system();
     }
 }
@@ -585,13 +588,60 @@ normals_compact_kernel(const float* __restrict__ depth, const float* __restrict_
                  threadIdx.y, smem_dyn);
 }
 
+// Sharded maps: the all-reduce of the 29 sums INSIDE the tracker launch, over NVLink peer memory, with a
+// low-latency (flag-in-data) protocol: every rank owns an exchange buffer [2 parities][world][32] of 64-bit words;
+// after its grid-level reduction CTA 0 stores {pass tag, float bits} for each of its 29 sums into slot `rank` of EVERY
+// peer's buffer (one 8-byte store each, atomic, through the peer mapping) — no fence, no separate flag, so the cost
+// is ONE NVLink traversal.  All CTAs then spin on the words in their OWN memory until each carries the tag of this
+// pass and add the world partials in rank order: identical sums, hence identical poses and stopping decisions, on
+// every rank, with no NCCL launch and no host involvement inside the Gauss-Newton loop.  Parity double-buffering
+// suffices: a rank needs everyone's words of pass k+1 before it may publish pass k+2.
+constexpr int kMaxPeers = 8;
+struct PeerExchange {
+    unsigned long long* data[kMaxPeers];  // data[r]: rank r's exchange buffer (peer-mapped; data[rank] is local)
+    int world, rank;                      // world <= 1: no exchange
+    unsigned int epoch0;                  // pass k of this launch carries the tag epoch0 + k + 1
+    int* error;                           // set to 1 if a peer did not show up in time
+};
+
+__device__ __forceinline__ void peer_allreduce_29(const PeerExchange& px, int k, float* s_tot) {
+    const int par = k & 1;
+    const unsigned long long ep = (unsigned long long)(px.epoch0 + (unsigned)k + 1u) << 32;
+    __syncthreads();  // s_tot holds this rank's sums
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i < px.world * kAccStride; i += blockDim.x) {
+            const int peer = i / kAccStride, term = i - peer * kAccStride;
+            if (term < kAccTerms)
+                *reinterpret_cast<volatile unsigned long long*>(px.data[peer] + (par * px.world + px.rank) * kAccStride + term) =
+                    ep | (unsigned long long)__float_as_uint(s_tot[term]);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < kAccTerms) {
+        const volatile unsigned long long* d = px.data[px.rank] + (size_t)par * px.world * kAccStride + threadIdx.x;
+        const unsigned long long t0 = global_ns();
+        float s = 0.f;
+        for (int r = 0; r < px.world; ++r) {
+            unsigned long long v;
+            unsigned int spins = 0;
+            while (((v = d[r * kAccStride]) >> 32 << 32) != ep) {
+                if ((++spins & 1023u) == 0 && global_ns() - t0 > 500000000ull) { *px.error = 1; break; }  // 0.5 s
+            }
+            s += __uint_as_float((unsigned int)v);
+        }
+        s_tot[threadIdx.x] = s;
+    }
+    __syncthreads();
+}
+
 template <int VARIANT>
 __global__ void __launch_bounds__(kTrackThreads, 2)
 track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr,
              FrameState* st, float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp,
              float* fuse_normals /* null: track only; else 3 planes used by the fusion at the end */,
              const float* __restrict__ planes /* the 11 cached FALS planes */, Counters* ctr,
-             ResultSnapshot* snap /* null, or pinned host memory for the frame result */, FramePhases ph) {
+             ResultSnapshot* snap /* null, or pinned host memory for the frame result */, FramePhases ph,
+             PeerExchange px) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char smem_dyn[];
     __shared__ float s_pose7[8];
@@ -646,6 +696,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
         grid.sync();
         GSDF_STAMP(3);
         grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
+        if (px.world > 1) peer_allreduce_29(px, k, s_tot);
         __syncthreads();
         GSDF_STAMP(4);
         if (threadIdx.x == 0) {
@@ -684,7 +735,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
         __syncthreads();
         if (threadIdx.x == 0) s_last = atomicInc(&ctr->ticket_snap, gridDim.x - 1) == gridDim.x - 1;
         __syncthreads();
-        if (s_last) { __threadfence(); write_snapshot(st, ctr, snap); }
+        if (s_last) { __threadfence(); write_snapshot(st, ctr, snap, px.world > 1 ? px.error : nullptr); }
     }
 }
 

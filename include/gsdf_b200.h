@@ -196,6 +196,14 @@ gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int3
 /* Multi-GPU: rank 0 calls gsdf_comm_unique_id, the 128 bytes are distributed by the caller (any transport),
  * then every rank calls gsdf_comm_init on its handle (cfg.world_size/rank).  Needed only for world_size > 1. */
 gsdf_status gsdf_comm_unique_id(uint8_t id128[128]);
+/* Optional, one node: the sharded tracker's all-reduce inside its cooperative launch, over NVLink peer memory (CUDA
+ * IPC) instead of an NCCL launch per Gauss-Newton pass.  Every rank calls gsdf_p2p_export, the 64-byte handles are
+ * gathered by the caller (any transport) and passed, in rank order, to gsdf_p2p_connect on every rank.  Afterwards
+ * gsdf_track / gsdf_scan_submit run track + fuse as one launch per frame on every rank; all ranks must submit the
+ * same frames in the same order (a rank that does not show up makes its peers fail with GSDF_ERR_NCCL after 0.5 s per
+ * pass instead of hanging).  At most 63 iterations per optimize. */
+gsdf_status gsdf_p2p_export(gsdf_handle h, uint8_t handle64[64]);
+gsdf_status gsdf_p2p_connect(gsdf_handle h, const uint8_t* handles);
 gsdf_status gsdf_comm_init(gsdf_handle h, const uint8_t id128[128]);
 const char* gsdf_version(void);
 

@@ -51,7 +51,30 @@ if rank == 0:
     idt.copy_(torch.tensor(list(buf), dtype=torch.uint8))
 dist.broadcast(idt, 0)
 sharded.comm_init(bytes(idt.cpu().tolist()))
+
+
+def check(got, tag):
+    for a, b in zip(got, ref):
+        assert a.converged == b.converged and a.iters == b.iters, (tag, a.converged, b.converged, a.iters, b.iters)
+        assert np.abs(np.array(a.pose7[:]) - np.array(b.pose7[:])).max() < 5e-4, tag
+    # every rank holds bit-identical poses (same sums in the same order on every rank)
+    mine = torch.tensor([list(r.pose7) for r in got], dtype=torch.float32, device="cuda")
+    allp = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(allp, mine)
+    assert all(torch.equal(allp[0], p) for p in allp), tag
+
+
+got = run(sharded)           # NCCL all-reduce per pass
+check(got, "nccl")
+# NVLink peer exchange inside the cooperative tracker launch
+hd = torch.tensor(list(sharded.p2p_export()), dtype=torch.uint8, device="cuda")
+allh = [torch.zeros_like(hd) for _ in range(world)]
+dist.all_gather(allh, hd)
+sharded.p2p_connect(bytes(torch.cat(allh).cpu().tolist()))
+sharded.reset()
+dist.barrier()
 got = run(sharded)
+check(got, "p2p")
 for a, b in zip(got, ref):
     assert a.converged == b.converged and a.iters == b.iters, (a.converged, b.converged, a.iters, b.iters)
     assert np.abs(np.array(a.pose7[:]) - np.array(b.pose7[:])).max() < 5e-4
