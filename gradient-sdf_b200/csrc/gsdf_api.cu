@@ -614,10 +614,6 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
         g_create_error = "invalid gsdf_config";
         return GSDF_ERR_INVALID;
     }
-    if (c.world_size > 1 && c.variant == GSDF_BASE_SDF) {
-        g_create_error = "base-sdf maps cannot be sharded yet (trilinear corners straddle shard boundaries)";
-        return GSDF_ERR_INVALID;
-    }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0 || c.device < 0 || c.device >= ndev) {

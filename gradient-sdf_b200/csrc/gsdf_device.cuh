@@ -77,6 +77,25 @@ __device__ __forceinline__ int block_owner(unsigned long long key, int world) {
     return (int)((mix64(key) >> 40) % (unsigned long long)world);
 }
 
+// Which voxels a shard keeps (bit 0) and which of them it answers for (bit 1).  grad-sdf: the voxels of its own
+// blocks.  base-sdf: a point's trilinear cell is evaluated on the shard owning the block of its FLOOR corner, so that
+// shard also keeps copies of the low-face voxels (local coordinate 0) of the up-to-7 neighbour blocks at +1 (halo);
+// every shard that keeps a voxel commits every sample of it, so the copies hold the same sums up to atomic order.
+template <int VARIANT>
+__device__ __forceinline__ int shard_keeps(int world, int rank, unsigned long long key, int vx, int vy, int vz) {
+    if (world <= 1 || block_owner(key, world) == rank) return 3;
+    if (VARIANT == 0) return 0;
+    const int fx = (vx & 7) == 0, fy = (vy & 7) == 0, fz = (vz & 7) == 0;
+    if (!(fx | fy | fz)) return 0;
+    const int bx = vx >> kBlockLog2, by = vy >> kBlockLog2, bz = vz >> kBlockLog2;
+#pragma unroll
+    for (int o = 1; o < 8; ++o) {
+        const int ox = o & 1, oy = (o >> 1) & 1, oz = o >> 2;
+        if (ox <= fx && oy <= fy && oz <= fz && block_owner(pack_block(bx - ox, by - oy, bz - oz), world) == rank) return 1;
+    }
+    return 0;
+}
+
 // Table hash: 32-bit multiply/xorshift mixing (the 64-bit finaliser above costs ~4x the integer instructions and
 // sits on the dependent path of every lookup; the hash function is not observable, only the key set is).
 __device__ __forceinline__ uint32_t hash_key(unsigned long long key) {

@@ -143,15 +143,13 @@ fuse_kernel(MapView m, FrameGeom g, Pose pose, const float* __restrict__ depth, 
             const float wgt = sdf_weight(sdf, g.T, g.inv_T);
             if (wgt > 0.f) {
                 const unsigned long long key = block_key_of(vx, vy, vz);
-                if (key != last_key) {
+                const int keep = shard_keeps<VARIANT>(m.world, m.rank, key, vx, vy, vz);  // 3 on a single GPU
+                if (keep && key != last_key) {
                     last_key = key;
-                    if (m.world > 1 && block_owner(key, m.world) != m.rank) slot = -2;  // another rank's block
-                    else {
-                        slot = map_find_or_insert(m, key, ctr);
-                        if (slot < 0) atomicAdd(&ctr->overflow, 1u);
-                    }
+                    slot = map_find_or_insert(m, key, ctr);
+                    if (slot < 0) atomicAdd(&ctr->overflow, 1u);
                 }
-                if (slot >= 0) {
+                if (keep && slot >= 0) {
                     const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
                     const float ws = wgt * sdf_truncate(sdf, g.T);
                     if (VARIANT == 0) {
@@ -160,7 +158,7 @@ fuse_kernel(MapView m, FrameGeom g, Pose pose, const float* __restrict__ depth, 
                     } else {
                         atomicAdd(m.acc2 + addr, make_float2(wgt, ws));  // MapPixelSdfOmp.cpp:183-185
                     }
-                    ++n_upd;
+                    n_upd += keep >> 1;  // halo copies are not counted twice
                 }
             }
         }
@@ -222,6 +220,8 @@ struct Lookup<1> {  // MapPixelSdf.h:107-143 + interp3, MapPixelSdfOmp.cpp:44-11
                                                  unsigned long long& ck, int& cs) {
         const float fx = __fmul_rn(g.vs_inv, px), fy = __fmul_rn(g.vs_inv, py), fz = __fmul_rn(g.vs_inv, pz);
         const int im = (int)floorf(fx), jm = (int)floorf(fy), km = (int)floorf(fz);
+        // sharded map: the cell is evaluated on the rank that owns its floor corner's block (which holds the halo)
+        if (m.world > 1 && block_owner(block_key_of(im, jm, km), m.world) != m.rank) return 0.f;
         float d[8];
         float Wn = 0.f;
         const int rx = (int)roundf(fx) - im, ry = (int)roundf(fy) - jm, rz = (int)roundf(fz) - km;  // nearest corner
@@ -510,7 +510,9 @@ count_kernel(MapView m, unsigned long long* n_voxels, unsigned long long* n_bloc
     unsigned long long cnt = 0, blk = 0;
     for (unsigned int slot = blockIdx.x * warps_per_block + (threadIdx.x >> 5); slot <= m.cap_mask;
          slot += gridDim.x * warps_per_block) {
-        if (m.keys[slot] == kEmptyKey) continue;
+        const unsigned long long key = m.keys[slot];
+        if (key == kEmptyKey) continue;
+        if (m.world > 1 && block_owner(key, m.world) != m.rank) continue;  // a halo block (sharded base-sdf): not reported
         if (lane == 0) ++blk;
         for (int v = lane; v < kBlockVoxels; v += 32) {
             const size_t addr = (size_t)slot * kBlockVoxels + v;
@@ -535,6 +537,7 @@ download_kernel(MapView m, unsigned long long* cursor, long long max_n, int* __r
          slot += gridDim.x * warps_per_block) {
         const unsigned long long key = m.keys[slot];
         if (key == kEmptyKey) continue;
+        if (m.world > 1 && block_owner(key, m.world) != m.rank) continue;  // a halo block (sharded base-sdf): not reported
         int bx, by, bz;
         unpack_block(key, bx, by, bz);
         for (int v = lane; v < kBlockVoxels; v += 32) {

@@ -361,21 +361,19 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                 const float wgt = sdf_weight(sdf, g.T, g.inv_T);
                 if (wgt > 0.f) {                                                       // :110-111
                     const unsigned long long key = block_key_of(vx, vy, vz);
-                    if (key != last_key) {
+                    const int keep = shard_keeps<VARIANT>(m.world, m.rank, key, vx, vy, vz);  // 3 on a single GPU
+                    if (keep && key != last_key) {
                         last_key = key;
-                        if (m.world > 1 && block_owner(key, m.world) != m.rank) slot = -2;  // another rank's block
-                        else {
-                            slot = map_find_or_insert(m, key, ctr);
-                            if (slot < 0) atomicAdd(&ctr->overflow, 1u);
-                        }
+                        slot = map_find_or_insert(m, key, ctr);
+                        if (slot < 0) atomicAdd(&ctr->overflow, 1u);
                     }
-                    if (slot >= 0) {
+                    if (keep && slot >= 0) {
                         has = true;
                         vaddr = (unsigned long long)slot * kBlockVoxels + local_index(vx, vy, vz);
                         const float ws = wgt * sdf_truncate(sdf, g.T);
                         if (VARIANT == 0) { v[0] = ws; v[1] = wgt * Rn0; v[2] = wgt * Rn1; v[3] = wgt * Rn2; v[4] = wgt; }
                         else { v[0] = wgt; v[1] = ws; }
-                        ++n_upd;
+                        n_upd += keep >> 1;  // halo copies are not counted twice
                     }
                 }
             }

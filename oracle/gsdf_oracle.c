@@ -39,6 +39,21 @@ static int voxel_owner(const int32_t* v, int world) {
     return (int)((mix64(key) >> 40) % (uint64_t)world);
 }
 
+/* Which voxels a shard keeps (bit 0) and which of them it answers for (bit 1).  grad-sdf: the voxels of its own blocks.
+ * base-sdf: a point's trilinear cell is evaluated on the shard that owns the block of its FLOOR corner, so that shard
+ * also keeps copies of the low-face voxels (local coordinate 0) of the up-to-7 neighbour blocks at +1 (the halo);
+ * every shard that keeps a voxel receives every sample of it, so the copies hold the same sums. */
+static int shard_keeps(int variant, int world, int rank, const int32_t* v) {
+    if (world <= 1 || voxel_owner(v, world) == rank) return 3;
+    if (variant == 0) return 0;
+    for (int o = 1; o < 8; ++o) {
+        if (((o & 1) && (v[0] & 7)) || ((o & 2) && (v[1] & 7)) || ((o & 4) && (v[2] & 7))) continue;
+        const int32_t nb[3] = {v[0] - 8 * (o & 1), v[1] - 8 * ((o >> 1) & 1), v[2] - 8 * (o >> 2)};
+        if (voxel_owner(nb, world) == rank) return 1;
+    }
+    return 0;
+}
+
 static size_t key_hash(const int32_t* k) {
     /* the reference's hash (hash_map.h:44-52) is not observable; any hash gives the same key set */
     uint64_t a = (uint32_t)k[0], b = (uint32_t)k[1], c = (uint32_t)k[2];
@@ -274,14 +289,14 @@ long long orc_update(orc_ctx* c, const float* depth, const float* R, const float
             for (int i = 0; i < 3; ++i) q[i] = vf[i] - t[i];
             const float sdf = dot3(Rt2, q) - z; /* :107-108 */
             const float wgt = sdf_weight(c, sdf);
-            if (wgt > 0 && c->world > 1 && voxel_owner(vi, c->world) != c->rank) continue; /* another shard's block */
-            if (wgt > 0) {
+            const int keep = wgt > 0 ? shard_keeps(c->variant, c->world, c->rank, vi) : 0;
+            if (keep) {
                 orc_slot* v = tab_get(c, vi); /* :114 */
                 v->weight += wgt;
                 v->dist += (sdf_truncate(c, sdf) - v->dist) * wgt / v->weight; /* :116 */
                 if (c->variant == 0)
                     for (int i = 0; i < 3; ++i) v->g[i] += wgt * Rn[i]; /* :117 */
-                ++updates;
+                updates += keep >> 1; /* halo copies are not counted twice */
             }
         }
         ++points;
@@ -291,13 +306,22 @@ long long orc_update(orc_ctx* c, const float* depth, const float* R, const float
     return updates;
 }
 
-long long orc_voxel_count(const orc_ctx* c) { return (long long)c->count; }
+/* sharded base-sdf: halo copies are neither counted nor downloaded (the union over shards is the unsharded map) */
+static int slot_reported(const orc_ctx* c, const orc_slot* s) {
+    return s->used && (c->world <= 1 || c->variant == 0 || voxel_owner(s->k, c->world) == c->rank);
+}
+long long orc_voxel_count(const orc_ctx* c) {
+    if (c->world <= 1 || c->variant == 0) return (long long)c->count;
+    long long n = 0;
+    for (size_t j = 0; j < c->cap; ++j) n += slot_reported(c, &c->tab[j]);
+    return n;
+}
 
 void orc_download(const orc_ctx* c, int32_t* keys, float* dist, float* weight, float* grad) {
     size_t i = 0;
     for (size_t j = 0; j < c->cap; ++j) {
         const orc_slot* s = &c->tab[j];
-        if (!s->used) continue;
+        if (!slot_reported(c, s)) continue;
         keys[3 * i] = s->k[0]; keys[3 * i + 1] = s->k[1]; keys[3 * i + 2] = s->k[2];
         dist[i] = s->dist; weight[i] = s->weight;
         grad[3 * i] = s->g[0]; grad[3 * i + 1] = s->g[1]; grad[3 * i + 2] = s->g[2];
@@ -331,6 +355,7 @@ static float grad_tsdf(const orc_ctx* c, const float* p, float* grad) { /* MapGr
 static float base_weights(const orc_ctx* c, const float* p) { /* MapPixelSdf.h:118-143 */
     int32_t m[3], k[3];
     for (int i = 0; i < 3; ++i) m[i] = (int32_t)floorf(c->vs_inv * p[i]);
+    if (c->world > 1 && voxel_owner(m, c->world) != c->rank) return 0.f; /* counted on the shard owning the floor corner */
     for (int dz = 0; dz < 2; ++dz) for (int dy = 0; dy < 2; ++dy) for (int dx = 0; dx < 2; ++dx) {
         k[0] = m[0] + dx; k[1] = m[1] + dy; k[2] = m[2] + dz;
         if (!tab_find(c, k)) return 0.f;

@@ -29,7 +29,9 @@ orc_ctx* orc_create(int variant, float voxel_size, float trunc_factor, int w, in
 void orc_destroy(orc_ctx* c);
 void orc_set_zrange(orc_ctx* c, float z_min, float z_max);
 /* Emulation of the multi-GPU sharding protocol (no counterpart in the reference): this context commits only samples
- * whose 8^3 block it owns and its tracker counts only pixels whose nearest voxel it owns; grad-sdf only. */
+ * whose 8^3 block it owns and its tracker counts only pixels whose nearest voxel it owns.  base-sdf: a pixel is
+ * counted on the shard owning the block of its trilinear cell's floor corner, and that shard also keeps halo copies of
+ * the low-face voxels of the +1 neighbour blocks (not counted, not downloaded). */
 void orc_set_shard(orc_ctx* c, int world, int rank);
 int orc_voxel_owner(const int32_t* v3, int world);
 

@@ -41,53 +41,58 @@ def run(sdf):
     return out
 
 
-single = pkg.MapGradPixelSdf(vs, T, nest, log2_capacity=16, device=local)
-ref = run(single)
-sharded = pkg.MapGradPixelSdf(vs, T, nest, log2_capacity=16, device=local, world_size=world, rank=rank)
-idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+def comm_id():
+    idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        buf = (C.c_uint8 * 128)()
+        assert pkg.lib().gsdf_comm_unique_id(buf) == 0
+        idt.copy_(torch.tensor(list(buf), dtype=torch.uint8))
+    dist.broadcast(idt, 0)
+    return bytes(idt.cpu().tolist())
+
+
+def check_variant(cls, tag):
+    single = cls(vs, T, nest, log2_capacity=16, device=local)
+    ref = run(single)
+    assert sum(r.converged for r in ref[1:]) >= len(ref) - 2, tag
+    sharded = cls(vs, T, nest, log2_capacity=16, device=local, world_size=world, rank=rank)
+    sharded.comm_init(comm_id())
+
+    def check(got, how):
+        for a, b in zip(got, ref):
+            assert a.converged == b.converged and a.iters == b.iters, (tag, how, a.converged, b.converged, a.iters, b.iters)
+            assert np.abs(np.array(a.pose7[:]) - np.array(b.pose7[:])).max() < 5e-4, (tag, how)
+        # every rank holds bit-identical poses (same sums in the same order on every rank)
+        mine = torch.tensor([list(r.pose7) for r in got], dtype=torch.float32, device="cuda")
+        allp = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allp, mine)
+        assert all(torch.equal(allp[0], p) for p in allp), (tag, how)
+
+    got = run(sharded)           # NCCL all-reduce per pass
+    check(got, "nccl")
+    # NVLink peer exchange inside the cooperative tracker launch
+    hd = torch.tensor(list(sharded.p2p_export()), dtype=torch.uint8, device="cuda")
+    allh = [torch.zeros_like(hd) for _ in range(world)]
+    dist.all_gather(allh, hd)
+    sharded.p2p_connect(bytes(torch.cat(allh).cpu().tolist()))
+    sharded.reset()
+    dist.barrier()
+    got = run(sharded)
+    check(got, "p2p")
+    upd = torch.tensor([sum(r.updates for r in got)], dtype=torch.int64, device="cuda")
+    dist.all_reduce(upd)
+    assert abs(int(upd) - sum(r.updates for r in ref)) <= 1e-3 * sum(r.updates for r in ref), tag
+    k = sharded.download()[0]
+    assert (pkg.shard_owner(k, world) == rank).all(), tag
+    n = torch.tensor([len(k)], dtype=torch.int64, device="cuda")
+    dist.all_reduce(n)
+    nref = single.voxel_count()[0]
+    assert abs(int(n) - nref) <= 1e-3 * nref, (tag, int(n), nref)
+    dist.barrier()
+    return int(n), nref
+
+
+res = {tag: check_variant(cls, tag) for tag, cls in (("grad", pkg.MapGradPixelSdf), ("base", pkg.MapPixelSdf))}
 if rank == 0:
-    buf = (C.c_uint8 * 128)()
-    assert pkg.lib().gsdf_comm_unique_id(buf) == 0
-    idt.copy_(torch.tensor(list(buf), dtype=torch.uint8))
-dist.broadcast(idt, 0)
-sharded.comm_init(bytes(idt.cpu().tolist()))
-
-
-def check(got, tag):
-    for a, b in zip(got, ref):
-        assert a.converged == b.converged and a.iters == b.iters, (tag, a.converged, b.converged, a.iters, b.iters)
-        assert np.abs(np.array(a.pose7[:]) - np.array(b.pose7[:])).max() < 5e-4, tag
-    # every rank holds bit-identical poses (same sums in the same order on every rank)
-    mine = torch.tensor([list(r.pose7) for r in got], dtype=torch.float32, device="cuda")
-    allp = [torch.zeros_like(mine) for _ in range(world)]
-    dist.all_gather(allp, mine)
-    assert all(torch.equal(allp[0], p) for p in allp), tag
-
-
-got = run(sharded)           # NCCL all-reduce per pass
-check(got, "nccl")
-# NVLink peer exchange inside the cooperative tracker launch
-hd = torch.tensor(list(sharded.p2p_export()), dtype=torch.uint8, device="cuda")
-allh = [torch.zeros_like(hd) for _ in range(world)]
-dist.all_gather(allh, hd)
-sharded.p2p_connect(bytes(torch.cat(allh).cpu().tolist()))
-sharded.reset()
-dist.barrier()
-got = run(sharded)
-check(got, "p2p")
-for a, b in zip(got, ref):
-    assert a.converged == b.converged and a.iters == b.iters, (a.converged, b.converged, a.iters, b.iters)
-    assert np.abs(np.array(a.pose7[:]) - np.array(b.pose7[:])).max() < 5e-4
-upd = torch.tensor([sum(r.updates for r in got)], dtype=torch.int64, device="cuda")
-dist.all_reduce(upd)
-assert abs(int(upd) - sum(r.updates for r in ref)) <= 1e-3 * sum(r.updates for r in ref)
-k = sharded.download()[0]
-assert (pkg.shard_owner(k, world) == rank).all()
-n = torch.tensor([len(k)], dtype=torch.int64, device="cuda")
-dist.all_reduce(n)
-nref = single.voxel_count()[0]
-assert abs(int(n) - nref) <= 1e-3 * nref, (int(n), nref)
-dist.barrier()
-if rank == 0:
-    print("MULTIGPU OK", world, "ranks; voxels", int(n), "vs", nref)
+    print("MULTIGPU OK", world, "ranks; voxels (sharded union, single GPU):", res)
 dist.destroy_process_group()

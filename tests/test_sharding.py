@@ -50,8 +50,9 @@ dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{os.environ['GSDF_
 rank, world = dist.get_rank(), 2
 W, H = 160, 120
 frames, poses, K, _ = synth.make_sequence(100, W, H)
-full = po.Oracle(0, 0.02, 5.0, W, H, K)
-mine = po.Oracle(0, 0.02, 5.0, W, H, K); mine.set_shard(world, rank)
+V = int(os.environ["GSDF_VARIANT"])  # 0 grad-sdf, 1 base-sdf (halo copies of the +1 neighbours' low faces)
+full = po.Oracle(V, 0.02, 5.0, W, H, K)
+mine = po.Oracle(V, 0.02, 5.0, W, H, K); mine.set_shard(world, rank)
 upd_full = upd_mine = 0
 for i in range(3):
     upd_full += full.update(frames[i], poses[i])[2]
@@ -87,13 +88,15 @@ print("rank", rank, "ok")
 '''
 
 
-def test_sharding_protocol_two_gloo_ranks(tmp_path):
+@pytest.mark.parametrize("variant", [0, 1])
+def test_sharding_protocol_two_gloo_ranks(tmp_path, variant):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
     port = _free_port()
     procs = []
     for r in range(2):
-        env = dict(os.environ, RANK=str(r), GSDF_PORT=str(port), GSDF_ROOT=str(ROOT), MASTER_ADDR="127.0.0.1")
+        env = dict(os.environ, RANK=str(r), GSDF_PORT=str(port), GSDF_ROOT=str(ROOT), MASTER_ADDR="127.0.0.1",
+                   GSDF_VARIANT=str(variant))
         procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE,
                                       stderr=subprocess.STDOUT, text=True))
     outs = [p.communicate(timeout=240)[0] for p in procs]
@@ -102,13 +105,15 @@ def test_sharding_protocol_two_gloo_ranks(tmp_path):
 
 
 @pytest.mark.gpu
-def test_two_shards_on_one_device_reproduce_the_unsharded_map(pkg, po, synth):
+@pytest.mark.parametrize("variant", ["grad", "base"])
+def test_two_shards_on_one_device_reproduce_the_unsharded_map(pkg, po, synth, variant):
     W, H = 320, 240
+    cls = pkg.MapGradPixelSdf if variant == "grad" else pkg.MapPixelSdf
     frames, poses, K, _ = synth.make_sequence(100, W, H)
     nest = pkg.NormalEstimator(W, H, K, 11)
     vs, T = np.float32(0.01), np.float32(0.05)
-    full = pkg.MapGradPixelSdf(vs, T, nest, log2_capacity=16)
-    shards = [pkg.MapGradPixelSdf(vs, T, nest, log2_capacity=16, world_size=2, rank=r) for r in range(2)]
+    full = cls(vs, T, nest, log2_capacity=16)
+    shards = [cls(vs, T, nest, log2_capacity=16, world_size=2, rank=r) for r in range(2)]
     for i in range(3):
         pts, upd, _ = full.update(frames[i], poses[i])
         parts = [s.update(frames[i], poses[i]) for s in shards]
@@ -134,8 +139,6 @@ def test_two_shards_on_one_device_reproduce_the_unsharded_map(pkg, po, synth):
     assert np.abs(part[:27] - ref[:27]).max() <= 1e-4 * np.abs(ref[:27]).max()
     with pytest.raises(pkg.GsdfError):                   # collective entry point without a communicator
         shards[0].accumulate(R, pn[:3])
-    with pytest.raises(pkg.GsdfError):                   # base-sdf cannot be sharded yet
-        pkg.MapPixelSdf(vs, T, nest, log2_capacity=12, world_size=2, rank=0)
 
 
 @pytest.mark.gpu
