@@ -35,7 +35,7 @@ EXPORTS = [
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
-    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_p2p_export", "gsdf_p2p_connect", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_scan_run", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_debug_frame_log", "gsdf_p2p_export", "gsdf_p2p_connect", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -116,6 +116,9 @@ def lib() -> C.CDLL:
     L.gsdf_scan_pending.argtypes = [H]
     L.gsdf_accumulate_noalloc.argtypes = [H, _f32p, _f32p, C.c_int32, C.c_void_p]
     L.gsdf_debug_track_timers.argtypes = [H, C.c_void_p, C.POINTER(C.c_int32)]
+    L.gsdf_debug_frame_log.argtypes = [H, C.c_void_p]
+    L.gsdf_scan_run.argtypes = [H, C.POINTER(C.c_void_p), C.c_int64, C.c_int32, C.c_int32, C.POINTER(FrameResult),
+                                C.POINTER(C.c_int64)]
     L.gsdf_trace_enable.argtypes = [H, C.c_int32]
     L.gsdf_trace_dump.restype = C.c_int64
     L.gsdf_trace_dump.argtypes = [H, C.c_char_p, C.c_int64]
@@ -354,6 +357,16 @@ class Sdf:
 
     def scan_pending(self) -> int:
         return int(self.L.gsdf_scan_pending(self.h))
+
+    def scan_run(self, frame_ptrs, on_device: bool, track: bool = True):
+        """The Scan3D frame loop in one call (gsdf_scan_run): frame_ptrs = host or device addresses of the frames, which
+        the caller keeps alive.  Returns the list of FrameResult in frame order."""
+        n = len(frame_ptrs)
+        ptrs = (C.c_void_p * n)(*[int(p) for p in frame_ptrs])
+        res = (FrameResult * n)()
+        done = C.c_int64(0)
+        self._check(self.L.gsdf_scan_run(self.h, ptrs, n, 1 if on_device else 0, 1 if track else 0, res, C.byref(done)))
+        return list(res)
 
     # -- Sdf::tsdf / weights (batched)
     def query(self, pts):

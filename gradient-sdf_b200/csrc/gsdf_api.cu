@@ -52,6 +52,7 @@ struct NcclApi {
 NcclApi g_nccl;
 constexpr int kNcclFloat = 7, kNcclSum = 0;  // ncclFloat32, ncclSum (nccl.h)
 std::string g_create_error;
+constexpr int kFlogFrames = 256;
 constexpr int kRing = 4;  // frames in flight in the submit/collect pipeline
 }  // namespace
 
@@ -79,11 +80,11 @@ struct gsdf_map {
     // device buffers
     float* d_planes = nullptr;        // 11 cached planes
     const float* d_depth = nullptr;   // current frame (ring slot or caller's device buffer)
-    float* d_normals[2] = {nullptr, nullptr};
+    float* d_normals[kRing] = {};     // one set of frame-only buffers (normals, pixel list, count) per frame in flight
     int normals_buf = 0;              // buffer index (normals, vlist, nvalid) of the current frame
     bool normals_valid = false, prepared = false;
-    int2* d_vlist[2] = {nullptr, nullptr};  // compacted valid pixels, double-buffered like the normals
-    int* d_nvalid = nullptr;                // [2] counts of the two lists
+    int2* d_vlist[kRing] = {};              // compacted valid pixels, buffered like the normals
+    int* d_nvalid = nullptr;                // [kRing] counts of the lists
     unsigned int* d_compact_flags = nullptr;  // [nseg] look-back flags {epoch, count} of compact_tiles_kernel
     unsigned int* d_compact_flags2 = nullptr; // [normals tiles] same for normals_compact_kernel
     unsigned int compact_epoch = 0;
@@ -123,8 +124,10 @@ struct gsdf_map {
     bool fuse_in_track = true;  // GSDF_FUSE_IN_TRACK=0: separate fusion launch instead of the tracker launch's tail
     bool merged_side = true;    // GSDF_MERGED_SIDE=0: compaction and normals as two launches
     bool serial = false;        // GSDF_SERIAL=1: frame-only kernels on the main stream instead of the side stream
+    bool shadow_side = true;    // GSDF_SHADOW_SIDE=0: frame-only kernel always at full occupancy
     bool frame_kernel = false;  // GSDF_FRAME_KERNEL=1: whole frame in one cooperative launch (experimental)
     unsigned long long* d_dbg = nullptr;  // tracker phase stamps (gsdf_debug_track_timers)
+    unsigned long long* d_flog = nullptr; // [kFlogFrames][4] kernel spans per pipeline frame (gsdf_debug_frame_log)
     // NVLink peer exchange of the sharded tracker (gsdf_p2p_export / gsdf_p2p_connect)
     void* d_p2p = nullptr;            // [2][world][32] 64-bit {tag, float} words, then one error word
     PeerExchange px{};
@@ -138,6 +141,8 @@ struct gsdf_map {
 };
 
 namespace {
+
+constexpr int kMaxDevices = 64;
 
 #define CUDA_TRY(h, expr)                                                                      \
     do {                                                                                       \
@@ -281,17 +286,23 @@ gsdf_status launch_prepare(gsdf_map* h, const float* depth, int buf, cudaStream_
     return check_launch(h, "compact_tiles_kernel");
 }
 
+// One CTA of the frame-only kernel per SM when it runs in the shadow of the tracker (requested through the dynamic
+// shared-memory size: more than half an SM's 227 KB).  At full occupancy its 600 CTAs are ONE wave that lives as long
+// as the kernel (~10 us) and holds every register file, so the next cooperative tracker launch waits for it; with
+// one 512-thread, 32-register CTA per SM the two 384-thread tracker CTAs always fit beside it.
+constexpr size_t kShadowSmem = 116 * 1024;
+
 // compaction + normals of a frame in one launch (the pipeline's frame-only work)
-gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cudaStream_t stream) {
+gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cudaStream_t stream, bool shadow = false) {
     const int w = h->cfg.width, ht = h->cfg.height, r = h->cfg.normal_window / 2;
     const size_t n = (size_t)w * ht;
     dim3 grid((w + NT_W - 1) / NT_W, (ht + NT_H - 1) / NT_H), block(NT_W, NT_H);
     float* nrm = h->d_normals[buf];
     h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu;
-    normals_compact_kernel<<<grid, block, normals_smem(h), stream>>>(
+    normals_compact_kernel<<<grid, block, shadow ? std::max(kShadowSmem, normals_smem(h)) : normals_smem(h), stream>>>(
         depth, h->d_planes + 2 * n, h->d_planes + 3 * n, h->d_planes + 4 * n, h->d_planes + 5 * n, nrm, nrm + n,
         nrm + 2 * n, w, ht, r, h->geom.z_min, h->geom.z_max, h->d_compact_flags2, h->compact_epoch, h->d_vlist[buf],
-        h->d_nvalid + buf);
+        h->d_nvalid + buf, h->d_flog ? h->d_flog + 4 * (h->seq_submitted % kFlogFrames) : nullptr);
     return check_launch(h, "normals_compact_kernel");
 }
 
@@ -356,14 +367,16 @@ gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream
             FramePhases ph;
             ph.depth = frame; ph.flags = h->d_compact_flags; ph.epoch = 0; ph.nseg = h->nseg_frame;
             ph.r = h->cfg.normal_window / 2; ph.fuse_mode = fuse_mode; ph.dbg = h->d_dbg;
+            ph.flog = (h->d_flog && snap_out) ? h->d_flog + 4 * (h->seq_submitted % kFlogFrames) : nullptr;
             if (frame) { h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu; ph.epoch = h->compact_epoch; }
             PeerExchange px = h->px;  // world <= 1 unless gsdf_p2p_connect succeeded
             if (px.world > 1 && tp.max_iters > 63) { h->err = "sharded tracking over NVLink supports at most 63 iterations"; return GSDF_ERR_INVALID; }
             if (px.world > 1) px.epoch0 = (++h->p2p_launches) * 64u;  // max_iters <= 63 passes per launch
             void* args[] = {&view, &geom, &ti_, &vlist, &nvalid, &st, &partials, &tp_, &fuse_normals, &planes, &ctr, &snap, &ph, &px};
+            // cooperative launch: the driver guarantees that all CTAs are resident together (grid_barrier relies on it)
             cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_kernel<decltype(V)::value>, dim3(h->track_blocks),
                                                         dim3(kTrackThreads), args, frame ? normals_smem(h) : 0, stream);
-            if (e != cudaSuccess) { h->err = std::string("cudaLaunchCooperativeKernel(track_kernel): ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
+            if (e != cudaSuccess) { h->err = std::string("launch of track_kernel: ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
             return check_launch(h, "track_kernel");
         });
     }
@@ -431,9 +444,10 @@ void free_all(gsdf_map* h) {
         if (h->p2p_peer_base[r] && r != h->cfg.rank) cudaIpcCloseMemHandle(h->p2p_peer_base[r]);
     cudaFree(h->d_p2p);
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
-    cudaFree(h->d_planes); cudaFree(h->d_normals[0]); cudaFree(h->d_normals[1]); cudaFree(h->d_res);
-    cudaFree(h->d_vlist[0]); cudaFree(h->d_vlist[1]); cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_compact_flags2); cudaFree(h->d_track_partials);
-    cudaFree(h->d_dbg);
+    cudaFree(h->d_planes); cudaFree(h->d_res);
+    for (int i = 0; i < kRing; ++i) { cudaFree(h->d_normals[i]); cudaFree(h->d_vlist[i]); }
+    cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_compact_flags2); cudaFree(h->d_track_partials);
+    cudaFree(h->d_dbg); cudaFree(h->d_flog);
     cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
     cudaFreeHost(h->h_state);
@@ -478,12 +492,12 @@ gsdf_status create_impl(gsdf_map* h) {
         CUDA_TRY(h, cudaMalloc(&h->view.acc2, sizeof(float2) * h->cap * kBlockVoxels));
     }
     CUDA_TRY(h, cudaMalloc(&h->d_planes, sizeof(float) * n * 11));
-    CUDA_TRY(h, cudaMalloc(&h->d_normals[0], sizeof(float) * n * 3));
-    CUDA_TRY(h, cudaMalloc(&h->d_normals[1], sizeof(float) * n * 3));
-    CUDA_TRY(h, cudaMalloc(&h->d_vlist[0], sizeof(int2) * n));
-    CUDA_TRY(h, cudaMalloc(&h->d_vlist[1], sizeof(int2) * n));
-    CUDA_TRY(h, cudaMalloc(&h->d_nvalid, sizeof(int) * 2));
-    CUDA_TRY(h, cudaMemset(h->d_nvalid, 0, sizeof(int) * 2));
+    for (int i = 0; i < kRing; ++i) {
+        CUDA_TRY(h, cudaMalloc(&h->d_normals[i], sizeof(float) * n * 3));
+        CUDA_TRY(h, cudaMalloc(&h->d_vlist[i], sizeof(int2) * n));
+    }
+    CUDA_TRY(h, cudaMalloc(&h->d_nvalid, sizeof(int) * kRing));
+    CUDA_TRY(h, cudaMemset(h->d_nvalid, 0, sizeof(int) * kRing));
     const int ntiles = ((c.width + kTileW - 1) / kTileW) * ((c.height + kTileH - 1) / kTileH);
     h->nseg = (ntiles + kTilesPerBlock - 1) / kTilesPerBlock;
     h->nseg_frame = (ntiles + kTrackWarps * kTilesPerWarp - 1) / (kTrackWarps * kTilesPerWarp);
@@ -527,10 +541,10 @@ gsdf_status create_impl(gsdf_map* h) {
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
     }
     CUDA_TRY(h, cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
-    if (normals_smem(h) > 48 * 1024) {
+    if (normals_smem(h) > 48 * 1024)
         CUDA_TRY(h, cudaFuncSetAttribute(normals_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
-        CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
-    }
+    CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)std::max(kShadowSmem, normals_smem(h))));
     build_normal_cache(c, h->h_planes);
     CUDA_TRY(h, cudaMemcpyAsync(h->d_planes, h->h_planes.data(), sizeof(float) * n * 11, cudaMemcpyHostToDevice, h->stream));
     return clear_map(h);
@@ -616,13 +630,14 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
-    if (e != cudaSuccess || ndev == 0 || c.device < 0 || c.device >= ndev) {
+    if (e != cudaSuccess || ndev == 0 || c.device < 0 || c.device >= ndev || c.device >= kMaxDevices) {
         g_create_error = std::string("no usable CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e);
         return GSDF_ERR_CUDA;
     }
     gsdf_map* h = new gsdf_map();
     h->cfg = c;
     if (const char* e = std::getenv("GSDF_FRAME_KERNEL")) h->frame_kernel = e[0] == '1';
+    if (const char* e = std::getenv("GSDF_SHADOW_SIDE")) h->shadow_side = e[0] == '1';
     if (const char* e = std::getenv("GSDF_SERIAL")) h->serial = e[0] == '1';
     if (const char* e = std::getenv("GSDF_MERGED_SIDE")) h->merged_side = e[0] == '1';
     if (const char* e = std::getenv("GSDF_FUSE_IN_TRACK")) h->fuse_in_track = e[0] == '1';
@@ -633,8 +648,6 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     h->geom.inv_T = (float)(1. / (double)c.truncation);   // Sdf.h:105
     h->geom.z_min = c.z_min; h->geom.z_max = c.z_max;
     h->geom.factor = (int)std::floor(c.truncation / c.voxel_size);  // MapGradPixelSdfOmp.cpp:78
-    h->geom.fuse_kpw = 2;
-    if (const char* e = std::getenv("GSDF_FUSE_KPW")) h->geom.fuse_kpw = std::max(1, std::atoi(e));
     gsdf_status s = create_impl(h);
     if (s != GSDF_OK) { g_create_error = h->err; free_all(h); return s; }
     *out = h;
@@ -939,7 +952,7 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
         CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, sl.ev_up, 0));
         frame = sl.d_depth;
     }
-    const int nbuf = (int)(seq & 1);
+    const int nbuf = (int)(seq % kRing);
     gsdf_status s = GSDF_OK;
     // single cooperative launch for track + fuse: one GPU, or a sharded map whose ranks are connected over NVLink
     const bool single = (h->cfg.world_size == 1 || h->p2p_connected) && !h->profiling;
@@ -954,19 +967,21 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
         if (s != GSDF_OK) return s;
     } else {
         // Pixel compaction and normals depend only on the frame, not on the map or the pose: they run on the side
-        // stream (overlapping the previous frame's main-stream work when several frames are in flight); their
-        // buffers (index seq & 1) were last read by the tracker/fusion of frame seq-2.
+        // stream, up to kRing - 1 frames ahead of the main stream (which has the higher priority: the side kernels
+        // fill the SMs the tracker leaves idle instead of competing with it for the moment a frame ends); their
+        // buffers (index seq % kRing) were last read by the tracker/fusion of frame seq - kRing, collected long ago.
         // per-kernel profiling runs everything on one stream so that the event brackets do not overlap
         const bool serial = h->serial || h->profiling;
         cudaStream_t side = serial ? h->stream : h->stream_n;
-        if (seq >= 2 && !serial) CUDA_TRY(h, cudaStreamWaitEvent(side, h->ring[(seq - 2) % kRing].ev_fused, 0));
+        if (seq >= kRing && !serial) CUDA_TRY(h, cudaStreamWaitEvent(side, h->ring[seq % kRing].ev_fused, 0));
         trace_mark(h, "side:begin", side);
         if (h->profiling || !h->merged_side) {  // separate launches (also keeps the per-kernel brackets meaningful)
             s = launch_prepare(h, frame, nbuf, side);
             if (s != GSDF_OK) return s;
             s = launch_normals(h, frame, nbuf, side, true);
         } else {
-            s = launch_normals_compact(h, frame, nbuf, side);
+            // frames already in flight: this one's frame-only work is not on the critical path, keep its footprint small
+            s = launch_normals_compact(h, frame, nbuf, side, h->shadow_side && h->seq_submitted > h->seq_collected);
         }
         if (s != GSDF_OK) return s;
         trace_mark(h, "side:normals", side);
@@ -1036,6 +1051,10 @@ gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
         h->err = "voxel-block hash full: samples dropped; raise gsdf_config.log2_capacity";
         return GSDF_ERR_CAPACITY;
     }
+    if (c.barrier_timeout) {
+        h->err = "tracker grid barrier timed out: its CTAs were not all resident (another persistent kernel on this device?)";
+        return GSDF_ERR_CUDA;
+    }
     if (c.peer_error) {
         h->err = "sharded tracker: a peer rank did not reach the NVLink exchange within 0.5 s";
         return GSDF_ERR_NCCL;
@@ -1044,6 +1063,34 @@ gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
 }
 
 int32_t gsdf_scan_pending(gsdf_handle h) { return h ? (int32_t)(h->seq_submitted - h->seq_collected) : 0; }
+
+gsdf_status gsdf_scan_run(gsdf_handle h, const float* const* frames, int64_t n, int32_t on_device, int32_t mode,
+                          gsdf_frame_result* results, int64_t* n_done) {
+    if (!h || !frames || !results || n < 0) return GSDF_ERR_INVALID;
+    if (n_done) *n_done = 0;
+    if (h->seq_submitted != h->seq_collected) { h->err = "gsdf_scan_run: frames are pending, collect them first"; return GSDF_ERR_INVALID; }
+    int64_t submitted = 0, collected = 0;
+    gsdf_status s = GSDF_OK;
+    while (collected < n) {
+        while (submitted < n && submitted - collected < kRing) {
+            s = gsdf_scan_submit(h, on_device ? nullptr : frames[submitted], on_device ? frames[submitted] : nullptr, mode);
+            if (s != GSDF_OK) break;
+            ++submitted;
+        }
+        if (s != GSDF_OK) break;
+        s = gsdf_scan_collect(h, results + collected);
+        if (s != GSDF_OK) break;
+        ++collected;
+        if (n_done) *n_done = collected;
+    }
+    if (s != GSDF_OK) {  // drain what is still in flight so that the handle stays usable; keep the first error
+        const std::string first = h->err;
+        gsdf_frame_result scratch;
+        while (h->seq_collected < h->seq_submitted) gsdf_scan_collect(h, &scratch);
+        h->err = first;
+    }
+    return s;
+}
 
 // ---- pose algebra ---------------------------------------------------------------------------------------------
 void gsdf_pose_matrix(const float* pose7, float* R9, float* pose7_normalised) {
@@ -1096,7 +1143,6 @@ gsdf_status gsdf_synchronize(gsdf_handle h) {
 static __device__ __align__(256) float g_noalloc_scratch[kStaticScratchFloats];
 
 namespace {
-constexpr int kMaxDevices = 64;
 float* g_noalloc_ptr[kMaxDevices] = {};
 std::mutex g_noalloc_mutex;
 }  // namespace
@@ -1150,7 +1196,7 @@ gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int3
     if (!h || !n_ctas) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
     *n_ctas = h->track_blocks;
-    const size_t bytes = sizeof(unsigned long long) * h->track_blocks * 24;
+    const size_t bytes = sizeof(unsigned long long) * h->track_blocks * 28;
     if (!h->d_dbg) {
         CUDA_TRY(h, cudaMalloc(&h->d_dbg, bytes));
         CUDA_TRY(h, cudaMemset(h->d_dbg, 0, bytes));
@@ -1161,6 +1207,26 @@ gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int3
         CUDA_TRY(h, cudaFree(h->d_dbg));
         h->d_dbg = nullptr;
     }
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_debug_frame_log(gsdf_handle h, unsigned long long* out /* null: arm; else kFlogFrames * 4 words */) {
+    if (!h) return GSDF_ERR_INVALID;
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    const size_t bytes = sizeof(unsigned long long) * 4 * kFlogFrames;
+    if (!out) {
+        if (!h->d_flog) CUDA_TRY(h, cudaMalloc(&h->d_flog, bytes));
+        std::vector<unsigned long long> init(4 * kFlogFrames);
+        for (int i = 0; i < kFlogFrames; ++i) { init[4 * i] = init[4 * i + 2] = ~0ull; init[4 * i + 1] = init[4 * i + 3] = 0; }
+        CUDA_TRY(h, cudaDeviceSynchronize());
+        CUDA_TRY(h, cudaMemcpy(h->d_flog, init.data(), bytes, cudaMemcpyHostToDevice));
+        return GSDF_OK;
+    }
+    if (!h->d_flog) { h->err = "gsdf_debug_frame_log: not armed"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaDeviceSynchronize());
+    CUDA_TRY(h, cudaMemcpy(out, h->d_flog, bytes, cudaMemcpyDeviceToHost));
+    CUDA_TRY(h, cudaFree(h->d_flog));
+    h->d_flog = nullptr;
     return GSDF_OK;
 }
 

@@ -45,6 +45,8 @@ struct Counters {
     unsigned int overflow;        // find-or-insert gave up: GSDF_ERR_CAPACITY
     unsigned int ticket;          // last-block-done ticket of the reduction
     unsigned int ticket_snap;     // last-block-done ticket of the frame-result snapshot
+    unsigned int barrier;         // arrival counter of track_kernel's grid barrier (0 between launches)
+    unsigned int barrier_timeout; // a grid barrier gave up waiting: GSDF_ERR_CUDA
     struct Slot {
         unsigned long long points;   // pixels that passed every validity test
         unsigned long long updates;  // committed (pixel,k) samples

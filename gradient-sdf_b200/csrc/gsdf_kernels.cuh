@@ -16,7 +16,6 @@ struct FrameGeom {
     int w, h;
     float vs, vs_inv, T, inv_T, z_min, z_max;
     int factor;  // floor(T / vs), MapGradPixelSdfOmp.cpp:78
-    int fuse_kpw;  // ray samples per fusion work item (tuning knob, see fuse_work)
 };
 
 struct Pose {

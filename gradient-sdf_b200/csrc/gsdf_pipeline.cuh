@@ -27,6 +27,16 @@ namespace gsdf {
 
 namespace cg = cooperative_groups;
 
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// debug frame log (gsdf_debug_frame_log): {first CTA entry, last CTA exit} of a kernel, into log[0], log[1]
+__device__ __forceinline__ void flog_enter(unsigned long long* log) { if (log) atomicMin(log, global_ns()); }
+__device__ __forceinline__ void flog_exit(unsigned long long* log) { if (log) atomicMax(log + 1, global_ns()); }
+
+
 // Device-resident tracker / frame state (RigidOptimizer::pose_ and friends live here between calls).
 struct FrameState {
     float pose7[7];             // tx ty tz qx qy qz qw, unit quaternion
@@ -47,28 +57,32 @@ struct ResultSnapshot {
     FrameState st;
     unsigned long long points, updates;  // cumulative
     unsigned int blocks, overflow;
-    unsigned int peer_error, pad;        // sharded tracker: a peer did not show up in the exchange
+    unsigned int peer_error;             // sharded tracker: a peer did not show up in the exchange
+    unsigned int barrier_timeout;        // the tracker's grid barrier gave up (its CTAs were not all resident)
 };
 
-// executed by one whole CTA (>= 64 threads) after every other CTA's writes are visible
+// executed by one whole CTA (>= 96 threads) after every other CTA's writes are visible
 __device__ __forceinline__ void write_snapshot(const FrameState* st, const Counters* ctr, ResultSnapshot* out,
                                                const int* peer_error = nullptr) {
-    __shared__ unsigned long long s_p[kCounterSlots], s_u[kCounterSlots];
+    // (the host reads the snapshot only after the event that follows this launch: no system-scope fence is needed)
+    static_assert(kCounterSlots == 64, "two slots per lane");
     const int t = threadIdx.x;
-    if (t < kCounterSlots) {
-        s_p[t] = __ldcg(&ctr->slot[t].points);
-        s_u[t] = __ldcg(&ctr->slot[t].updates);
-    }
     constexpr int kWords = (int)(sizeof(FrameState) / sizeof(int));
-    if (t < kWords) reinterpret_cast<int*>(&out->st)[t] = __ldcg(reinterpret_cast<const int*>(st) + t);
-    __syncthreads();
-    if (t == 0) {
-        unsigned long long p = 0, u = 0;
-        for (int i = 0; i < kCounterSlots; ++i) { p += s_p[i]; u += s_u[i]; }
-        out->points = p; out->updates = u;
-        out->blocks = __ldcg(&ctr->blocks); out->overflow = __ldcg(&ctr->overflow);
-        out->peer_error = peer_error ? (unsigned int)__ldcg(peer_error) : 0u;
-        __threadfence_system();
+    if (t >= 32 && t < 32 + kWords) reinterpret_cast<int*>(&out->st)[t - 32] = __ldcg(reinterpret_cast<const int*>(st) + t - 32);
+    if (t < 32) {
+        unsigned long long p = __ldcg(&ctr->slot[t].points) + __ldcg(&ctr->slot[t + 32].points);
+        unsigned long long u = __ldcg(&ctr->slot[t].updates) + __ldcg(&ctr->slot[t + 32].updates);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            p += __shfl_xor_sync(0xffffffffu, p, off);
+            u += __shfl_xor_sync(0xffffffffu, u, off);
+        }
+        if (t == 0) {
+            out->points = p; out->updates = u;
+            out->blocks = __ldcg(&ctr->blocks); out->overflow = __ldcg(&ctr->overflow);
+            out->peer_error = peer_error ? (unsigned int)__ldcg(peer_error) : 0u;
+            out->barrier_timeout = __ldcg(&ctr->barrier_timeout);
+        }
     }
 }
 
@@ -186,7 +200,7 @@ __device__ __forceinline__ void track_pixel(const MapView& m, const FrameGeom& g
     }
 }
 
-constexpr int kTrackThreads = 512;
+constexpr int kTrackThreads = 384;
 constexpr int kTrackWarps = kTrackThreads / 32;
 
 struct TrackParams {
@@ -288,14 +302,10 @@ __device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool h
     }
 }
 
-// Work decomposition: a work item is (chunk of 32 consecutive list entries, group of g.fuse_kpw ray samples) and
-// belongs to one warp; the 2*factor+1 samples of a pixel are therefore spread over several warps (of the same
-// CTA, so the per-pixel planes come from L1) instead of forming one long dependent instruction stream per lane —
-// with ~2 k warps of 11 serial samples each the kernel was latency-bound at 25 us; with ~6x more, shorter warps the
-// SMs have something to switch to.
-
-// The fusion work of one CTA: warps stride over the (chunk, sample group) items.  Called by fuse_list_kernel and by
-// the tail of track_kernel (fused track+fuse launch).
+// Work decomposition: the unit of work is (chunk of 32 consecutive list entries, ONE ray sample); the 2*factor+1
+// samples of a pixel are therefore spread over several warps instead of forming one long dependent instruction
+// stream per lane (with ~2 k warps of 11 serial samples each the kernel was latency-bound at 25 us), and every warp
+// gets the same number of units (+-1).  Called by fuse_list_kernel and by the tail of track_kernel (fused launch).
 // COHERENT: the list and the normals were produced earlier in the SAME launch (frame kernel) -> L2 loads, not the
 // non-coherent read-only path.
 template <int VARIANT, bool COHERENT>
@@ -308,13 +318,19 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
     const float* R = pose.R;
     const int lane = threadIdx.x & 31;
     const int S = 2 * g.factor + 1;
-    const int kpw = g.fuse_kpw;
-    const int kgroups = (S + kpw - 1) / kpw;
+    // Work unit = (32-pixel chunk of the list, one ray sample); every warp takes an equal, CONTIGUOUS range of the
+    // chunk-major unit sequence (sizes differ by at most one unit; before, whole (chunk, sample-group) items were
+    // dealt round-robin and a warp had 3 or 4 of them: the 4-item CTAs finished 6 us after the others), so a warp
+    // loads the pixel data of only one or two chunks.  Warp ranges are interleaved over the CTAs (warp-major).
     const int nchunks = (n_valid + 31) >> 5;
-    const int items = nchunks * kgroups;
+    const long long units = (long long)nchunks * S;
     const int warps_total = (gridDim.x * blockDim.x) >> 5;
-    for (int it = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; it < items; it += warps_total) {
-        const int chunk = it / kgroups, kg = it - chunk * kgroups;
+    const int wid = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    const int u1 = (int)(units * (wid + 1) / warps_total);
+    for (int u = (int)(units * wid / warps_total); u < u1;) {
+        const int chunk = u / S, k_first = u - chunk * S;
+        const int k_end = min(S, k_first + (u1 - u));  // exclusive
+        u += k_end - k_first;
         const int j = chunk * 32 + lane;
         bool valid = j < n_valid;
         float z = 0.f, Rxy0 = 0.f, Rxy1 = 0.f, Rxy2 = 0.f, Rn0 = 0.f, Rn1 = 0.f, Rn2 = 0.f;
@@ -339,12 +355,10 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                 Rn2 = dot3_rn(R[6], R[7], R[8], a, b, c);
             }
         }
-        n_pts += (valid && kg == 0) ? 1u : 0u;
+        n_pts += (valid && k_first == 0) ? 1u : 0u;
         unsigned long long last_key = kEmptyKey;
         int slot = -1;
-        const int k_lo = kg * kpw - g.factor;
-        const int k_hi = min(k_lo + kpw - 1, g.factor);
-        for (int kk = k_lo; kk <= k_hi; ++kk) {                                        // :103
+        for (int kk = k_first - g.factor; kk < k_end - g.factor; ++kk) {               // :103
             bool has = false;
             unsigned long long vaddr = 0;
             float v[VARIANT == 0 ? 5 : 2];
@@ -530,29 +544,28 @@ struct FramePhases {
     int nseg;                // segments of kTrackWarps * kTilesPerWarp tiles
     int r;                   // normal window radius
     int fuse_mode;           // 0 = never, 1 = always (setup / ground-truth pose), 2 = iff the optimisation converged
-    unsigned long long* dbg; // null, or [gridDim.x][4 passes][6] %globaltimer stamps of the tracker's phases
+    unsigned long long* flog; // null, or this frame's entry of the debug frame log (main kernel: words 2, 3)
+    unsigned long long* dbg; // null, or [gridDim.x][4 passes][6] + [gridDim.x][4] %globaltimer stamps of the tracker's phases
 };
 
-__device__ __forceinline__ unsigned long long global_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
 #define GSDF_STAMP(i) do { if (ph.dbg && threadIdx.x == 0 && k < 4) ph.dbg[((size_t)blockIdx.x * 4 + k) * 6 + (i)] = global_ns(); } while (0)
+// whole-launch stamps, after the per-pass ones: [gridDim.x][4] = entry, Gauss-Newton loop left, fusion done, exit
+#define GSDF_STAMPX(i) do { if (ph.dbg && threadIdx.x == 0) ph.dbg[(size_t)gridDim.x * 24 + (size_t)blockIdx.x * 4 + (i)] = global_ns(); } while (0)
 
 // Frame-only work of the pipeline in ONE launch: each CTA compacts the z-valid pixels of its 32x16 tile (16 warps <->
 // its sixteen 8x4 sub-tiles, chained look-back over the CTAs for the exclusive prefix) and then computes the tile's
 // normals.  List order: 32x16 tiles row-major, 8x4 sub-tiles row-major inside, pixels row-major inside.
-__global__ void __launch_bounds__(NT_W* NT_H)
+__global__ void __launch_bounds__(NT_W* NT_H, 4)  // <= 32 registers: one CTA fits beside the resident tracker CTAs
 normals_compact_kernel(const float* __restrict__ depth, const float* __restrict__ x0n, const float* __restrict__ y0n,
                        const float* __restrict__ nsi, const float* __restrict__ Q, float* __restrict__ nx,
                        float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r, float z_min, float z_max,
                        unsigned int* __restrict__ flags, unsigned int epoch, int2* __restrict__ vlist,
-                       int* __restrict__ n_valid_out) {
+                       int* __restrict__ n_valid_out, unsigned long long* flog) {
     extern __shared__ __align__(16) unsigned char smem_dyn[];
     __shared__ int s_warp[NT_W * NT_H / 32];
     __shared__ int s_base;
     const int tid = threadIdx.y * NT_W + threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) flog_enter(flog);
     const int cta = blockIdx.y * gridDim.x + blockIdx.x, ncta = gridDim.x * gridDim.y;
     const int px = blockIdx.x * NT_W + (warp & 3) * kTileW + (lane & 7);
     const int py = blockIdx.y * NT_H + (warp >> 2) * kTileH + (lane >> 3);
@@ -581,9 +594,34 @@ normals_compact_kernel(const float* __restrict__ depth, const float* __restrict_
             vlist[s_base + before + __popc(mask & ((1u << lane) - 1))] = make_int2((py << 16) | px, __float_as_int(z));
         if (cta == ncta - 1 && tid == 0) *n_valid_out = s_base + total;
     }
-    if (total == 0) return;  // no valid pixel in the tile: fusion never reads its normals
+    if (total == 0) { if (tid == 0) flog_exit(flog); return; }  // no valid pixel in the tile: fusion never reads its normals
     normals_tile(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
                  threadIdx.y, smem_dyn);
+    if (tid == 0) flog_exit(flog);
+}
+
+// Grid-wide barrier of the persistent tracker (cooperative launch: all CTAs are resident).  An arrival counter
+// instead of cooperative_groups' grid.sync(): barrier number b is passed once the counter reaches (b + 1) * gridDim.x,
+// the last CTA to leave the kernel resets it, and a wait that exceeds 2 s sets barrier_timeout (reported by
+// gsdf_scan_collect as an error) instead of hanging the device.
+__device__ __forceinline__ void grid_barrier(Counters* ctr, unsigned int target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(&ctr->barrier, 1u);
+        unsigned int seen, spins = 0;
+        unsigned long long t0 = 0;
+        for (;;) {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(&ctr->barrier) : "memory");
+            if (seen >= target) break;
+            if ((++spins & 4095u) == 0) {
+                const unsigned long long now = global_ns();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 2000000000ull) { ctr->barrier_timeout = 1u; break; }
+            }
+        }
+    }
+    __syncthreads();
 }
 
 // Sharded maps: the all-reduce of the 29 sums INSIDE the tracker launch, over NVLink peer memory, with a
@@ -633,21 +671,23 @@ __device__ __forceinline__ void peer_allreduce_29(const PeerExchange& px, int k,
 }
 
 template <int VARIANT>
-__global__ void __launch_bounds__(kTrackThreads, 2)
+__global__ void __launch_bounds__(512, 2)
 track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr,
              FrameState* st, float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp,
              float* fuse_normals /* null: track only; else 3 planes used by the fusion at the end */,
              const float* __restrict__ planes /* the 11 cached FALS planes */, Counters* ctr,
              ResultSnapshot* snap /* null, or pinned host memory for the frame result */, FramePhases ph,
              PeerExchange px) {
-    cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char smem_dyn[];
+    unsigned int barriers = 0;  // grid barriers passed so far in this launch
     __shared__ float s_pose7[8];
     __shared__ Pose s_pose;
     __shared__ float s_tot[kAccStride];
     __shared__ float s_warp[kTrackWarps][kAccStride];
     __shared__ int s_conv;
-    if (ph.depth != nullptr) {
+    GSDF_STAMPX(0);
+    if (threadIdx.x == 0 && ph.flog) flog_enter(ph.flog + 2);
+    if constexpr (kTrackThreads == NT_W * NT_H) if (ph.depth != nullptr) {
         // compaction (look-back over segments) and normals (tiles) both depend only on the depth frame
         __shared__ int s_cw[kTrackWarps];
         __shared__ int s_cb;
@@ -663,7 +703,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
                          threadIdx.x & (NT_W - 1), threadIdx.x / NT_W, smem_dyn);
             __syncthreads();
         }
-        grid.sync();
+        grid_barrier(ctr, ++barriers * gridDim.x);
     }
     if (threadIdx.x < 7) s_pose7[threadIdx.x] = st->pose7[threadIdx.x];
     __syncthreads();
@@ -673,17 +713,27 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
     }
     __syncthreads();
     const int n_valid = __ldcg(n_valid_ptr);
-    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+    // pixel j of the list -> warp-sized chunk j/32 -> CTA (chunk % grid), warp (chunk / grid): a frame with fewer valid
+    // pixels than resident threads (the usual case: ~90 k of 151 k) is spread over ALL SMs instead of filling the
+    // first CTAs completely and leaving the rest idle (the slowest CTA sets the length of every pass)
+    const int nthreads = gridDim.x * blockDim.x;
+    const int gtid = (((threadIdx.x >> 5) * gridDim.x + blockIdx.x) << 5) | (threadIdx.x & 31);
     int converged = 0, k = 0;
     float valid_sum = 0.f;
     unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
     int cs = -1;
+    // the thread's first list entry stays in registers over the passes (with fewer valid pixels than resident threads
+    // it is the only one): one dependent L2 round trip less in every pass after the first
+    const bool has0 = gtid < n_valid;
+    int2 e0 = make_int2(0, 0);
+    if (has0) e0 = __ldcg(vlist + gtid);
     for (k = 0; k < tp.max_iters; ++k) {
         float acc[kAccTerms];
 #pragma unroll
         for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
         GSDF_STAMP(0);
-        for (int j = gtid; j < n_valid; j += nthreads) {
+        if (has0) track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e0.x, __int_as_float(e0.y), acc, ck, cs);
+        for (int j = gtid + nthreads; j < n_valid; j += nthreads) {
             const int2 e = __ldcg(vlist + j);
             track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
         }
@@ -691,7 +741,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
         float* mine = partials + ((size_t)(k & 1) * gridDim.x + blockIdx.x) * kAccStride;
         block_reduce_29<kTrackWarps>(acc, s_warp, mine);
         GSDF_STAMP(2);
-        grid.sync();
+        grid_barrier(ctr, ++barriers * gridDim.x);
         GSDF_STAMP(3);
         grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
         if (px.world > 1) peer_allreduce_29(px, k, s_tot);
@@ -707,6 +757,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
         GSDF_STAMP(5);
         if (s_conv) { converged = 1; break; }
     }
+    GSDF_STAMPX(1);
     if (blockIdx.x == 0) {
         if (threadIdx.x < 7) st->pose7[threadIdx.x] = s_pose7[threadIdx.x];
         if (threadIdx.x < kAccTerms) st->sums[threadIdx.x] = s_tot[threadIdx.x];
@@ -727,14 +778,21 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
                                  planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd);
         fuse_stats_flush(ctr, n_pts, n_upd);
     }
-    if (snap != nullptr) {  // the last CTA to get here publishes the frame result
+    GSDF_STAMPX(2);
+    {   // the last CTA to get here re-arms the grid barrier and publishes the frame result
         __shared__ bool s_last;
         __threadfence();
         __syncthreads();
         if (threadIdx.x == 0) s_last = atomicInc(&ctr->ticket_snap, gridDim.x - 1) == gridDim.x - 1;
         __syncthreads();
-        if (s_last) { __threadfence(); write_snapshot(st, ctr, snap, px.world > 1 ? px.error : nullptr); }
+        if (s_last) {
+            __threadfence();
+            if (threadIdx.x == 0) ctr->barrier = 0u;
+            if (snap != nullptr) write_snapshot(st, ctr, snap, px.world > 1 ? px.error : nullptr);
+        }
     }
+    GSDF_STAMPX(3);
+    if (threadIdx.x == 0 && ph.flog) flog_exit(ph.flog + 2);
 }
 
 // Per-iteration variant (sharded maps): sums of this rank's pixels -> out29 (last-block-done), the caller

@@ -162,6 +162,12 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
 /* Wait for the oldest pending frame and return its result. */
 gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out);
 int32_t gsdf_scan_pending(gsdf_handle h);
+/* The Scan3D frame loop (main_scan_3d.cpp:208-266) for n frames in one call: frame i is submitted as soon as fewer
+ * than 4 are pending and results[i] is filled in frame order (the pipeline must be empty on entry and is empty on
+ * return).  frames[i] are host pointers (on_device = 0) or device pointers (on_device = 1); mode as gsdf_scan_submit.
+ * Stops at the first error (results of the frames collected so far are valid, *n_done says how many). */
+gsdf_status gsdf_scan_run(gsdf_handle h, const float* const* frames, int64_t n, int32_t on_device, int32_t mode,
+                          gsdf_frame_result* results, int64_t* n_done);
 
 /* -- pose algebra used by the tracker (Sophus::SE3f semantics: so3.hpp:297-303,325-339,356-366,583-619,
  *    se3.hpp:761-782; Eigen toRotationMatrix), exported so callers without Sophus get identical poses -------- */
@@ -193,6 +199,11 @@ gsdf_status gsdf_trace_enable(gsdf_handle h, int32_t on);
 int64_t gsdf_trace_dump(gsdf_handle h, char* buf, int64_t size);
 /* Debug aid: per-CTA %globaltimer stamps of the tracker's phases (see gsdf_api.cu); not for production use. */
 gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int32_t* n_ctas);
+/* Debug aid, no reference counterpart: device-clock spans of the pipeline's two kernels per submitted frame.
+ * out == NULL arms the log; otherwise out receives 256 x {frame-only kernel first entry, last exit, track+fuse kernel
+ * first entry, last exit} in ns of %globaltimer (entry = ~0 / exit = 0 where nothing ran), frame seq modulo 256, and
+ * the log is released. */
+gsdf_status gsdf_debug_frame_log(gsdf_handle h, unsigned long long* out);
 /* Multi-GPU: rank 0 calls gsdf_comm_unique_id, the 128 bytes are distributed by the caller (any transport),
  * then every rank calls gsdf_comm_init on its handle (cfg.world_size/rank).  Needed only for world_size > 1. */
 gsdf_status gsdf_comm_unique_id(uint8_t id128[128]);

@@ -28,9 +28,9 @@ n = C.c_int32(0)
 sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, None, C.byref(n)))
 opt.set_pose(poses[5])
 conv = opt.optimize(frames[6])
-buf = np.zeros((n.value, 4, 6), np.uint64)
-sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, buf.ctypes.data, C.byref(n)))
-t = buf.astype(np.int64)
+raw = np.zeros(n.value * 28, np.uint64)
+sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, raw.ctypes.data, C.byref(n)))
+t = raw[: n.value * 24].reshape(n.value, 4, 6).astype(np.int64)
 print(variant, "ctas", n.value, "converged", conv, "iters", opt.last_iterations)
 names = ["lookups", "cta reduce", "grid barrier", "grid reduce", "solve"]
 for k in range(min(4, opt.last_iterations + 1)):
@@ -41,3 +41,36 @@ for k in range(min(4, opt.last_iterations + 1)):
     for i, nm in enumerate(names):
         d = (tk[ok, i + 1] - tk[ok, i]) / 1e3
         print(f"   {nm:12s} mean {d.mean():6.2f}  max {d.max():6.2f} us   (phase ends at {(tk[ok, i + 1].max() - t0) / 1e3:6.2f} us)")
+
+
+# anatomy of the fused track + fuse launch inside the frame pipeline (entry, loop left, fusion done, exit per CTA)
+def anatomy(tag, inflight):
+    sdf.reset()
+    sdf.scan_set_pose(np.array([0, 0, 0, 0, 0, 0, 1], np.float32))
+    sdf.scan_set_tracker(25, 1e-3, 1.0)
+    sdf.scan_submit(depth_host=frames[0], track=False)
+    sdf.scan_collect()
+    for i in range(1, 20):
+        sdf.scan_submit(depth_host=frames[i], track=True)
+        sdf.scan_collect()
+    sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, None, C.byref(n)))
+    for i in range(20, 20 + inflight):
+        sdf.scan_submit(depth_host=frames[i], track=True)
+    res = [sdf.scan_collect() for _ in range(inflight)]
+    raw = np.zeros(n.value * 28, np.uint64)
+    sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, raw.ctypes.data, C.byref(n)))
+    x = raw[n.value * 24:].reshape(n.value, 4).astype(np.int64)
+    p = raw[: n.value * 24].reshape(n.value, 4, 6).astype(np.int64)
+    t0 = x[:, 0].min()
+    f = lambda a: f"first {(a.min() - t0) / 1e3:6.2f}  mean {(a.mean() - t0) / 1e3:6.2f}  last {(a.max() - t0) / 1e3:6.2f}"
+    print(f"{tag}: last frame iters {res[-1].iters} converged {res[-1].converged}")
+    print("   CTA entry      ", f(x[:, 0]))
+    for k in range(min(4, res[-1].iters + 1)):
+        print(f"   pass {k} begin   ", f(p[:, k, 0]), "  solved", f(p[:, k, 5]))
+    print("   loop left      ", f(x[:, 1]))
+    print("   fusion done    ", f(x[:, 2]))
+    print("   exit           ", f(x[:, 3]))
+
+
+anatomy("one frame in flight", 1)
+anatomy("four frames in flight (stamps of the last)", 4)

@@ -306,4 +306,18 @@ def test_scan_pipeline_matches_synchronous_calls(pkg, po, synth, variant):
     ka, kb = a.download()[0], b.download()[0]
     sa, sb = {tuple(x) for x in ka}, {tuple(x) for x in kb}
     assert len(sa & sb) / len(sa | sb) > 0.999
-    a.close(); b.close()
+    # C: the same frame loop in one call (gsdf_scan_run)
+    c, _ = make_pair(pkg, po, variant, 0.01, 5, W, H, K, log2cap=16)
+    c.scan_set_pose(ident)
+    c.scan_set_tracker(25, 1e-3, 1.0)
+    c.scan_submit(depth_dev=dev[0].data_ptr(), track=False)
+    c.scan_collect()
+    run = c.scan_run([dev[i].data_ptr() for i in range(1, len(frames))], on_device=True)
+    assert c.scan_pending() == 0 and len(run) == len(got)
+    for r, q in zip(run, got):
+        assert (r.converged, r.iters, r.fused) == (q.converged, q.iters, q.fused)
+        assert np.abs(np.array(r.pose7[:]) - np.array(q.pose7[:])).max() < (5e-4 if variant == 0 else 5e-5)
+        assert abs(r.updates - q.updates) <= 1e-3 * max(1, q.updates)
+    run_h = c.scan_run([host[i].numpy().ctypes.data for i in range(1, 4)], on_device=False)
+    assert len(run_h) == 3 and c.scan_pending() == 0
+    a.close(); b.close(); c.close()
