@@ -64,7 +64,7 @@ struct DeviceResult {
 
 struct FrameSlot {
     float* d_depth = nullptr;              // landing buffer for host uploads
-    cudaEvent_t ev_up = nullptr, ev_norm = nullptr, ev_fused = nullptr, ev_done = nullptr;
+    cudaEvent_t ev_up = nullptr, ev_norm = nullptr, ev_done = nullptr;
     ResultSnapshot* h_snap = nullptr;      // pinned + mapped: the frame's last kernel writes the result here
     int mode = 0;
 };
@@ -455,7 +455,6 @@ void free_all(gsdf_map* h) {
         cudaFree(sl.d_depth); cudaFreeHost(sl.h_snap);
         if (sl.ev_up) cudaEventDestroy(sl.ev_up);
         if (sl.ev_norm) cudaEventDestroy(sl.ev_norm);
-        if (sl.ev_fused) cudaEventDestroy(sl.ev_fused);
         if (sl.ev_done) cudaEventDestroy(sl.ev_done);
     }
     for (auto& v : h->prof_events) for (auto& pr : v) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
@@ -537,7 +536,6 @@ gsdf_status create_impl(gsdf_map* h) {
         CUDA_TRY(h, cudaHostAlloc(&sl.h_snap, sizeof(ResultSnapshot), cudaHostAllocMapped));
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_up, cudaEventDisableTiming));
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_norm, cudaEventDisableTiming));
-        CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_fused, cudaEventDisableTiming));
         CUDA_TRY(h, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
     }
     CUDA_TRY(h, cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
@@ -973,7 +971,7 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
         // per-kernel profiling runs everything on one stream so that the event brackets do not overlap
         const bool serial = h->serial || h->profiling;
         cudaStream_t side = serial ? h->stream : h->stream_n;
-        if (seq >= kRing && !serial) CUDA_TRY(h, cudaStreamWaitEvent(side, h->ring[seq % kRing].ev_fused, 0));
+        if (seq >= kRing && !serial) CUDA_TRY(h, cudaStreamWaitEvent(side, h->ring[seq % kRing].ev_done, 0));
         trace_mark(h, "side:begin", side);
         if (h->profiling || !h->merged_side) {  // separate launches (also keeps the per-kernel brackets meaningful)
             s = launch_prepare(h, frame, nbuf, side);
@@ -1008,7 +1006,6 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
             if (s != GSDF_OK) return s;
         }
     }
-    CUDA_TRY(h, cudaEventRecord(sl.ev_fused, h->stream));
     trace_mark(h, "main:tracked+fused", h->stream);
     CUDA_TRY(h, cudaEventRecord(sl.ev_done, h->stream));
     trace_mark(h, "main:result", h->stream);

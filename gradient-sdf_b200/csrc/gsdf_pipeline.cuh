@@ -705,13 +705,8 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
         }
         grid_barrier(ctr, ++barriers * gridDim.x);
     }
-    if (threadIdx.x < 7) s_pose7[threadIdx.x] = st->pose7[threadIdx.x];
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
-        s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
-    }
-    __syncthreads();
+    // the three loads every CTA starts with (pose, list length, the thread's list entry) are issued together: the
+    // entry is fetched before it is known to exist (the list buffer holds one entry per pixel of the frame)
     const int n_valid = __ldcg(n_valid_ptr);
     // pixel j of the list -> warp-sized chunk j/32 -> CTA (chunk % grid), warp (chunk / grid): a frame with fewer valid
     // pixels than resident threads (the usual case: ~90 k of 151 k) is spread over ALL SMs instead of filling the
@@ -724,9 +719,16 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
     int cs = -1;
     // the thread's first list entry stays in registers over the passes (with fewer valid pixels than resident threads
     // it is the only one): one dependent L2 round trip less in every pass after the first
-    const bool has0 = gtid < n_valid;
     int2 e0 = make_int2(0, 0);
-    if (has0) e0 = __ldcg(vlist + gtid);
+    if (gtid < g.w * g.h) e0 = __ldcg(vlist + gtid);
+    if (threadIdx.x < 7) s_pose7[threadIdx.x] = __ldcg(&st->pose7[threadIdx.x]);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
+        s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+    }
+    __syncthreads();
+    const bool has0 = gtid < n_valid;
     for (k = 0; k < tp.max_iters; ++k) {
         float acc[kAccTerms];
 #pragma unroll

@@ -127,8 +127,15 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
         for (int j = 0; j < 6; ++j)
             if (j < k) x -= A[6 * k + j] * A[6 * k + j];
         const bool good = ok && !(x <= 0.f);
+#ifdef __CUDA_ARCH__
+        // on the device one MUFU.RSQ (2 ulp) replaces the IEEE square root and reciprocal (two ~60-cycle sequences on
+        // the dependent chain of each of the 6 columns); the solve is a tolerance-level quantity (tests: 1e-4 relative)
+        const float ir = rsqrtf(x);
+        const float r = x * ir;
+#else
         const float r = sqrtf(x);
         const float ir = 1.f / r;
+#endif
         A[6 * k + k] = good ? r : A[6 * k + k];
         inv[k] = good ? ir : 1.f / A[6 * k + k];
 #pragma unroll
