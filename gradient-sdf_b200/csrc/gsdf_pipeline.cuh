@@ -283,22 +283,27 @@ __device__ __forceinline__ void grid_reduce_29(const float* partials, int nblock
 // duplicates are spread, so the number of REDs — not the bytes — bounds this kernel; merging cuts them 3-6x.
 // pose_src: 0 = pose by value, 1 = pose from the device state, 2 = pose from the device state and only if the last
 // optimize converged (main_scan_3d.cpp:261).
+// The members of a group (lanes with the same voxel address) form a list in lane order; the list is summed by
+// pointer jumping (v += v[next], next = next[next]): ceil(log2(group size)) rounds of NV + 1 shuffles, where a
+// leader that collects its members one by one needs group size - 1 rounds — and at 1 cm voxels a voxel spans ~12
+// pixels of an 8x4 tile.  After the last round the first member (the leader) holds the group's sum.
 template <int NV>
-__device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool has, float* v, bool& leader) {
-    // lanes without a sample get a key no one else has
+__device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool narrow, bool has, float* v, bool& leader) {
     const int lane = threadIdx.x & 31;
-    const unsigned long long k = has ? key : (0xFFFFFFFF00000000ull | (unsigned)lane);
-    const unsigned int peers = __match_any_sync(0xffffffffu, k);
+    // lanes without a sample get a key no one else has; narrow: every key of this map fits in 32 bits
+    const unsigned int peers = narrow ? __match_any_sync(0xffffffffu, has ? (unsigned int)key : (0xFFFFFFE0u | (unsigned)lane))
+                                      : __match_any_sync(0xffffffffu, has ? key : (0xFFFFFFFF00000000ull | (unsigned)lane));
     leader = has && ((int)__ffs(peers) - 1 == lane);
-    unsigned int rest = peers & (peers - 1);  // the group without its leader (identical on every member)
-    while (__any_sync(0xffffffffu, rest != 0)) {
-        const int src = rest ? __ffs(rest) - 1 : lane;
+    const unsigned int above = peers & (0xFFFFFFFEu << lane);
+    int nxt = above ? __ffs(above) - 1 : -1;
+    while (__any_sync(0xffffffffu, nxt >= 0)) {
+        const int src = nxt >= 0 ? nxt : lane;
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const float o = __shfl_sync(0xffffffffu, v[i], src);
-            if (leader && rest) v[i] += o;
+            if (nxt >= 0) v[i] += o;
         }
-        rest &= rest - 1;
+        nxt = __shfl_sync(0xffffffffu, nxt, src);
     }
 }
 
@@ -322,6 +327,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
     // chunk-major unit sequence (sizes differ by at most one unit; before, whole (chunk, sample-group) items were
     // dealt round-robin and a warp had 3 or 4 of them: the 4-item CTAs finished 6 us after the others), so a warp
     // loads the pixel data of only one or two chunks.  Warp ranges are interleaved over the CTAs (warp-major).
+    const bool narrow = m.cap_mask < (1u << 23) - 32u;  // voxel addresses (slot * 512 + local) below 2^32 - 2^14
     const int nchunks = (n_valid + 31) >> 5;
     const long long units = (long long)nchunks * S;
     const int warps_total = (gridDim.x * blockDim.x) >> 5;
@@ -396,7 +402,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                 for (int i = 0; i < (VARIANT == 0 ? 5 : 2); ++i) v[i] = 0.f;
             }
             bool leader;
-            warp_merge_by_key<(VARIANT == 0 ? 5 : 2)>(vaddr, has, v, leader);
+            warp_merge_by_key<(VARIANT == 0 ? 5 : 2)>(vaddr, narrow, has, v, leader);
             if (leader) {
                 if (VARIANT == 0) {
                     atomicAdd(m.acc4 + vaddr, make_float4(v[0], v[1], v[2], v[3]));    // :115-117
