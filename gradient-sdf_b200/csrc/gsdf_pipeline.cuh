@@ -50,9 +50,8 @@ struct FrameState {
     float sums[32];             // last reduced sums
 };
 
-// What gsdf_scan_collect reports for a frame.  Written by the LAST CTA of the frame's last kernel straight into pinned
-// host memory (mapped), so that no copy operation sits on the main stream between one frame's fusion and the next
-// frame's tracking (a 1 KB cudaMemcpyAsync there measured 8 us, 10 % of a frame).
+// What gsdf_scan_collect reports for a frame.  Written to device memory by the LAST CTA of the frame's last kernel and
+// copied to pinned host memory on the result stream (see FrameSlot in gsdf_api.cu).
 struct ResultSnapshot {
     FrameState st;
     unsigned long long points, updates;  // cumulative
@@ -438,7 +437,7 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
                  const int* __restrict__ n_valid_ptr, FrameState* st, const float* __restrict__ nx,
                  const float* __restrict__ ny, const float* __restrict__ nz, const float* __restrict__ x0,
                  const float* __restrict__ y0, const float* __restrict__ hom_inv, Counters* ctr,
-                 ResultSnapshot* snap /* null, or pinned host memory: the last CTA publishes the frame result */) {
+                 ResultSnapshot* snap /* null, or where the last CTA leaves the frame result */) {
     if (pose_src == 2 && !st->converged) {  // nothing to integrate (main_scan_3d.cpp:261): only the result is published
         if (snap != nullptr && blockIdx.x == 0) write_snapshot(st, ctr, snap);
         return;
@@ -682,7 +681,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
              FrameState* st, float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp,
              float* fuse_normals /* null: track only; else 3 planes used by the fusion at the end */,
              const float* __restrict__ planes /* the 11 cached FALS planes */, Counters* ctr,
-             ResultSnapshot* snap /* null, or pinned host memory for the frame result */, FramePhases ph,
+             ResultSnapshot* snap /* null, or where the last CTA leaves the frame result */, FramePhases ph,
              PeerExchange px) {
     extern __shared__ __align__(16) unsigned char smem_dyn[];
     unsigned int barriers = 0;  // grid barriers passed so far in this launch
