@@ -43,24 +43,16 @@ for (W, H) in [(320, 240), (640, 480), (1280, 720)]:
             sdf.reset()
             sdf.scan_set_pose(ident)
             sdf.profile_enable(False)
-            out = []
             sdf.scan_submit(depth_dev=dev[0].data_ptr(), track=False)
-            for i in range(1, N):
-                if i == 4:
-                    sdf.synchronize() if False else None
-                    while sdf.scan_pending():
-                        out.append(sdf.scan_collect())
-                    if profile:
-                        sdf.profile_enable(True)
-                    torch.cuda.synchronize()
-                    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-                    ext = torch.cuda.ExternalStream(sdf.stream)
-                    e0.record(ext)
-                sdf.scan_submit(depth_dev=dev[i].data_ptr(), track=True)
-                if sdf.scan_pending() == 4:
-                    out.append(sdf.scan_collect())
-            while sdf.scan_pending():
-                out.append(sdf.scan_collect())
+            out = [sdf.scan_collect()]
+            out += sdf.scan_run([dev[i].data_ptr() for i in range(1, 4)], on_device=True)
+            if profile:
+                sdf.profile_enable(True)
+            torch.cuda.synchronize()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            ext = torch.cuda.ExternalStream(sdf.stream)
+            e0.record(ext)
+            out += sdf.scan_run([dev[i].data_ptr() for i in range(4, N)], on_device=True)  # the frame loop in C
             e1.record(ext)
             e1.synchronize()
             return out, e0.elapsed_time(e1)
