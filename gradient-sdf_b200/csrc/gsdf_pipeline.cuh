@@ -373,20 +373,24 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                 const float py = __fadd_rn(__fmul_rn(s, Rxy1), pose.t[1]);
                 const float pz = __fadd_rn(__fmul_rn(s, Rxy2), pose.t[2]);
                 const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
-                const float qx = __fsub_rn(__fmul_rn(g.vs, (float)vx), pose.t[0]);     // :107
-                const float qy = __fsub_rn(__fmul_rn(g.vs, (float)vy), pose.t[1]);
-                const float qz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pose.t[2]);
-                const float sdf = __fsub_rn(dot3_rn(R[2], R[5], R[8], qx, qy, qz), z); // :107-108
-                const float wgt = sdf_weight(sdf, g.T, g.inv_T);
+                const unsigned long long key = block_key_of(vx, vy, vz);
+                // sharded map: samples of other ranks' blocks (7 of 8 on 8 GPUs) are dropped before the sdf arithmetic
+                const int keep = m.world > 1 ? shard_keeps<VARIANT>(m.world, m.rank, key, vx, vy, vz) : 3;
+                float sdf = 0.f, wgt = 0.f;
+                if (keep) {
+                    const float qx = __fsub_rn(__fmul_rn(g.vs, (float)vx), pose.t[0]);     // :107
+                    const float qy = __fsub_rn(__fmul_rn(g.vs, (float)vy), pose.t[1]);
+                    const float qz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pose.t[2]);
+                    sdf = __fsub_rn(dot3_rn(R[2], R[5], R[8], qx, qy, qz), z);             // :107-108
+                    wgt = sdf_weight(sdf, g.T, g.inv_T);
+                }
                 if (wgt > 0.f) {                                                       // :110-111
-                    const unsigned long long key = block_key_of(vx, vy, vz);
-                    const int keep = shard_keeps<VARIANT>(m.world, m.rank, key, vx, vy, vz);  // 3 on a single GPU
-                    if (keep && key != last_key) {
+                    if (key != last_key) {
                         last_key = key;
                         slot = map_find_or_insert(m, key, ctr);
                         if (slot < 0) atomicAdd(&ctr->overflow, 1u);
                     }
-                    if (keep && slot >= 0) {
+                    if (slot >= 0) {
                         has = true;
                         vaddr = (unsigned long long)slot * kBlockVoxels + local_index(vx, vy, vz);
                         const float ws = wgt * sdf_truncate(sdf, g.T);
@@ -396,6 +400,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                     }
                 }
             }
+            if (!__any_sync(0xffffffffu, has)) continue;  // nothing to commit in this unit (outside the band / not ours)
             if (!has) {
 #pragma unroll
                 for (int i = 0; i < (VARIANT == 0 ? 5 : 2); ++i) v[i] = 0.f;

@@ -1,7 +1,9 @@
 """Room-scale stress run (BASELINE.json configs[3] style): grad-sdf track+fuse over a long synthetic trajectory inside
 a bumpy spherical room, ~10^8 allocated voxels on ONE B200.  The frames are rendered on the GPU with torch (input
 generation, not the product), everything else goes through the C ABI (gsdf_scan_run).
-    python profiles/large_map.py [n_frames=2000] [voxel_mm=4] [trunc=10] [grad|base]"""
+    python profiles/large_map.py [n_frames=2000] [voxel_mm=4] [trunc=10] [grad|base]
+Under torchrun (N ranks, one GPU each) the map is sharded by block key and the tracker sums are exchanged over NVLink
+peer memory, as in bench.py."""
 import json
 import sys
 import time
@@ -24,7 +26,13 @@ trunc = np.float32(float(sys.argv[3]) if len(sys.argv) > 3 else 10.0)
 variant = sys.argv[4] if len(sys.argv) > 4 else "grad"
 W, H = 640, 480
 K = synth.scaled_intrinsics(W, H)
-dev = torch.device("cuda")
+import os  # noqa: E402
+world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+torch.cuda.set_device(local)
+if world > 1:
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+dev = torch.device("cuda", local)
 
 # scene: a spherical shell of radius 3.3 m seen from inside, 64 bumps (spheres) sticking out of it
 rng = np.random.default_rng(42)
@@ -78,36 +86,75 @@ poses = trajectory(n_frames)
 t0 = time.time()
 frames = torch.stack([render(poses[k]) for k in range(n_frames)])
 torch.cuda.synchronize()
-print(f"rendered {n_frames} frames in {time.time() - t0:.1f} s ({frames.numel() * 4 / 2**30:.2f} GiB in HBM)", flush=True)
+if rank == 0:
+    print(f"rendered {n_frames} frames in {time.time() - t0:.1f} s ({frames.numel() * 4 / 2**30:.2f} GiB in HBM)", flush=True)
 
 nest = pkg.NormalEstimator(W, H, K.astype(np.float32), 11)
 cls = pkg.MapGradPixelSdf if variant == "grad" else pkg.MapPixelSdf
-sdf = cls(vs, trunc * vs, nest, log2_capacity=21)
+sdf = cls(vs, trunc * vs, nest, log2_capacity=21 if world == 1 else 20, device=local, world_size=world, rank=rank)
+if world > 1:
+    import ctypes as C
+    idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        buf = (C.c_uint8 * 128)()
+        assert pkg.lib().gsdf_comm_unique_id(buf) == 0
+        idt.copy_(torch.tensor(list(buf), dtype=torch.uint8))
+    dist.broadcast(idt, 0)
+    sdf.comm_init(bytes(idt.cpu().tolist()))
+    hd = torch.tensor(list(sdf.p2p_export()), dtype=torch.uint8, device=dev)
+    allh = [torch.zeros_like(hd) for _ in range(world)]
+    dist.all_gather(allh, hd)
+    sdf.p2p_connect(bytes(torch.cat(allh).cpu().tolist()))
+    dist.barrier()
 sdf.scan_set_pose(poses[0].astype(np.float32))
 sdf.scan_set_tracker(25, 1e-3, 1.0)
 sdf.scan_submit(depth_dev=frames[0].data_ptr(), track=False)
 sdf.scan_collect()
 ext = torch.cuda.ExternalStream(sdf.stream)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+torch.cuda.synchronize()
+if world > 1:
+    dist.barrier()
 e0.record(ext)
-res = sdf.scan_run([frames[k].data_ptr() for k in range(1, n_frames)], on_device=True)
+ptrs = [frames[k].data_ptr() for k in range(1, n_frames)]
+res = sdf.scan_run(ptrs, on_device=True)
 e1.record(ext)
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1)
+upd_all = float(sum(r.updates for r in res))
+if world > 1:
+    t = torch.tensor([ms], dtype=torch.float64, device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t)
+    t = torch.tensor([upd_all], dtype=torch.float64, device=dev); dist.all_reduce(t); upd_all = float(t)
+# anatomy: the last 200 frames once more over the finished map (in-kernel spans, outside the timed region)
+sdf._check(sdf.L.gsdf_debug_frame_log(sdf.h, None))
+sdf.scan_run(ptrs[-200:], on_device=True)
+log = np.zeros((256, 4), np.uint64)
+sdf._check(sdf.L.gsdf_debug_frame_log(sdf.h, log.ctypes.data))
+tl = log[(log[:, 3] > 0) & (log[:, 1] > 0)].astype(np.int64)
+tl = tl[np.argsort(tl[:, 2])][2:-2]
+anatomy = {"period": float(np.diff(tl[:, 2]).mean() / 1e3), "track_fuse_kernel": float((tl[:, 3] - tl[:, 2]).mean() / 1e3),
+           "frame_only_kernel_in_shadow": float((tl[:, 1] - tl[:, 0]).mean() / 1e3),
+           "gap_between_track_fuse_kernels": float((tl[1:, 2] - tl[:-1, 3]).mean() / 1e3)}
 conv = sum(r.converged for r in res)
 err_t = max(float(np.abs(np.array(r.pose7[:3]) - poses[k + 1, :3]).max()) for k, r in enumerate(res))
 last = np.array(res[-1].pose7[:])
 voxels, blocks = sdf.voxel_count()
+if world > 1:
+    t = torch.tensor([voxels, blocks], dtype=torch.float64, device=dev); dist.all_reduce(t); voxels, blocks = int(t[0]), int(t[1])
 free, total = torch.cuda.mem_get_info()
 out = {
     "workload": f"C4-style: {variant}-sdf track+fuse, {n_frames} frames 640x480 inside a bumpy 3.3 m spherical room, "
-                f"{float(vs) * 1e3:.0f} mm voxels, trunc {float(trunc):.0f}, one B200",
+                f"{float(vs) * 1e3:.0f} mm voxels, trunc {float(trunc):.0f}, {world} B200" + (" (hash sharded by block key)" if world > 1 else ""),
+    "n_gpus": world,
     "frames_per_s": 1e3 * (n_frames - 1) / ms, "ms_per_frame": ms / (n_frames - 1),
     "converged": conv, "tracked": len(res), "gn_iterations_per_frame": sum(r.iters for r in res) / len(res),
-    "updates_per_frame": sum(r.updates for r in res) / len(res),
-    "voxel_updates_per_s": 1e3 * sum(r.updates for r in res) / ms,
-    "voxels": int(voxels), "blocks": int(blocks), "hash_load": blocks / float(1 << 21),
+    "updates_per_frame": upd_all / len(res),
+    "voxel_updates_per_s": 1e3 * upd_all / ms,
+    "voxels": int(voxels), "blocks": int(blocks), "hash_load_per_rank": blocks / float(world) / float(1 << (21 if world == 1 else 20)),
     "max_translation_error_m": err_t, "final_pose": last.tolist(), "final_pose_true": poses[-1].tolist(),
-    "hbm_used_GiB": (total - free) / 2**30,
+    "hbm_used_GiB": (total - free) / 2**30, "anatomy_us_200_frames_replayed": anatomy,
 }
-print(json.dumps(out))
+if rank == 0:
+    print(json.dumps(out))
+if world > 1:
+    dist.destroy_process_group()
