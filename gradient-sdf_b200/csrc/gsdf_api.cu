@@ -53,7 +53,8 @@ NcclApi g_nccl;
 constexpr int kNcclFloat = 7, kNcclSum = 0;  // ncclFloat32, ncclSum (nccl.h)
 std::string g_create_error;
 constexpr int kFlogFrames = 256;
-constexpr int kRing = 4;  // frames in flight in the submit/collect pipeline
+constexpr int kRing = 12;       // frame slots: gsdf_scan_run keeps up to three batches of kMaxBatch frames in flight
+constexpr int kMaxPending = 4;  // frames in flight through gsdf_scan_submit (the documented limit)
 }  // namespace
 
 // tracker state and statistics live side by side on the device so that a frame's result is ONE small copy
@@ -74,6 +75,7 @@ struct FrameSlot {
     ResultSnapshot* d_snap = nullptr;
     ResultSnapshot* h_snap = nullptr;
     bool direct = false;                   // this frame's result goes straight to h_snap
+    cudaEvent_t wait_ev = nullptr;         // what gsdf_scan_collect waits for (the event of the frame's batch)
     int mode = 0;
 };
 
@@ -98,7 +100,6 @@ struct gsdf_map {
     unsigned int* d_compact_flags2 = nullptr; // [normals tiles] same for normals_compact_kernel
     unsigned int compact_epoch = 0;
     int nseg = 0;                           // CTAs of the compaction (64 tiles of 8x4 pixels each)
-    int nseg_frame = 0;                     // segments of the frame kernel's compaction (128 tiles each)
     DeviceResult* d_res = nullptr;    // owns d_state and d_ctr
     FrameState* d_state = nullptr;
     Counters* d_ctr = nullptr;
@@ -133,8 +134,8 @@ struct gsdf_map {
     bool fuse_in_track = true;  // GSDF_FUSE_IN_TRACK=0: separate fusion launch instead of the tracker launch's tail
     bool merged_side = true;    // GSDF_MERGED_SIDE=0: compaction and normals as two launches
     bool serial = false;        // GSDF_SERIAL=1: frame-only kernels on the main stream instead of the side stream
+    int batch_frames = kMaxBatch;  // GSDF_BATCH_FRAMES=1..4: frames per tracker launch in gsdf_scan_run
     bool shadow_side = true;    // GSDF_SHADOW_SIDE=0: frame-only kernel always at full occupancy
-    bool frame_kernel = false;  // GSDF_FRAME_KERNEL=1: whole frame in one cooperative launch (experimental)
     unsigned long long* d_dbg = nullptr;  // tracker phase stamps (gsdf_debug_track_timers)
     unsigned long long* d_flog = nullptr; // [kFlogFrames][4] kernel spans per pipeline frame (gsdf_debug_frame_log)
     // NVLink peer exchange of the sharded tracker (gsdf_p2p_export / gsdf_p2p_connect)
@@ -302,7 +303,8 @@ gsdf_status launch_prepare(gsdf_map* h, const float* depth, int buf, cudaStream_
 constexpr size_t kShadowSmem = 116 * 1024;
 
 // compaction + normals of a frame in one launch (the pipeline's frame-only work)
-gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cudaStream_t stream, bool shadow = false) {
+gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cudaStream_t stream, bool shadow = false,
+                                   int64_t seq = -1) {
     const int w = h->cfg.width, ht = h->cfg.height, r = h->cfg.normal_window / 2;
     const size_t n = (size_t)w * ht;
     dim3 grid((w + NT_W - 1) / NT_W, (ht + NT_H - 1) / NT_H), block(NT_W, NT_H);
@@ -311,7 +313,7 @@ gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cud
     normals_compact_kernel<<<grid, block, shadow ? std::max(kShadowSmem, normals_smem(h)) : normals_smem(h), stream>>>(
         depth, h->d_planes + 2 * n, h->d_planes + 3 * n, h->d_planes + 4 * n, h->d_planes + 5 * n, nrm, nrm + n,
         nrm + 2 * n, w, ht, r, h->geom.z_min, h->geom.z_max, h->d_compact_flags2, h->compact_epoch, h->d_vlist[buf],
-        h->d_nvalid + buf, h->d_flog ? h->d_flog + 4 * (h->seq_submitted % kFlogFrames) : nullptr);
+        h->d_nvalid + buf, h->d_flog ? h->d_flog + 4 * ((seq < 0 ? h->seq_submitted : seq) % kFlogFrames) : nullptr);
     return check_launch(h, "normals_compact_kernel");
 }
 
@@ -351,44 +353,55 @@ gsdf_status launch_fuse(gsdf_map* h, const Pose& pose, int pose_src, int nbuf, c
     });
 }
 
-// the Gauss-Newton loop from the pose in d_state; result (pose, converged, iters) stays in d_state
-// fuse_after: integrate the frame in the same launch if the optimisation converged (single-GPU path only)
-// fuse_mode 0/1/2 (never / always / iff converged) integrates the frame in the same launch; frame != null also runs
-// compaction and normals at the head of the launch (single-GPU path only)
+// The Gauss-Newton loop from the pose in d_state for nb frames in ONE launch (frame i uses the frame-only buffers
+// bufs[i] and leaves its result in snaps[i]); pose, converged flag and iteration count of the last frame stay in
+// d_state.  fuse_mode 0/1/2 (never / always / iff converged) integrates each frame in the same launch.  Sharded maps
+// without a peer connection take the per-iteration NCCL path below (nb = 1 only).
+gsdf_status launch_track_batch(gsdf_map* h, const TrackParams& tp, const int* bufs, int nb, cudaStream_t stream, int fuse_mode,
+                               ResultSnapshot* const* snaps, int64_t seq0);
+
 gsdf_status launch_track(gsdf_map* h, const TrackParams& tp, int buf, cudaStream_t stream, int fuse_mode = 0,
-                         ResultSnapshot* snap_out = nullptr, const float* frame = nullptr) {
+                         ResultSnapshot* snap_out = nullptr) {
+    return launch_track_batch(h, tp, &buf, 1, stream, fuse_mode, &snap_out, h->seq_submitted);
+}
+
+gsdf_status launch_track_batch(gsdf_map* h, const TrackParams& tp, const int* bufs, int nb, cudaStream_t stream, int fuse_mode,
+                               ResultSnapshot* const* snaps, int64_t seq0) {
     const TrackIntr ti = make_intr(h, 1);
+    const int buf = bufs[0];
+    if (nb < 1 || nb > kMaxBatch) { h->err = "launch_track_batch: bad batch size"; return GSDF_ERR_INVALID; }
     if (h->cfg.world_size == 1 || h->p2p_connected) {
         return by_variant(h, [&](auto V) {
             ProfScope prof(h, GSDF_PROF_ACCUMULATE, stream);
             MapView view = h->view;
             FrameGeom geom = h->geom;
             TrackIntr ti_ = ti;
-            int2* vlist = h->d_vlist[buf];
-            int* nvalid = h->d_nvalid + buf;
             FrameState* st = h->d_state;
             float* partials = h->d_track_partials;
             TrackParams tp_ = tp;
-            float* fuse_normals = fuse_mode ? h->d_normals[buf] : nullptr;
             const float* planes = h->d_planes;
             Counters* ctr = h->d_ctr;
-            ResultSnapshot* snap = snap_out;
-            FramePhases ph;
-            ph.depth = frame; ph.flags = h->d_compact_flags; ph.epoch = 0; ph.nseg = h->nseg_frame;
-            ph.r = h->cfg.normal_window / 2; ph.fuse_mode = fuse_mode; ph.dbg = h->d_dbg;
-            ph.flog = (h->d_flog && snap_out) ? h->d_flog + 4 * (h->seq_submitted % kFlogFrames) : nullptr;
-            if (frame) { h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu; ph.epoch = h->compact_epoch; }
+            FrameBatch fb = {};
+            fb.n = nb; fb.fuse_mode = fuse_mode; fb.dbg = h->d_dbg;
+            for (int i = 0; i < nb; ++i) {
+                fb.vlist[i] = h->d_vlist[bufs[i]];
+                fb.n_valid[i] = h->d_nvalid + bufs[i];
+                fb.normals[i] = fuse_mode ? h->d_normals[bufs[i]] : nullptr;
+                fb.snap[i] = snaps[i];
+                fb.flog[i] = (h->d_flog && snaps[i]) ? h->d_flog + 4 * ((seq0 + i) % kFlogFrames) : nullptr;
+            }
             PeerExchange px = h->px;  // world <= 1 unless gsdf_p2p_connect succeeded
             if (px.world > 1 && tp.max_iters > 63) { h->err = "sharded tracking over NVLink supports at most 63 iterations"; return GSDF_ERR_INVALID; }
-            if (px.world > 1) px.epoch0 = (++h->p2p_launches) * 64u;  // max_iters <= 63 passes per launch
-            void* args[] = {&view, &geom, &ti_, &vlist, &nvalid, &st, &partials, &tp_, &fuse_normals, &planes, &ctr, &snap, &ph, &px};
+            if (px.world > 1) px.epoch0 = (++h->p2p_launches) * 256u;  // <= kMaxBatch * 63 passes per launch
+            void* args[] = {&view, &geom, &ti_, &st, &partials, &tp_, &planes, &ctr, &fb, &px};
             // cooperative launch: the driver guarantees that all CTAs are resident together (grid_barrier relies on it)
             cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_kernel<decltype(V)::value>, dim3(h->track_blocks),
-                                                        dim3(kTrackThreads), args, frame ? normals_smem(h) : 0, stream);
+                                                        dim3(kTrackThreads), args, 0, stream);
             if (e != cudaSuccess) { h->err = std::string("launch of track_kernel: ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
             return check_launch(h, "track_kernel");
         });
     }
+    if (nb != 1) { h->err = "launch_track_batch: batches need one GPU or a peer-connected shard"; return GSDF_ERR_INVALID; }
     // sharded map: per-iteration launches with an all-reduce between the sums and the solve
     if (!h->comm) { h->err = "world_size > 1 but gsdf_comm_init was not called"; return GSDF_ERR_NCCL; }
     track_begin_kernel<<<1, 32, 0, stream>>>(h->d_state);
@@ -511,7 +524,6 @@ gsdf_status create_impl(gsdf_map* h) {
     CUDA_TRY(h, cudaMemset(h->d_nvalid, 0, sizeof(int) * kRing));
     const int ntiles = ((c.width + kTileW - 1) / kTileW) * ((c.height + kTileH - 1) / kTileH);
     h->nseg = (ntiles + kTilesPerBlock - 1) / kTilesPerBlock;
-    h->nseg_frame = (ntiles + kTrackWarps * kTilesPerWarp - 1) / (kTrackWarps * kTilesPerWarp);
     CUDA_TRY(h, cudaMalloc(&h->d_compact_flags, sizeof(unsigned int) * h->nseg));
     CUDA_TRY(h, cudaMemset(h->d_compact_flags, 0, sizeof(unsigned int) * h->nseg));
     const int n_ntiles = ((c.width + NT_W - 1) / NT_W) * ((c.height + NT_H - 1) / NT_H);
@@ -522,15 +534,10 @@ gsdf_status create_impl(gsdf_map* h) {
     h->d_ctr = &h->d_res->ctr;
     h->acc_blocks = h->sm_count * 2;
     CUDA_TRY(h, cudaMalloc(&h->d_partials, sizeof(float) * kAccStride * h->sm_count * 4));
-    // persistent tracker: one CTA per SM (all co-resident, as grid.sync requires)
+    // persistent tracker: two CTAs per SM, all co-resident (cooperative launch; grid_barrier relies on it)
     int per_sm = 0;
-    if (c.variant == GSDF_GRAD_SDF) {
-        CUDA_TRY(h, cudaFuncSetAttribute(track_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
-        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<0>, kTrackThreads, normals_smem(h)));
-    } else {
-        CUDA_TRY(h, cudaFuncSetAttribute(track_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
-        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<1>, kTrackThreads, normals_smem(h)));
-    }
+    if (c.variant == GSDF_GRAD_SDF) CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<0>, kTrackThreads, 0));
+    else CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<1>, kTrackThreads, 0));
     if (per_sm < 1) { h->err = "track_kernel does not fit on an SM"; return GSDF_ERR_CUDA; }
     h->track_blocks = h->sm_count * (per_sm >= 2 ? 2 : 1);
     if (const char* e = std::getenv("GSDF_TRACK_CTAS_PER_SM")) h->track_blocks = h->sm_count * (e[0] == '1' ? 1 : (per_sm >= 2 ? 2 : 1));
@@ -648,8 +655,8 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     }
     gsdf_map* h = new gsdf_map();
     h->cfg = c;
-    if (const char* e = std::getenv("GSDF_FRAME_KERNEL")) h->frame_kernel = e[0] == '1';
     if (const char* e = std::getenv("GSDF_SHADOW_SIDE")) h->shadow_side = e[0] == '1';
+    if (const char* e = std::getenv("GSDF_BATCH_FRAMES")) h->batch_frames = std::min(kMaxBatch, std::max(1, std::atoi(e)));
     if (const char* e = std::getenv("GSDF_SERIAL")) h->serial = e[0] == '1';
     if (const char* e = std::getenv("GSDF_MERGED_SIDE")) h->merged_side = e[0] == '1';
     if (const char* e = std::getenv("GSDF_FUSE_IN_TRACK")) h->fuse_in_track = e[0] == '1';
@@ -938,57 +945,58 @@ gsdf_status gsdf_scan_set_tracker(gsdf_handle h, int32_t max_iters, float conv_t
     return GSDF_OK;
 }
 
-gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float* depth_dev, int32_t mode) {
-    if (!h || (!depth_host && !depth_dev) || (depth_host && depth_dev) || (mode != GSDF_SCAN_FUSE && mode != GSDF_SCAN_TRACK_FUSE))
-        return GSDF_ERR_INVALID;
-    if (depth_dev && ((uintptr_t)depth_dev & 15)) { h->err = "device frame must be 16-byte aligned"; return GSDF_ERR_INVALID; }
-    if (h->seq_submitted - h->seq_collected >= kRing) {
-        h->err = "gsdf_scan_submit: 4 frames already in flight, call gsdf_scan_collect";
-        return GSDF_ERR_INVALID;
-    }
+namespace {
+
+// can this handle run several frames per tracker launch?  (one GPU or a peer-connected shard, fused track+fuse launch,
+// merged frame-only kernel, no per-kernel profiling / tracing / serial debugging mode)
+bool batch_capable(const gsdf_map* h) {
+    return (h->cfg.world_size == 1 || h->p2p_connected) && !h->profiling && !h->serial && !h->tracing && h->fuse_in_track &&
+           h->merged_side;
+}
+
+// Enqueue nb frames: their uploads (copy stream), their frame-only kernels (side stream) and ONE tracker launch that
+// works through them in order (main stream).  nb > 1 requires batch_capable() and GSDF_SCAN_TRACK_FUSE.  The caller has
+// checked that nb free slots exist.
+gsdf_status submit_frames(gsdf_map* h, const float* const* host, const float* const* dev, int nb, int32_t mode) {
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
-    const int64_t seq = h->seq_submitted;
-    FrameSlot& sl = h->ring[seq % kRing];
     const size_t n = (size_t)h->cfg.width * h->cfg.height;
-    const float* frame = depth_dev;
-    if (h->seq_submitted == h->seq_collected) {
+    const bool idle = h->seq_submitted == h->seq_collected;
+    if (idle) {
         // pipeline was idle: whatever the synchronous entry points left running on the main stream may still use
         // the buffers the side streams are about to overwrite
         CUDA_TRY(h, cudaEventRecord(h->ev_main, h->stream));
         CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, h->ev_main, 0));
         CUDA_TRY(h, cudaStreamWaitEvent(h->stream_c, h->ev_main, 0));
     }
-    if (depth_host) {
-        CUDA_TRY(h, cudaMemcpyAsync(sl.d_depth, depth_host, sizeof(float) * n, cudaMemcpyHostToDevice, h->stream_c));
-        CUDA_TRY(h, cudaEventRecord(sl.ev_up, h->stream_c));
-        CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_up, 0));
-        CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, sl.ev_up, 0));
-        frame = sl.d_depth;
-    }
-    const int nbuf = (int)(seq % kRing);
-    sl.direct = h->seq_submitted == h->seq_collected;
-    ResultSnapshot* snap_dst = sl.direct ? sl.h_snap : sl.d_snap;
-    gsdf_status s = GSDF_OK;
     // single cooperative launch for track + fuse: one GPU, or a sharded map whose ranks are connected over NVLink
     const bool single = (h->cfg.world_size == 1 || h->p2p_connected) && !h->profiling;
-    if (single && h->frame_kernel) {
-        // ONE cooperative launch per frame: compaction + normals, the Gauss-Newton loop, fusion, result snapshot.
-        // Measured slower than the split below (95 vs 73 us per frame at 640x480: with one 512-thread CTA per SM the
-        // frame-only phases run at a quarter of their stand-alone occupancy), kept behind GSDF_FRAME_KERNEL=1.
-        trace_mark(h, "main:begin", h->stream);
-        TrackParams tp = h->scan_tp;
-        if (mode == GSDF_SCAN_FUSE) tp.max_iters = 0;
-        s = launch_track(h, tp, nbuf, h->stream, mode == GSDF_SCAN_FUSE ? 1 : 2, snap_dst, frame);
-        if (s != GSDF_OK) return s;
-    } else {
+    // per-kernel profiling runs everything on one stream so that the event brackets do not overlap
+    const bool serial = h->serial || h->profiling;
+    cudaStream_t side = serial ? h->stream : h->stream_n;
+    const int64_t seq0 = h->seq_submitted;
+    int bufs[kMaxBatch];
+    ResultSnapshot* snaps[kMaxBatch];
+    const float* frame = nullptr;
+    gsdf_status s = GSDF_OK;
+    for (int i = 0; i < nb; ++i) {
+        const int64_t seq = seq0 + i;
+        FrameSlot& sl = h->ring[seq % kRing];
+        frame = dev ? dev[i] : nullptr;
+        if (host) {
+            CUDA_TRY(h, cudaMemcpyAsync(sl.d_depth, host[i], sizeof(float) * n, cudaMemcpyHostToDevice, h->stream_c));
+            CUDA_TRY(h, cudaEventRecord(sl.ev_up, h->stream_c));
+            CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_up, 0));
+            CUDA_TRY(h, cudaStreamWaitEvent(h->stream_n, sl.ev_up, 0));
+            frame = sl.d_depth;
+        }
+        const int nbuf = (int)(seq % kRing);
+        sl.direct = idle && nb == 1;
+        bufs[i] = nbuf;
+        snaps[i] = sl.direct ? sl.h_snap : sl.d_snap;
         // Pixel compaction and normals depend only on the frame, not on the map or the pose: they run on the side
-        // stream, up to kRing - 1 frames ahead of the main stream (which has the higher priority: the side kernels
-        // fill the SMs the tracker leaves idle instead of competing with it for the moment a frame ends); their
-        // buffers (index seq % kRing) were last read by the tracker/fusion of frame seq - kRing, collected long ago.
-        // per-kernel profiling runs everything on one stream so that the event brackets do not overlap
-        const bool serial = h->serial || h->profiling;
-        cudaStream_t side = serial ? h->stream : h->stream_n;
-        if (seq >= kRing && !serial) CUDA_TRY(h, cudaStreamWaitEvent(side, h->ring[seq % kRing].ev_done, 0));
+        // stream, frames ahead of the main stream (which has the higher priority: the side kernels fill what the
+        // tracker leaves idle instead of competing with it for the moment a frame ends).  Their buffers (index
+        // seq % kRing) were last read by the tracker/fusion of frame seq - kRing, collected long ago.
         trace_mark(h, "side:begin", side);
         if (h->profiling || !h->merged_side) {  // separate launches (also keeps the per-kernel brackets meaningful)
             s = launch_prepare(h, frame, nbuf, side);
@@ -996,7 +1004,7 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
             s = launch_normals(h, frame, nbuf, side, true);
         } else {
             // frames already in flight: this one's frame-only work is not on the critical path, keep its footprint small
-            s = launch_normals_compact(h, frame, nbuf, side, h->shadow_side && h->seq_submitted > h->seq_collected);
+            s = launch_normals_compact(h, frame, nbuf, side, h->shadow_side && (!idle || i > 0), seq);
         }
         if (s != GSDF_OK) return s;
         trace_mark(h, "side:normals", side);
@@ -1004,41 +1012,59 @@ gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float
             CUDA_TRY(h, cudaEventRecord(sl.ev_norm, side));
             CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.ev_norm, 0));
         }
-        trace_mark(h, "main:begin", h->stream);
-        if (single && mode == GSDF_SCAN_TRACK_FUSE && h->fuse_in_track) {
-            // track, fuse iff converged and publish the result in ONE cooperative launch (2 CTAs of 512 threads per
-            // SM: measured 16.5 k frames/s against 14.4 k with a separate fusion launch, grad-sdf 1 cm)
-            s = launch_track(h, h->scan_tp, nbuf, h->stream, 2, snap_dst);
+        sl.mode = mode;
+    }
+    trace_mark(h, "main:begin", h->stream);
+    if (single && mode == GSDF_SCAN_TRACK_FUSE && h->fuse_in_track) {
+        // track, fuse iff converged and leave the result, for every frame of the batch, in ONE cooperative launch
+        s = launch_track_batch(h, h->scan_tp, bufs, nb, h->stream, 2, snaps, seq0);
+        if (s != GSDF_OK) return s;
+    } else {
+        if (nb != 1) { h->err = "submit_frames: this configuration takes one frame per launch"; return GSDF_ERR_INVALID; }
+        if (mode == GSDF_SCAN_TRACK_FUSE) {
+            s = launch_track(h, h->scan_tp, bufs[0], h->stream);
             if (s != GSDF_OK) return s;
-        } else {
-            if (mode == GSDF_SCAN_TRACK_FUSE) {
-                s = launch_track(h, h->scan_tp, nbuf, h->stream);
-                if (s != GSDF_OK) return s;
-                trace_mark(h, "main:tracked", h->stream);
-            }
-            // fusion (predicated on the device-side converged flag); its last CTA publishes the frame result
-            Pose unused;
-            std::memset(&unused, 0, sizeof(unused));
-            s = launch_fuse(h, unused, mode == GSDF_SCAN_TRACK_FUSE ? 2 : 1, nbuf, h->stream, snap_dst);
-            if (s != GSDF_OK) return s;
+            trace_mark(h, "main:tracked", h->stream);
         }
+        // fusion (predicated on the device-side converged flag); its last CTA publishes the frame result
+        Pose unused;
+        std::memset(&unused, 0, sizeof(unused));
+        s = launch_fuse(h, unused, mode == GSDF_SCAN_TRACK_FUSE ? 2 : 1, bufs[0], h->stream, snaps[0]);
+        if (s != GSDF_OK) return s;
     }
     trace_mark(h, "main:tracked+fused", h->stream);
-    CUDA_TRY(h, cudaEventRecord(sl.ev_done, h->stream));
-    if (!sl.direct) {
-        CUDA_TRY(h, cudaStreamWaitEvent(h->stream_r, sl.ev_done, 0));
-        CUDA_TRY(h, cudaMemcpyAsync(sl.h_snap, sl.d_snap, sizeof(ResultSnapshot), cudaMemcpyDeviceToHost, h->stream_r));
-        CUDA_TRY(h, cudaEventRecord(sl.ev_result, h->stream_r));
+    FrameSlot& last = h->ring[(seq0 + nb - 1) % kRing];
+    CUDA_TRY(h, cudaEventRecord(last.ev_done, h->stream));
+    if (!last.direct) {
+        CUDA_TRY(h, cudaStreamWaitEvent(h->stream_r, last.ev_done, 0));
+        for (int i = 0; i < nb; ++i) {
+            FrameSlot& sl = h->ring[(seq0 + i) % kRing];
+            CUDA_TRY(h, cudaMemcpyAsync(sl.h_snap, sl.d_snap, sizeof(ResultSnapshot), cudaMemcpyDeviceToHost, h->stream_r));
+        }
+        CUDA_TRY(h, cudaEventRecord(last.ev_result, h->stream_r));
     }
+    for (int i = 0; i < nb; ++i) h->ring[(seq0 + i) % kRing].wait_ev = last.direct ? last.ev_done : last.ev_result;
     trace_mark(h, "main:result", h->stream);
-    sl.mode = mode;
-    h->seq_submitted++;
-    // the synchronous entry points see this frame as current once the pipeline has drained
+    h->seq_submitted += nb;
+    // the synchronous entry points see the last frame as current once the pipeline has drained
     h->d_depth = frame;
-    h->normals_buf = nbuf;
+    h->normals_buf = bufs[nb - 1];
     h->normals_valid = true;
     h->prepared = true;
     return GSDF_OK;
+}
+
+}  // namespace
+
+gsdf_status gsdf_scan_submit(gsdf_handle h, const float* depth_host, const float* depth_dev, int32_t mode) {
+    if (!h || (!depth_host && !depth_dev) || (depth_host && depth_dev) || (mode != GSDF_SCAN_FUSE && mode != GSDF_SCAN_TRACK_FUSE))
+        return GSDF_ERR_INVALID;
+    if (depth_dev && ((uintptr_t)depth_dev & 15)) { h->err = "device frame must be 16-byte aligned"; return GSDF_ERR_INVALID; }
+    if (h->seq_submitted - h->seq_collected >= kMaxPending) {
+        h->err = "gsdf_scan_submit: 4 frames already in flight, call gsdf_scan_collect";
+        return GSDF_ERR_INVALID;
+    }
+    return submit_frames(h, depth_host ? &depth_host : nullptr, depth_dev ? &depth_dev : nullptr, 1, mode);
 }
 
 gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
@@ -1046,7 +1072,7 @@ gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
     if (h->seq_collected == h->seq_submitted) { h->err = "gsdf_scan_collect: nothing pending"; return GSDF_ERR_INVALID; }
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
     FrameSlot& sl = h->ring[h->seq_collected % kRing];
-    CUDA_TRY(h, cudaEventSynchronize(sl.direct ? sl.ev_done : sl.ev_result));
+    CUDA_TRY(h, cudaEventSynchronize(sl.wait_ev));
     h->seq_collected++;
     const FrameState& st = sl.h_snap->st;
     const ResultSnapshot& c = *sl.h_snap;
@@ -1085,16 +1111,26 @@ int32_t gsdf_scan_pending(gsdf_handle h) { return h ? (int32_t)(h->seq_submitted
 
 gsdf_status gsdf_scan_run(gsdf_handle h, const float* const* frames, int64_t n, int32_t on_device, int32_t mode,
                           gsdf_frame_result* results, int64_t* n_done) {
-    if (!h || !frames || !results || n < 0) return GSDF_ERR_INVALID;
+    if (!h || !frames || !results || n < 0 || (mode != GSDF_SCAN_FUSE && mode != GSDF_SCAN_TRACK_FUSE)) return GSDF_ERR_INVALID;
     if (n_done) *n_done = 0;
     if (h->seq_submitted != h->seq_collected) { h->err = "gsdf_scan_run: frames are pending, collect them first"; return GSDF_ERR_INVALID; }
+    for (int64_t i = 0; i < n; ++i) {
+        if (!frames[i]) { h->err = "gsdf_scan_run: null frame"; return GSDF_ERR_INVALID; }
+        if (on_device && ((uintptr_t)frames[i] & 15)) { h->err = "device frame must be 16-byte aligned"; return GSDF_ERR_INVALID; }
+    }
+    // Knowing the frames ahead, the loop hands the tracker up to kMaxBatch frames per launch (one grid barrier between two
+    // frames instead of leaving and relaunching the kernel) and keeps up to three such batches in flight: the batch being
+    // tracked, and two whose uploads and frame-only kernels run ahead of it.
+    const bool batches = batch_capable(h) && mode == GSDF_SCAN_TRACK_FUSE && h->batch_frames > 1;
     int64_t submitted = 0, collected = 0;
     gsdf_status s = GSDF_OK;
     while (collected < n) {
-        while (submitted < n && submitted - collected < kRing) {
-            s = gsdf_scan_submit(h, on_device ? nullptr : frames[submitted], on_device ? frames[submitted] : nullptr, mode);
+        while (submitted < n) {
+            const int nb = batches ? (int)std::min<int64_t>(h->batch_frames, n - submitted) : 1;
+            if (submitted - collected + nb > (batches ? kRing : kMaxPending)) break;
+            s = submit_frames(h, on_device ? nullptr : frames + submitted, on_device ? frames + submitted : nullptr, nb, mode);
             if (s != GSDF_OK) break;
-            ++submitted;
+            submitted += nb;
         }
         if (s != GSDF_OK) break;
         s = gsdf_scan_collect(h, results + collected);

@@ -544,23 +544,33 @@ normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x
                  threadIdx.y, smem_dyn);
 }
 
-// Optional frame-only phases run at the head of track_kernel (the "frame kernel": ONE cooperative launch per frame
-// does compaction, normals, the Gauss-Newton loop, fusion and the result snapshot — no side streams, no events, no
-// launch gaps between dependent kernels inside a frame).
-struct FramePhases {
-    const float* depth;      // null: the list and the normals were prepared by earlier launches
-    unsigned int* flags;     // look-back flags of the compaction
-    unsigned int epoch;
-    int nseg;                // segments of kTrackWarps * kTilesPerWarp tiles
-    int r;                   // normal window radius
-    int fuse_mode;           // 0 = never, 1 = always (setup / ground-truth pose), 2 = iff the optimisation converged
-    unsigned long long* flog; // null, or this frame's entry of the debug frame log (main kernel: words 2, 3)
-    unsigned long long* dbg; // null, or [gridDim.x][4 passes][6] + [gridDim.x][4] %globaltimer stamps of the tracker's phases
+// The frames one launch of track_kernel works through, in order (gsdf_scan_run hands it up to kMaxBatch frames whose
+// lists and normals the side stream has prepared; every other caller passes one).  Entering, leaving and relaunching
+// the kernel costs 7.6 us per launch at 640x480 (entry 1.2, result + exit 2.4, kernel-to-kernel gap 4); between two
+// frames of a batch there is one grid barrier instead.
+constexpr int kMaxBatch = 4;
+struct FrameBatch {
+    int n;                                  // frames in this launch
+    int fuse_mode;                          // 0 = never, 1 = always (setup / ground-truth pose), 2 = iff the optimisation converged
+    int2* vlist[kMaxBatch];                 // compacted valid pixels of frame f
+    int* n_valid[kMaxBatch];
+    float* normals[kMaxBatch];              // null: track only; else the 3 planes the fusion of frame f reads
+    ResultSnapshot* snap[kMaxBatch];        // null, or where the result of frame f is left
+    unsigned long long* flog[kMaxBatch];    // null, or frame f's entry of the debug frame log (words 2, 3)
+    unsigned long long* dbg;                // null, or [gridDim.x][4 passes][6] + [gridDim.x][4] %globaltimer stamps
 };
+// element f of a kernel-parameter array without a runtime-indexed access (which would copy the array to local memory)
+template <typename T>
+__device__ __forceinline__ T pick(T const (&a)[kMaxBatch], int f) {
+    T r = a[0];
+#pragma unroll
+    for (int i = 1; i < kMaxBatch; ++i) r = (f == i) ? a[i] : r;
+    return r;
+}
 
-#define GSDF_STAMP(i) do { if (ph.dbg && threadIdx.x == 0 && k < 4) ph.dbg[((size_t)blockIdx.x * 4 + k) * 6 + (i)] = global_ns(); } while (0)
+#define GSDF_STAMP(i) do { if (fb.dbg && threadIdx.x == 0 && k < 4) fb.dbg[((size_t)blockIdx.x * 4 + k) * 6 + (i)] = global_ns(); } while (0)
 // whole-launch stamps, after the per-pass ones: [gridDim.x][4] = entry, Gauss-Newton loop left, fusion done, exit
-#define GSDF_STAMPX(i) do { if (ph.dbg && threadIdx.x == 0) ph.dbg[(size_t)gridDim.x * 24 + (size_t)blockIdx.x * 4 + (i)] = global_ns(); } while (0)
+#define GSDF_STAMPX(i) do { if (fb.dbg && threadIdx.x == 0) fb.dbg[(size_t)gridDim.x * 24 + (size_t)blockIdx.x * 4 + (i)] = global_ns(); } while (0)
 
 // Frame-only work of the pipeline in ONE launch: each CTA compacts the z-valid pixels of its 32x16 tile (16 warps <->
 // its sixteen 8x4 sub-tiles, chained look-back over the CTAs for the exclusive prefix) and then computes the tile's
@@ -646,7 +656,7 @@ constexpr int kMaxPeers = 8;
 struct PeerExchange {
     unsigned long long* data[kMaxPeers];  // data[r]: rank r's exchange buffer (peer-mapped; data[rank] is local)
     int world, rank;                      // world <= 1: no exchange
-    unsigned int epoch0;                  // pass k of this launch carries the tag epoch0 + k + 1
+    unsigned int epoch0;                  // pass k of this launch (counted over its frames) carries the tag epoch0 + k + 1
     int* error;                           // set to 1 if a peer did not show up in time
 };
 
@@ -682,116 +692,112 @@ __device__ __forceinline__ void peer_allreduce_29(const PeerExchange& px, int k,
 
 template <int VARIANT>
 __global__ void __launch_bounds__(512, 2)
-track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr,
-             FrameState* st, float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp,
-             float* fuse_normals /* null: track only; else 3 planes used by the fusion at the end */,
-             const float* __restrict__ planes /* the 11 cached FALS planes */, Counters* ctr,
-             ResultSnapshot* snap /* null, or where the last CTA leaves the frame result */, FramePhases ph,
+track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
+             float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp,
+             const float* __restrict__ planes /* the 11 cached FALS planes */, Counters* ctr, FrameBatch fb,
              PeerExchange px) {
-    extern __shared__ __align__(16) unsigned char smem_dyn[];
     unsigned int barriers = 0;  // grid barriers passed so far in this launch
+    int pass_id = 0;            // Gauss-Newton passes run so far in this launch (buffer parity, tags of the peer exchange)
     __shared__ float s_pose7[8];
     __shared__ Pose s_pose;
     __shared__ float s_tot[kAccStride];
     __shared__ float s_warp[kTrackWarps][kAccStride];
     __shared__ int s_conv;
     GSDF_STAMPX(0);
-    if (threadIdx.x == 0 && ph.flog) flog_enter(ph.flog + 2);
-    if constexpr (kTrackThreads == NT_W * NT_H) if (ph.depth != nullptr) {
-        // compaction (look-back over segments) and normals (tiles) both depend only on the depth frame
-        __shared__ int s_cw[kTrackWarps];
-        __shared__ int s_cb;
-        for (int seg = blockIdx.x; seg < ph.nseg; seg += gridDim.x)
-            compact_segment<kTrackWarps>(ph.depth, g.w, g.h, g.z_min, g.z_max, ph.flags, ph.epoch, vlist, n_valid_ptr, seg,
-                                         ph.nseg, s_cw, &s_cb);
-        const size_t np = (size_t)g.w * g.h;
-        const int ntx = (g.w + NT_W - 1) / NT_W, nty = (g.h + NT_H - 1) / NT_H;
-        for (int tile = blockIdx.x; tile < ntx * nty; tile += gridDim.x) {
-            const int ty = tile / ntx, tx = tile - ty * ntx;
-            normals_tile(ph.depth, planes + 2 * np, planes + 3 * np, planes + 4 * np, planes + 5 * np, fuse_normals,
-                         fuse_normals + np, fuse_normals + 2 * np, g.w, g.h, ph.r, g.z_min, g.z_max, tx, ty,
-                         threadIdx.x & (NT_W - 1), threadIdx.x / NT_W, smem_dyn);
-            __syncthreads();
-        }
-        grid_barrier(ctr, ++barriers * gridDim.x);
-    }
-    // the three loads every CTA starts with (pose, list length, the thread's list entry) are issued together: the
-    // entry is fetched before it is known to exist (the list buffer holds one entry per pixel of the frame)
-    const int n_valid = __ldcg(n_valid_ptr);
     // pixel j of the list -> warp-sized chunk j/32 -> CTA (chunk % grid), warp (chunk / grid): a frame with fewer valid
-    // pixels than resident threads (the usual case: ~90 k of 151 k) is spread over ALL SMs instead of filling the
+    // pixels than resident threads (the usual case: ~90 k of 114 k) is spread over ALL SMs instead of filling the
     // first CTAs completely and leaving the rest idle (the slowest CTA sets the length of every pass)
     const int nthreads = gridDim.x * blockDim.x;
     const int gtid = (((threadIdx.x >> 5) * gridDim.x + blockIdx.x) << 5) | (threadIdx.x & 31);
-    int converged = 0, k = 0;
-    float valid_sum = 0.f;
-    unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
-    int cs = -1;
-    // the thread's first list entry stays in registers over the passes (with fewer valid pixels than resident threads
-    // it is the only one): one dependent L2 round trip less in every pass after the first
-    int2 e0 = make_int2(0, 0);
-    if (gtid < g.w * g.h) e0 = __ldcg(vlist + gtid);
+    // the pose the first frame starts from; later frames of the batch continue from the pose in shared memory
     if (threadIdx.x < 7) s_pose7[threadIdx.x] = __ldcg(&st->pose7[threadIdx.x]);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
-        s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
-    }
-    __syncthreads();
-    const bool has0 = gtid < n_valid;
-    for (k = 0; k < tp.max_iters; ++k) {
-        float acc[kAccTerms];
-#pragma unroll
-        for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
-        GSDF_STAMP(0);
-        if (has0) track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e0.x, __int_as_float(e0.y), acc, ck, cs);
-        for (int j = gtid + nthreads; j < n_valid; j += nthreads) {
-            const int2 e = __ldcg(vlist + j);
-            track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
+    for (int f = 0; f < fb.n; ++f) {
+        int2* vlist = pick(fb.vlist, f);
+        float* fuse_normals = pick(fb.normals, f);
+        unsigned long long* flog = pick(fb.flog, f);
+        if (f > 0) {
+            // every CTA's fusion of the previous frame (and its statistics) is complete before anyone reads the map again
+            grid_barrier(ctr, ++barriers * gridDim.x);
+            // CTA 0 publishes the previous frame; it does so before it arrives at this frame's first pass barrier, so no
+            // CTA can have added statistics of this frame yet
+            ResultSnapshot* prev = pick(fb.snap, f - 1);
+            if (blockIdx.x == 0 && prev != nullptr) write_snapshot(st, ctr, prev, px.world > 1 ? px.error : nullptr);
         }
-        GSDF_STAMP(1);
-        float* mine = partials + ((size_t)(k & 1) * gridDim.x + blockIdx.x) * kAccStride;
-        block_reduce_29<kTrackWarps>(acc, s_warp, mine);
-        GSDF_STAMP(2);
-        grid_barrier(ctr, ++barriers * gridDim.x);
-        GSDF_STAMP(3);
-        grid_reduce_29<kTrackWarps>(partials + (size_t)(k & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
-        if (px.world > 1) peer_allreduce_29(px, k, s_tot);
+        if (threadIdx.x == 0 && flog) flog_enter(flog + 2);
+        // the loads every frame starts with (list length, the thread's list entry, the pose) are issued together: the
+        // entry is fetched before it is known to exist (the list buffer holds one entry per pixel of the frame)
+        const int n_valid = __ldcg(pick(fb.n_valid, f));
+        int converged = 0, k = 0;
+        float valid_sum = 0.f;
+        unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
+        int cs = -1;
+        // the thread's first list entry stays in registers over the passes (with fewer valid pixels than resident
+        // threads it is the only one): one dependent L2 round trip less in every pass after the first
+        int2 e0 = make_int2(0, 0);
+        if (gtid < g.w * g.h) e0 = __ldcg(vlist + gtid);
         __syncthreads();
-        GSDF_STAMP(4);
         if (threadIdx.x == 0) {
-            valid_sum += s_tot[28];
-            s_conv = gauss_newton_step(s_tot, tp.damping, tp.thr_sq, s_pose7);
-            quat_to_R(s_pose7 + 3, s_pose.R);
+            quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
             s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
         }
         __syncthreads();
-        GSDF_STAMP(5);
-        if (s_conv) { converged = 1; break; }
-    }
-    GSDF_STAMPX(1);
-    if (blockIdx.x == 0) {
-        if (threadIdx.x < 7) st->pose7[threadIdx.x] = s_pose7[threadIdx.x];
-        if (threadIdx.x < kAccTerms) st->sums[threadIdx.x] = s_tot[threadIdx.x];
-        if (threadIdx.x == 0) {
-            st->n_valid = n_valid;
-            st->converged = converged;
-            st->iters = converged ? k : tp.max_iters;
-            st->track_iters += (unsigned long long)(converged ? k + 1 : tp.max_iters);
-            st->track_valid += (unsigned long long)valid_sum;
+        const bool has0 = gtid < n_valid;
+        for (k = 0; k < tp.max_iters; ++k, ++pass_id) {
+            float acc[kAccTerms];
+#pragma unroll
+            for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
+            GSDF_STAMP(0);
+            if (has0) track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e0.x, __int_as_float(e0.y), acc, ck, cs);
+            for (int j = gtid + nthreads; j < n_valid; j += nthreads) {
+                const int2 e = __ldcg(vlist + j);
+                track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
+            }
+            GSDF_STAMP(1);
+            float* mine = partials + ((size_t)(pass_id & 1) * gridDim.x + blockIdx.x) * kAccStride;
+            block_reduce_29<kTrackWarps>(acc, s_warp, mine);
+            GSDF_STAMP(2);
+            grid_barrier(ctr, ++barriers * gridDim.x);
+            GSDF_STAMP(3);
+            grid_reduce_29<kTrackWarps>(partials + (size_t)(pass_id & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
+            if (px.world > 1) peer_allreduce_29(px, pass_id, s_tot);
+            __syncthreads();
+            GSDF_STAMP(4);
+            if (threadIdx.x == 0) {
+                valid_sum += s_tot[28];
+                s_conv = gauss_newton_step(s_tot, tp.damping, tp.thr_sq, s_pose7);
+                quat_to_R(s_pose7 + 3, s_pose.R);
+                s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+            }
+            __syncthreads();
+            GSDF_STAMP(5);
+            if (s_conv) { converged = 1; ++pass_id; break; }
         }
+        GSDF_STAMPX(1);
+        if (blockIdx.x == 0) {
+            if (threadIdx.x < 7) st->pose7[threadIdx.x] = s_pose7[threadIdx.x];
+            if (threadIdx.x < kAccTerms) st->sums[threadIdx.x] = s_tot[threadIdx.x];
+            if (threadIdx.x == 0) {
+                st->n_valid = n_valid;
+                st->converged = converged;
+                st->iters = converged ? k : tp.max_iters;
+                st->track_iters += (unsigned long long)(converged ? k + 1 : tp.max_iters);
+                st->track_valid += (unsigned long long)valid_sum;
+            }
+            __threadfence();  // the snapshot of this frame is read back from L2 (by other threads of this CTA, or by the last CTA)
+        }
+        // main_scan_3d.cpp:261-264: integrate the frame at the pose just found, iff the optimisation converged — in the
+        // same launch (every CTA holds the final pose in shared memory; the map is not read by anyone else meanwhile)
+        if (fuse_normals != nullptr && (fb.fuse_mode == 1 || (fb.fuse_mode == 2 && converged))) {
+            const size_t np = (size_t)g.w * g.h;
+            unsigned int n_upd = 0, n_pts = 0;
+            fuse_work<VARIANT, true>(m, g, s_pose, vlist, n_valid, fuse_normals, fuse_normals + np, fuse_normals + 2 * np,
+                                     planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd);
+            fuse_stats_flush(ctr, n_pts, n_upd);
+        }
+        GSDF_STAMPX(2);
+        if (threadIdx.x == 0 && flog) flog_exit(flog + 2);
     }
-    // main_scan_3d.cpp:261-264: integrate the frame at the pose just found, iff the optimisation converged — in the
-    // same launch (every CTA holds the final pose in shared memory; the map is not read by anyone else meanwhile)
-    if (fuse_normals != nullptr && (ph.fuse_mode == 1 || (ph.fuse_mode == 2 && converged))) {
-        const size_t np = (size_t)g.w * g.h;
-        unsigned int n_upd = 0, n_pts = 0;
-        fuse_work<VARIANT, true>(m, g, s_pose, vlist, n_valid, fuse_normals, fuse_normals + np, fuse_normals + 2 * np,
-                                 planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd);
-        fuse_stats_flush(ctr, n_pts, n_upd);
-    }
-    GSDF_STAMPX(2);
-    {   // the last CTA to get here re-arms the grid barrier and publishes the frame result
+    {   // the last CTA to get here re-arms the grid barrier and publishes the result of the last frame
         __shared__ bool s_last;
         __threadfence();
         __syncthreads();
@@ -800,11 +806,11 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, int2* vlist, int* n_valid_ptr
         if (s_last) {
             __threadfence();
             if (threadIdx.x == 0) ctr->barrier = 0u;
+            ResultSnapshot* snap = pick(fb.snap, fb.n - 1);
             if (snap != nullptr) write_snapshot(st, ctr, snap, px.world > 1 ? px.error : nullptr);
         }
     }
     GSDF_STAMPX(3);
-    if (threadIdx.x == 0 && ph.flog) flog_exit(ph.flog + 2);
 }
 
 // Per-iteration variant (sharded maps): sums of this rank's pixels -> out29 (last-block-done), the caller

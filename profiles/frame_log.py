@@ -30,15 +30,8 @@ sdf.scan_submit(depth_dev=dev[0].data_ptr(), track=False)
 sdf.scan_collect()
 sdf._check(sdf.L.gsdf_debug_frame_log(sdf.h, None))
 hn = host.numpy()
-for i in range(1, N):
-    if mode == "dev":
-        sdf.scan_submit(depth_dev=dev[i].data_ptr(), track=True)
-    else:
-        sdf.scan_submit(depth_host=hn[i], track=True)
-    if sdf.scan_pending() == 4:
-        sdf.scan_collect()
-while sdf.scan_pending():
-    sdf.scan_collect()
+ptrs = [dev[i].data_ptr() if mode == "dev" else hn[i].ctypes.data for i in range(1, N)]
+sdf.scan_run(ptrs, on_device=(mode == "dev"))  # the frame loop in C (batches of frames per tracker launch)
 log = np.zeros((256, 4), np.uint64)
 sdf._check(sdf.L.gsdf_debug_frame_log(sdf.h, log.ctypes.data))
 t = log[1:N].astype(np.int64)
