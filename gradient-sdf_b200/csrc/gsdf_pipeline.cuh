@@ -715,6 +715,13 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
         int2* vlist = pick(fb.vlist, f);
         float* fuse_normals = pick(fb.normals, f);
         unsigned long long* flog = pick(fb.flog, f);
+        // the loads every frame starts with (list length, the thread's list entry) do not depend on the map: they are
+        // issued before the barrier that ends the previous frame; the entry is fetched before it is known to exist
+        // (the list buffer holds one entry per pixel of the frame) and stays in registers over the passes (with fewer
+        // valid pixels than resident threads it is the thread's only one)
+        const int n_valid = __ldcg(pick(fb.n_valid, f));
+        int2 e0 = make_int2(0, 0);
+        if (gtid < g.w * g.h) e0 = __ldcg(vlist + gtid);
         if (f > 0) {
             // every CTA's fusion of the previous frame (and its statistics) is complete before anyone reads the map again
             grid_barrier(ctr, ++barriers * gridDim.x);
@@ -724,17 +731,10 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
             if (blockIdx.x == 0 && prev != nullptr) write_snapshot(st, ctr, prev, px.world > 1 ? px.error : nullptr);
         }
         if (threadIdx.x == 0 && flog) flog_enter(flog + 2);
-        // the loads every frame starts with (list length, the thread's list entry, the pose) are issued together: the
-        // entry is fetched before it is known to exist (the list buffer holds one entry per pixel of the frame)
-        const int n_valid = __ldcg(pick(fb.n_valid, f));
         int converged = 0, k = 0;
         float valid_sum = 0.f;
         unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
         int cs = -1;
-        // the thread's first list entry stays in registers over the passes (with fewer valid pixels than resident
-        // threads it is the only one): one dependent L2 round trip less in every pass after the first
-        int2 e0 = make_int2(0, 0);
-        if (gtid < g.w * g.h) e0 = __ldcg(vlist + gtid);
         __syncthreads();
         if (threadIdx.x == 0) {
             quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
