@@ -431,9 +431,12 @@ def run_ours(args):
         # duration in the pipeline is taken from the in-kernel span log of an identical, separately run pass (events
         # cannot bracket it without putting operations between the frames); the per-kernel event brackets of the
         # unfused profile pass are kept in per_kernel_GBps.
-        kname = (f"track_kernel<{v}> (fused launch: Gauss-Newton loop, "
-                 f"{main['track_iters'] / max(1, n_a):.2f} passes, + fusion of the frame)")
-        per_launch_bytes, per_launch_ms = main["fused_bytes_per_frame"], an["track_fuse_kernel"] / 1e3
+        # gsdf_scan_run gives the tracker up to 4 frames per launch: launches in the timed region = one frame-only
+        # kernel per frame + the tracker launches
+        fpl = args.steps / max(1, main["launches"] - args.steps)
+        kname = (f"track_kernel<{v}> (fused launch over {fpl:.2f} frames: per frame the Gauss-Newton loop, "
+                 f"{main['track_iters'] / max(1, n_a):.2f} passes, + the fusion)")
+        per_launch_bytes, per_launch_ms = main["fused_bytes_per_frame"] * fpl, an["track_fuse_kernel"] * fpl / 1e3
     achieved = per_launch_bytes / max(per_launch_ms, 1e-12) / 1e6  # GB/s
     step_ms = main["ms_per_step"] * args.steps
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "peak_source": peak_src,
