@@ -24,6 +24,7 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 W, H = 320, 240
 frames, poses, K, _ = synth.make_sequence(800, W, H, noise=False)
 frames = frames[:8]
+dev_frames = torch.from_numpy(frames).cuda()
 nest = pkg.NormalEstimator(W, H, K, 11)
 vs, T = np.float32(0.01), np.float32(0.05)
 ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
@@ -39,6 +40,15 @@ def run(sdf):
         sdf.scan_submit(depth_host=frames[i], track=True)
         out.append(sdf.scan_collect())
     return out
+
+
+def run_loop(sdf):
+    """the same frames through gsdf_scan_run (several frames per tracker launch, device-resident frames)"""
+    sdf.scan_set_pose(ident)
+    sdf.scan_set_tracker(25, 1e-3, 1.0)
+    sdf.scan_submit(depth_dev=dev_frames[0].data_ptr(), track=False)
+    out = [sdf.scan_collect()]
+    return out + sdf.scan_run([dev_frames[i].data_ptr() for i in range(1, len(frames))], on_device=True)
 
 
 def comm_id():
@@ -79,6 +89,10 @@ def check_variant(cls, tag):
     dist.barrier()
     got = run(sharded)
     check(got, "p2p")
+    sharded.reset()
+    dist.barrier()
+    got = run_loop(sharded)
+    check(got, "p2p, frame loop in one call")
     upd = torch.tensor([sum(r.updates for r in got)], dtype=torch.int64, device="cuda")
     dist.all_reduce(upd)
     assert abs(int(upd) - sum(r.updates for r in ref)) <= 1e-3 * sum(r.updates for r in ref), tag
