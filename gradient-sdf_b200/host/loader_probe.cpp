@@ -1,0 +1,40 @@
+// Test helper for the dataset loaders (no GPU, no library): loads every frame of a dataset directory through
+// img_loader.h and writes
+//     <out>.f32   the depth frames, float32 metres, concatenated
+//     stdout      one line per frame: "<depth timestamp> <rgb timestamp> <width> <height>", then "K k00 ... k22"
+//   loader_probe <tum|synth|printed|rw> <dataset dir with trailing /> <out prefix>
+#include <cstdio>
+
+#include "img_loader.h"
+
+int main(int argc, char** argv) {
+    if (argc != 4) { std::fprintf(stderr, "usage: loader_probe <type> <dir/> <out prefix>\n"); return 2; }
+    const std::string type = argv[1], dir = argv[2], out = argv[3];
+    ImageLoader* loader = nullptr;
+    if (type == "tum") loader = new TumrgbdLoader(dir);
+    else if (type == "synth") loader = new SynthLoader(dir);
+    else if (type == "printed") loader = new Printed3dLoader(dir);
+    else if (type == "rw" || type == "redwood") loader = new RedwoodLoader(dir);
+    else { std::fprintf(stderr, "unknown dataset type\n"); return 2; }
+    FILE* f = std::fopen((out + ".f32").c_str(), "wb");
+    if (!f) return 2;
+    std::streambuf* keep = std::cout.rdbuf(std::cerr.rdbuf());  // the loaders chat on cout like the reference's: keep stdout clean
+    cv::Mat color, depth;
+    std::vector<std::string> lines;
+    while (loader->load_next(color, depth)) {
+        std::fwrite(depth.data, sizeof(float), (size_t)depth.rows * depth.cols, f);
+        lines.push_back(loader->depth_timestamp() + " " + loader->rgb_timestamp() + " " + std::to_string(depth.cols) + " " +
+                        std::to_string(depth.rows));
+    }
+    std::fclose(f);
+    std::cout.rdbuf(keep);
+    for (const auto& l : lines) std::printf("%s\n", l.c_str());
+    if (loader->load_intrinsics()) {
+        const Mat3f K = loader->K();
+        std::printf("K");
+        for (int i = 0; i < 9; ++i) std::printf(" %.9g", K.m[i]);
+        std::printf("\n");
+    }
+    delete loader;
+    return 0;
+}

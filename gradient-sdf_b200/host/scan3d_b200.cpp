@@ -2,8 +2,9 @@
 // sdf_tracker.h.  Same options, same ordering contract (track against the map, fuse only if converged; first frame
 // fused at identity or at the first ground-truth pose; with a pose file every frame is fused without tracking),
 // same output files (<results>_poses.txt, <results>gradient_sdf_cloud_final.ply, <results>gradient_sdf_grid_info.txt,
-// ..._sdf_d.txt, ..._sdf_weight.txt, ..._sdf_n{0,1,2}.txt).  Dataset loaders (PNG decoding through OpenCV,
-// img_loader/*.h) are out of scope: --data-type raw reads
+// ..._sdf_d.txt, ..._sdf_weight.txt, ..._sdf_n{0,1,2}.txt).  --data-type tum | synth | printed | rw | redwood reads the
+// reference's dataset conventions through img_loader.h (16-bit depth PNGs decoded with zlib, no OpenCV); in addition
+// --data-type raw reads
 //     <input>/intrinsics.txt   3x3 row-major, as ImageLoader::load_intrinsics (ImageLoader.h:138-157)
 //     <input>/frames.f32       n frames of height*width float32 depths in metres (what convertTo yields, :172)
 //     <input>/meta.txt         "width height n_frames"
@@ -16,6 +17,7 @@
 #include <iomanip>
 #include <sstream>
 
+#include "img_loader.h"
 #include "sdf_tracker.h"
 
 namespace {
@@ -61,11 +63,16 @@ int main(int argc, char* argv[]) {
         std::cerr << "Your specified scan type is not supported (yet)." << std::endl;
         return 1;
     }
-    if (dtype != "raw") {  // main_scan_3d.cpp:123-139; the PNG loaders are not part of this path
+    if (!input.empty() && input.back() != '/') input += '/';
+    ImageLoader* loader = nullptr;  // main_scan_3d.cpp:116-157
+    if (dtype == "tum") loader = new TumrgbdLoader(input);
+    else if (dtype == "synth") loader = new SynthLoader(input);
+    else if (dtype == "printed") loader = new Printed3dLoader(input);
+    else if (dtype == "rw" || dtype == "redwood") loader = new RedwoodLoader(input);
+    else if (dtype != "raw") {
         std::cerr << "Your specified dataset type is not supported (yet)." << std::endl;
         return 1;
     }
-    if (!input.empty() && input.back() != '/') input += '/';
 
     // intrinsics (ImageLoader::load_intrinsics)
     Mat3f K;
@@ -78,12 +85,13 @@ int main(int argc, char* argv[]) {
     for (int i = 0; i < 3; ++i) std::cout << K(i, 0) << " " << K(i, 1) << " " << K(i, 2) << std::endl;
     int width = 0, height = 0;
     size_t n_frames = 0;
-    {
+    std::ifstream frames;
+    if (!loader) {
         std::ifstream f(input + "meta.txt");
         if (!f.is_open() || !(f >> width >> height >> n_frames)) { std::cerr << "No meta.txt in " << input << "!" << std::endl; return 1; }
+        frames.open(input + "frames.f32", std::ios::binary);
+        if (!frames.is_open()) { std::cerr << "No frames.f32 in " << input << "!" << std::endl; return 1; }
     }
-    std::ifstream frames(input + "frames.f32", std::ios::binary);
-    if (!frames.is_open()) { std::cerr << "No frames.f32 in " << input << "!" << std::endl; return 1; }
 
     // ground-truth poses (ImageLoader::load_pose)
     std::vector<SE3> poses;
@@ -105,9 +113,15 @@ int main(int argc, char* argv[]) {
         else { std::cout << poses.size() << " GT poses are loaded!" << std::endl; GT_pose = true; }
     }
 
-    T.tic();
-    cv::NormalEstimator<float>* NEst = new cv::NormalEstimator<float>(width, height, K, cv::Size(2 * 5 + 1, 2 * 5 + 1));
-    T.toc("Init normal estimation");
+    // the estimator needs the frame size: with a PNG dataset it is created when the first frame has been decoded
+    // (the reference hard-codes 640x480, main_scan_3d.cpp:182)
+    cv::NormalEstimator<float>* NEst = nullptr;
+    auto make_estimator = [&]() {
+        T.tic();
+        NEst = new cv::NormalEstimator<float>(width, height, K, cv::Size(2 * 5 + 1, 2 * 5 + 1));
+        T.toc("Init normal estimation");
+    };
+    if (!loader) make_estimator();
     const float truncation = truncation_factor * voxel_size;  // main_scan_3d.cpp:191
 
     Sdf* tSDF = nullptr;
@@ -115,7 +129,15 @@ int main(int argc, char* argv[]) {
     std::ofstream pose_file(output + "_poses.txt");
     std::vector<float> depth_buf((size_t)width * height);
     cv::Mat color, depth(height, width, CV_32FC1, depth_buf.data());
+    std::string cur_stamp;  // loader->depth_timestamp(), what main_scan_3d.cpp:276 writes in front of every pose
     auto load_next = [&]() -> bool {
+        if (loader) {
+            if (!loader->load_next(color, depth)) return false;
+            cur_stamp = loader->depth_timestamp();
+            if (!NEst) { width = depth.cols; height = depth.rows; make_estimator(); }
+            if (depth.cols != width || depth.rows != height) { std::cerr << "frame size changed" << std::endl; return false; }
+            return true;
+        }
         frames.read((char*)depth_buf.data(), (std::streamsize)(depth_buf.size() * sizeof(float)));
         return (size_t)frames.gcount() == depth_buf.size() * sizeof(float);
     };
@@ -125,7 +147,7 @@ int main(int argc, char* argv[]) {
     size_t n_tracked = 0, n_fused = 0;
     auto write_pose = [&](size_t i, const SE3& p) {  // main_scan_3d.cpp:268-280
         const float* d = p.data();
-        pose_file << (i < stamps.size() ? stamps[i] : std::to_string(i)) << " " << d[0] << " " << d[1] << " " << d[2] << " "
+        pose_file << (loader ? cur_stamp : (i < stamps.size() ? stamps[i] : std::to_string(i))) << " " << d[0] << " " << d[1] << " " << d[2] << " "
                   << d[3] << " " << d[4] << " " << d[5] << " " << d[6] << "\n";
     };
     int pending = 0;
@@ -171,7 +193,7 @@ int main(int argc, char* argv[]) {
         } else if (pipelined) {
             // the host buffer is reused for the next frame: wait for the copy stream before overwriting it
             if (pending == 4) collect_one();
-            if (gsdf_scan_submit(tSDF->gpu(), depth_buf.data(), nullptr, GSDF_SCAN_TRACK_FUSE) != GSDF_OK) {
+            if (gsdf_scan_submit(tSDF->gpu(), (const float*)depth.data, nullptr, GSDF_SCAN_TRACK_FUSE) != GSDF_OK) {
                 std::cerr << gsdf_last_error(tSDF->gpu()) << std::endl;
                 return 2;
             }

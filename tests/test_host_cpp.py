@@ -29,8 +29,10 @@ def test_driver_builds_and_rejects_like_the_reference():
     assert BIN.exists(), "run __graft_entry__.build()"
     r = run(["--scan-type", "voxel-gp", "--data-type", "raw"])
     assert r.returncode == 1 and "Your specified scan type is not supported (yet)." in r.stderr  # main_scan_3d.cpp:112
-    r = run(["--scan-type", "grad-sdf", "--data-type", "tum"])
-    assert r.returncode == 1 and "Your specified dataset type is not supported (yet)." in r.stderr
+    r = run(["--scan-type", "grad-sdf", "--data-type", "kitti"])
+    assert r.returncode == 1 and "Your specified dataset type is not supported (yet)." in r.stderr  # main_scan_3d.cpp:137
+    r = run(["--scan-type", "grad-sdf", "--data-type", "tum", "--input", "/nonexistent"])
+    assert r.returncode == 1 and "No intrinsics file found" in r.stderr
     r = run(["--scan-type", "grad-sdf", "--data-type", "raw", "--input", "/nonexistent"])
     assert r.returncode == 1 and "No intrinsics file found" in r.stderr  # main_scan_3d.cpp:163
 
@@ -99,3 +101,35 @@ def test_scan3d_driver_ground_truth_poses(pkg, po, synth, tmp_path):
         orc.update(frames[i], p)
     d = np.loadtxt(str(out) + "gradient_sdf_sdf_d.txt")
     assert len(d) == orc.voxel_count()
+
+
+@pytest.mark.gpu
+def test_scan3d_driver_reads_the_reference_dataset_conventions(synth, tmp_path):
+    """--data-type synth (16-bit PNGs, depth/%03d.png, SynthLoader.h) must give the poses of --data-type raw on the same
+    frames, and label them with the loader's depth timestamps (main_scan_3d.cpp:276)."""
+    cv2 = pytest.importorskip("cv2")
+    W, H = 320, 240
+    frames, poses, K, _ = synth.make_sequence(400, W, H)
+    frames = frames[:6]
+    raw = tmp_path / "raw"
+    png = tmp_path / "png"
+    raw.mkdir()
+    (png / "depth").mkdir(parents=True)
+    (png / "rgb").mkdir()
+    write_raw(raw, frames, K)
+    np.savetxt(png / "intrinsics.txt", K.reshape(3, 3), fmt="%.9g")
+    for i, f in enumerate(frames):
+        u16 = np.round(f.astype(np.float64) * 1000).astype(np.uint16)
+        assert cv2.imwrite(str(png / "depth" / f"{i + 1:03d}.png"), u16)
+        assert cv2.imwrite(str(png / "rgb" / f"{i + 1:03d}.png"), np.zeros((H, W, 3), np.uint8))
+    res = {}
+    for kind, d in (("raw", raw), ("synth", png)):
+        out = tmp_path / f"res_{kind}"
+        r = run(["--input", str(d), "--results", str(out), "--scan-type", "base-sdf", "--data-type", kind,
+                 "--voxel-size", "0.01", "--trunc", "5", "--capacity-log2", "15", "--last", "5"])
+        assert r.returncode == 0, r.stderr[-2000:]
+        res[kind] = [l.split() for l in Path(str(out) + "_poses.txt").read_text().splitlines()]
+    assert [l[0] for l in res["synth"]] == [f"{i + 1:03d}" for i in range(6)]
+    a = np.array([[float(x) for x in l[1:]] for l in res["raw"]])
+    b = np.array([[float(x) for x in l[1:]] for l in res["synth"]])
+    assert a.shape == b.shape == (6, 7) and np.abs(a - b).max() < 5e-5
