@@ -35,7 +35,7 @@ EXPORTS = [
     "gsdf_track", "gsdf_query", "gsdf_voxel_count", "gsdf_download", "gsdf_pose_matrix", "gsdf_pose_apply_increment",
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
-    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_scan_run", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_debug_frame_log", "gsdf_p2p_export", "gsdf_p2p_connect", "gsdf_comm_unique_id", "gsdf_comm_init",
+    "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_scan_run", "gsdf_upload", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_debug_frame_log", "gsdf_p2p_export", "gsdf_p2p_connect", "gsdf_comm_unique_id", "gsdf_comm_init",
     "gsdf_version",
 ]
 
@@ -117,6 +117,7 @@ def lib() -> C.CDLL:
     L.gsdf_accumulate_noalloc.argtypes = [H, _f32p, _f32p, C.c_int32, C.c_void_p]
     L.gsdf_debug_track_timers.argtypes = [H, C.c_void_p, C.POINTER(C.c_int32)]
     L.gsdf_debug_frame_log.argtypes = [H, C.c_void_p]
+    L.gsdf_upload.argtypes = [H, C.c_int64, _i32p, _f32p, _f32p, _f32p]
     L.gsdf_scan_run.argtypes = [H, C.POINTER(C.c_void_p), C.c_int64, C.c_int32, C.c_int32, C.POINTER(FrameResult),
                                 C.POINTER(C.c_int64)]
     L.gsdf_trace_enable.argtypes = [H, C.c_int32]
@@ -398,6 +399,14 @@ class Sdf:
         n, b = C.c_int64(0), C.c_int64(0)
         self._check(self.L.gsdf_voxel_count(self.h, C.byref(n), C.byref(b)))
         return int(n.value), int(b.value)
+
+    def upload(self, keys, dist, weight, grad=None):
+        """Checkpoint / resume: set the listed voxels (arrays as returned by download())."""
+        k = np.ascontiguousarray(keys, np.int32).reshape(-1, 3)
+        d, w = _f32(dist).reshape(-1), _f32(weight).reshape(-1)
+        g = None if grad is None else _f32(grad).reshape(-1, 3)
+        assert len(d) == len(w) == len(k) and (g is None or len(g) == len(k))
+        self._check(self.L.gsdf_upload(self.h, len(k), k.ctypes.data_as(_i32p), _fp(d), _fp(w), _fp(g) if g is not None else None))
 
     def download(self, sort: bool = True):
         n, _ = self.voxel_count()

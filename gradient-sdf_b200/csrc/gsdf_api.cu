@@ -925,6 +925,35 @@ gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* di
     return s;
 }
 
+gsdf_status gsdf_upload(gsdf_handle h, int64_t n, const int32_t* keys, const float* dist, const float* weight, const float* grad) {
+    if (!h || n < 0) return GSDF_ERR_INVALID;
+    if (n == 0) return GSDF_OK;
+    if (!keys || !dist || !weight || (h->cfg.variant == GSDF_GRAD_SDF && !grad)) return GSDF_ERR_INVALID;
+    if (h->seq_submitted != h->seq_collected) { h->err = "gsdf_upload: frames are pending, collect them first"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    int* d_keys = nullptr;
+    float* d_f = nullptr;
+    CUDA_TRY(h, cudaMalloc(&d_keys, sizeof(int) * 3 * n));
+    if (cudaMalloc(&d_f, sizeof(float) * 5 * n) != cudaSuccess) { cudaFree(d_keys); h->err = "cudaMalloc(upload)"; return GSDF_ERR_CUDA; }
+    gsdf_status s = GSDF_OK;
+    do {
+        cudaMemcpyAsync(d_keys, keys, sizeof(int) * 3 * n, cudaMemcpyHostToDevice, h->stream);
+        cudaMemcpyAsync(d_f, dist, sizeof(float) * n, cudaMemcpyHostToDevice, h->stream);
+        cudaMemcpyAsync(d_f + n, weight, sizeof(float) * n, cudaMemcpyHostToDevice, h->stream);
+        if (grad) cudaMemcpyAsync(d_f + 2 * n, grad, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, h->stream);
+        s = by_variant(h, [&](auto V) {
+            upload_kernel<decltype(V)::value><<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(
+                h->view, (long long)n, d_keys, d_f, d_f + n, d_f + 2 * n, h->d_ctr);
+            return check_launch(h, "upload_kernel");
+        });
+        if (s != GSDF_OK) break;
+        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { h->err = "upload: stream sync failed"; s = GSDF_ERR_CUDA; break; }
+        s = check_overflow(h);
+    } while (0);
+    cudaFree(d_keys); cudaFree(d_f);
+    return s;
+}
+
 // ---- the asynchronous frame pipeline ------------------------------------------------------------------------
 gsdf_status gsdf_scan_set_pose(gsdf_handle h, const float* pose7) {
     if (!h || !pose7) return GSDF_ERR_INVALID;

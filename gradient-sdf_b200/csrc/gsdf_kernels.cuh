@@ -565,4 +565,30 @@ download_kernel(MapView m, unsigned long long* cursor, long long max_n, int* __r
     }
 }
 
+// Restore voxels from a download (checkpoint / resume; no counterpart in the reference): one thread per listed voxel,
+// the block is found or inserted, the voxel's accumulators are SET to {dist * W, grad, W}.  A sharded map keeps only
+// what its ownership rule assigns to it (including base-sdf halo copies), so every rank may be handed the whole list.
+template <int VARIANT>
+__global__ void __launch_bounds__(256)
+upload_kernel(MapView m, long long n, const int* __restrict__ keys, const float* __restrict__ dist,
+              const float* __restrict__ weight, const float* __restrict__ grad, Counters* ctr) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float W = weight[i];
+    if (!(W > 0.f)) return;
+    const int vx = keys[3 * i], vy = keys[3 * i + 1], vz = keys[3 * i + 2];
+    const unsigned long long key = block_key_of(vx, vy, vz);
+    if (!shard_keeps<VARIANT>(m.world, m.rank, key, vx, vy, vz)) return;
+    const int slot = map_find_or_insert(m, key, ctr);
+    if (slot < 0) { atomicAdd(&ctr->overflow, 1u); return; }
+    const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
+    const float S = __fmul_rn(dist[i], W);
+    if (VARIANT == 0) {
+        m.acc4[addr] = make_float4(S, grad[3 * i], grad[3 * i + 1], grad[3 * i + 2]);
+        m.accW[addr] = W;
+    } else {
+        m.acc2[addr] = make_float2(W, S);
+    }
+}
+
 }  // namespace gsdf

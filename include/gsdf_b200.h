@@ -129,6 +129,14 @@ gsdf_status gsdf_voxel_count(gsdf_handle h, int64_t* n_voxels, int64_t* n_blocks
 gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* dist, float* weight, float* grad,
                           int64_t* n_out);
 
+/* Checkpoint / resume, no counterpart in the reference (which can only dump the final map as text, save_sdf): sets the
+ * listed voxels to the given state — the arrays are what gsdf_download returns (grad may be NULL for base-sdf); voxels
+ * with weight <= 0 are skipped.  Into an empty map (gsdf_reset) this restores a downloaded one: same key set, same
+ * weight and grad, dist within one ulp (the map stores dist * weight).  A sharded map keeps only what its ownership
+ * rule assigns to this rank, so every rank may be given the whole list.  GSDF_ERR_CAPACITY if the block hash fills up. */
+gsdf_status gsdf_upload(gsdf_handle h, int64_t n, const int32_t* keys, const float* dist, const float* weight,
+                        const float* grad);
+
 /* -- the frame pipeline: main_scan_3d.cpp:208-266 without the host in the loop --------------------------------
  * The reference's loop body is "optimize(depth); if (converged) update(depth, pose())" with the pose living in the
  * optimizer object.  Here the pose, the converged flag and the frame's compacted pixel list live on the device, so a
