@@ -510,8 +510,11 @@ def run_ours(args):
                          "once (L2 = 126 MB); the map is state carried from frame to frame by design; "
                          "value_l2_flushed_unpipelined = one frame in flight, 256 MiB L2 flush before each",
                    "timing": "K / device-timeline span (CUDA events on the library's stream) from the first timed submit "
-                             "to the last result, up to 4 frames in flight, no untimed gaps, max over ranks",
-                   "api": "gsdf_scan_run (the frame loop: gsdf_scan_submit / gsdf_scan_collect, 4 frames in flight)"},
+                             "to the last result, up to 12 frames in flight, no untimed gaps, max over ranks; every pass = "
+                             "reset map, frame 0 fused, W warm-up frames, K timed frames; one whole pass is run and "
+                             "discarded before the first timed one",
+                   "api": "gsdf_scan_run (the frame loop in C: up to 4 frames per tracker launch, uploads and frame-only "
+                          "kernels ahead of it)"},
         "voxel_updates_per_s": main["voxel_updates_per_s"], "updates_per_frame": main["updates_per_frame"],
         "converged_steps": main["converged_steps"], "gn_iterations_per_step": iters_per_step,
         "map": {"voxels": main["voxels"], "blocks": main["blocks"]},
