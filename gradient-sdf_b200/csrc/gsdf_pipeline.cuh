@@ -1,31 +1,28 @@
-// Frame pipeline kernels (v2): everything a frame needs runs on the stream without a host round trip.
+// Frame pipeline kernels: everything a frame needs runs on the streams without a host round trip.
 //
-//   compact_tiles_kernel                      deterministic single-pass compaction of the z-valid pixels of the frame
-//                                             into vlist = {(y<<16)|x, z} in 8x4-tile order, so that every lane of
-//                                             every warp downstream has work (the sphere scenes have ~20 % valid
-//                                             pixels, spatially clustered: a per-pixel grid leaves most warps idle
-//                                             and a few with all the work) and a warp's pixels are neighbours;
-//   track_kernel<V>                           the WHOLE Gauss-Newton loop of RigidPointOptimizer::optimize_sampled
-//                                             (RigidPointOptimizerOmp.cpp:44-106) as one persistent cooperative
-//                                             kernel: per-pixel lookup + Jacobian, warp -> block -> grid tree
-//                                             reduction of the 29 sums, and — redundantly in every CTA, on
-//                                             identical data, so no broadcast is needed — the 6x6 LLT solve,
-//                                             the stopping test and pose <- exp(-xi) * pose.  One grid.sync per
-//                                             iteration, no host involvement until the loop ends;
-//   accumulate_list_kernel<V> + solve_kernel  the same split into per-iteration launches, for sharded maps where
-//                                             an NCCL all-reduce sits between the sums and the solve;
-//   fuse_list_kernel<V>                       fusion over vlist, pose and converged flag read from the device;
-//   normals_tile_kernel                       FALS normals, skipping tiles without any valid pixel.
+//   normals_compact_kernel                    the frame-only work in one launch per frame (side stream): deterministic
+//                                             single-pass compaction of the z-valid pixels into vlist = {(y<<16)|x, z}
+//                                             in tile order (so that every lane of every warp downstream has work and a
+//                                             warp's pixels are neighbours) + FALS normals of the tiles that hold any;
+//   track_kernel<V>                           main stream, persistent cooperative launch over up to kMaxBatch frames;
+//                                             per frame the WHOLE Gauss-Newton loop of
+//                                             RigidPointOptimizer::optimize_sampled (RigidPointOptimizerOmp.cpp:44-106):
+//                                             per-pixel lookup + Jacobian, warp -> CTA -> grid reduction of the 29 sums
+//                                             (across GPUs too: allreduce over NVLink peer memory), and — redundantly in
+//                                             every CTA, on identical data, so no broadcast is needed — the 6x6 LLT
+//                                             solve, the stopping test and pose <- exp(-xi) * pose; then the fusion of
+//                                             the frame iff converged (main_scan_3d.cpp:261), then the next frame;
+//   compact_tiles_kernel, normals_tile_kernel the two halves of the frame-only work as separate launches (fine-grained
+//                                             entry points, per-kernel profiling);
+//   fuse_list_kernel<V>                       fusion over vlist as its own launch (gsdf_integrate*, profiling);
+//   accumulate_list_kernel<V> + solve_kernel  the Gauss-Newton loop split into per-iteration launches, for sharded maps
+//                                             without a peer connection: an NCCL all-reduce sits between the two.
 #pragma once
-
-#include <cooperative_groups.h>
 
 #include "gsdf_kernels.cuh"
 #include "gsdf_pose.cuh"
 
 namespace gsdf {
-
-namespace cg = cooperative_groups;
 
 __device__ __forceinline__ unsigned long long global_ns() {
     unsigned long long t;
@@ -85,7 +82,6 @@ __device__ __forceinline__ void write_snapshot(const FrameState* st, const Count
     }
 }
 
-__global__ void snapshot_kernel(const FrameState* st, const Counters* ctr, ResultSnapshot* out) { write_snapshot(st, ctr, out); }
 
 constexpr int kTileW = 8, kTileH = 4;           // one warp <-> one 8x4 pixel tile
 constexpr int kTilesPerWarp = 8;
