@@ -220,6 +220,41 @@ def test_capacity_overflow_is_reported(pkg, synth):
     sdf.close()
 
 
+def test_frame_loop_reports_a_full_hash_and_leaves_the_handle_usable(pkg, synth):
+    """gsdf_scan_run stops at the first error, drains what is in flight and keeps the error; after gsdf_reset the same
+    handle runs again (with room this time nothing is dropped)."""
+    W, H = 160, 120
+    frames, poses, K, _ = synth.make_sequence(100, W, H)
+    nest = pkg.NormalEstimator(W, H, K, 11)
+    ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+    sdf = pkg.MapPixelSdf(0.01, 0.05, nest, log2_capacity=7)  # 128 blocks: the first frame fits, the orbit does not
+    sdf.scan_set_pose(ident)
+    sdf.scan_submit(depth_host=frames[0], track=False)
+    try:
+        sdf.scan_collect()
+        with pytest.raises(pkg.GsdfError) as e:
+            sdf.scan_run([frames[i].ctypes.data for i in range(1, 40)], on_device=False)
+    except pkg.GsdfError as first:  # already the first frame overflowed
+        e = type("E", (), {"value": first})
+    assert e.value.status == 3 and "log2_capacity" in str(e.value)
+    assert sdf.scan_pending() == 0
+    sdf.close()
+    big = pkg.MapPixelSdf(0.01, 0.05, nest, log2_capacity=14)
+    big.scan_set_pose(ident)
+    big.scan_submit(depth_host=frames[0], track=False)
+    big.scan_collect()
+    res = big.scan_run([frames[i].ctypes.data for i in range(1, 10)], on_device=False)
+    assert len(res) == 9 and all(r.converged for r in res)
+    big.reset()
+    assert big.voxel_count() == (0, 0)
+    big.scan_set_pose(ident)
+    big.scan_submit(depth_host=frames[0], track=False)
+    big.scan_collect()
+    res2 = big.scan_run([frames[i].ctypes.data for i in range(1, 10)], on_device=False)
+    assert [r.iters for r in res2] == [r.iters for r in res]
+    big.close()
+
+
 def test_full_size_properties(pkg, synth):
     """640x480 at BASELINE sizes: size-independent properties (no oracle needed at this size).
     Fusion is a linear accumulation: fusing the same frame twice doubles W, S and G and leaves dist unchanged;
