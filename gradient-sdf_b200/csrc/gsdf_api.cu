@@ -1033,7 +1033,7 @@ gsdf_status submit_frames(gsdf_map* h, const float* const* host, const float* co
             s = launch_normals(h, frame, nbuf, side, true);
         } else {
             // frames already in flight: this one's frame-only work is not on the critical path, keep its footprint small
-            s = launch_normals_compact(h, frame, nbuf, side, h->shadow_side && (!idle || i > 0), seq);
+            s = launch_normals_compact(h, frame, nbuf, side, h->shadow_side && !idle, seq);
         }
         if (s != GSDF_OK) return s;
         trace_mark(h, "side:normals", side);
@@ -1152,14 +1152,18 @@ gsdf_status gsdf_scan_run(gsdf_handle h, const float* const* frames, int64_t n, 
     // tracked, and two whose uploads and frame-only kernels run ahead of it.
     const bool batches = batch_capable(h) && mode == GSDF_SCAN_TRACK_FUSE && h->batch_frames > 1;
     int64_t submitted = 0, collected = 0;
+    int launches = 0;
     gsdf_status s = GSDF_OK;
     while (collected < n) {
         while (submitted < n) {
-            const int nb = batches ? (int)std::min<int64_t>(h->batch_frames, n - submitted) : 1;
+            // batch sizes ramp up 1, 2, 4, ...: the first tracker launch waits for ONE frame-only kernel, not for four
+            const int ramp = std::min(h->batch_frames, 1 << std::min(launches, 3));
+            const int nb = batches ? (int)std::min<int64_t>(ramp, n - submitted) : 1;
             if (submitted - collected + nb > (batches ? kRing : kMaxPending)) break;
             s = submit_frames(h, on_device ? nullptr : frames + submitted, on_device ? frames + submitted : nullptr, nb, mode);
             if (s != GSDF_OK) break;
             submitted += nb;
+            ++launches;
         }
         if (s != GSDF_OK) break;
         s = gsdf_scan_collect(h, results + collected);
