@@ -1,0 +1,51 @@
+"""The bench lines committed under profiles/ carry every key of the driver's contract (CPU only: checks the recorded
+lines of the last GPU run, and that bench.py parses its flags)."""
+import json
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+REQUIRED = ["metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+            "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "clocks", "roofline", "cpu_baseline"]
+
+
+def _last_line(name):
+    return json.loads((ROOT / "profiles" / name).read_text().strip().splitlines()[-1])
+
+
+@pytest.mark.parametrize("name", ["r1f_bench_base.json", "r1f_bench_grad.json"])
+def test_recorded_bench_line_has_the_contract_keys(name):
+    d = _last_line(name)
+    assert all(k in d for k in REQUIRED), [k for k in REQUIRED if k not in d]
+    assert d["unit"] == "frames/s" and d["higher_is_better"] is True and d["vs_baseline"] is None and d["dtype"] == "f32"
+    assert "workload" in d["config"] and "model" not in d["config"]
+    e = d["e2e"]
+    assert e["unit"] == d["unit"] and e["h2d_bytes_per_step"] == 640 * 480 * 4 and e["d2h_bytes_per_step"] > 0
+    assert e["value"] != d["value"]  # measured separately, not a copy of the device-resident figure
+    r = d["roofline"]
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
+    c = d["cpu_baseline"]
+    assert c["kind"] == "reference" and c["cores"] >= 1 and c["unit"] == d["unit"] and c["sample"]
+    assert d["gpu_launches"] > 0 and d["clocks"]["reasons"] == [] and d["clocks"]["sm_mhz"] <= d["clocks"]["sm_max_mhz"]
+    assert d["steps"] >= 1 and d["warmup"] >= 3
+
+
+def test_recorded_reference_arm_line():
+    d = _last_line("r1f_bench_reference.json")
+    assert d["impl"] == "reference" and d["gpu_launches"] == 0 and d["unit"] == "frames/s"
+    assert d["e2e"] == {"value": d["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["cpu_baseline"]["value"] == d["value"] and d["cpu_baseline"]["kind"] == "reference"
+    ours = _last_line("r1f_bench_base.json")
+    assert d["metric"] == ours["metric"] and d["config"]["workload"] == ours["config"]["workload"]
+
+
+def test_bench_refuses_to_run_without_a_gpu_instead_of_falling_back():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--steps", "2", "--warmup", "1"], capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
