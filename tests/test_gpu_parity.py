@@ -198,6 +198,35 @@ def test_tracking_trajectory_vs_oracle(pkg, po, synth):
         assert np.abs(opt.pose()[:3] - poses[i][:3]).max() < 0.02
 
 
+def test_frame_loop_trajectory_vs_oracle_at_bench_size(pkg, po, synth):
+    """The bench's own path (gsdf_scan_run: frame-only kernel + tracker launches over several frames) on its own
+    workload (C2: base-sdf, 1 cm, 640x480, noisy depth) against the oracle's optimize / update-if-converged loop:
+    same converged flags and iteration counts, poses within 2 mm / 0.1 deg (rotation: |dq| < 1e-3) frame by frame."""
+    W, H = 640, 480
+    frames, poses, K, _ = synth.make_sequence(100, W, H)
+    n = 9
+    sdf, orc = make_pair(pkg, po, 1, 0.01, 5, W, H, K, log2cap=17)
+    ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+    sdf.scan_set_pose(ident)
+    sdf.scan_set_tracker(25, 1e-3, 1.0)
+    sdf.scan_submit(depth_host=frames[0], track=False)
+    sdf.scan_collect()
+    res = sdf.scan_run([frames[i].ctypes.data for i in range(1, n)], on_device=False)
+    orc.set_pose(ident)
+    orc.update(frames[0], ident)
+    for i in range(1, n):
+        co, it = orc.optimize(frames[i])
+        if co:
+            orc.update(frames[i], orc.get_pose())
+        r = res[i - 1]
+        dp = np.abs(np.array(r.pose7[:]) - orc.get_pose())
+        assert bool(r.converged) == bool(co) and r.iters == it, (i, r.converged, co, r.iters, it)
+        assert dp[:3].max() < 2e-3 and dp[3:].max() < 1e-3, (i, dp)
+    ka, kb = {tuple(x) for x in sdf.download()[0]}, {tuple(x) for x in orc.download()[0]}
+    assert len(ka & kb) / len(ka | kb) > 0.999
+    sdf.close()
+
+
 def test_edge_cases(pkg, po, synth):
     W, H = 64, 48
     K = synth.scaled_intrinsics(W, H).astype(np.float32)
