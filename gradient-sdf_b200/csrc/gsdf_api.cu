@@ -925,6 +925,17 @@ gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* di
     return s;
 }
 
+gsdf_status gsdf_host_alloc(size_t bytes, void** out) {
+    if (!out || bytes == 0) return GSDF_ERR_INVALID;
+    *out = nullptr;
+    if (cudaHostAlloc(out, bytes, cudaHostAllocDefault) != cudaSuccess) { g_create_error = "cudaHostAlloc failed"; *out = nullptr; return GSDF_ERR_CUDA; }
+    return GSDF_OK;
+}
+gsdf_status gsdf_host_free(void* p) {
+    if (!p) return GSDF_OK;
+    return cudaFreeHost(p) == cudaSuccess ? GSDF_OK : GSDF_ERR_CUDA;
+}
+
 gsdf_status gsdf_upload(gsdf_handle h, int64_t n, const int32_t* keys, const float* dist, const float* weight, const float* grad) {
     if (!h || n < 0) return GSDF_ERR_INVALID;
     if (n == 0) return GSDF_OK;

@@ -28,6 +28,13 @@
 #define CV_32FC1 5
 #endif
 
+// One frame of a dataset as the loaders enumerate it: file names relative to the dataset directory and the two
+// timestamps.  Enumeration (next_entry) is sequential and cheap; decoding (ImageLoader::decode) touches no loader
+// state, so a thread pool may decode entries in parallel (host/prefetch.h).
+struct FrameEntry {
+    std::string depth_file, color_file, stamp_depth, stamp_rgb;
+};
+
 class ImageLoader {
 protected:
     Mat3f K_;
@@ -67,18 +74,40 @@ public:
         return true;
     }
 
-    bool load_depth(const std::string& filename, cv::Mat& depth) {  // ImageLoader.h:159-175
-        if (filename.empty()) { std::cerr << "Error: missing filename" << std::endl; return false; }
+    // Decode one entry's depth image into `out` (float metres) and check its colour image: thread-safe, no loader state.
+    // `out` must hold at least capacity floats if capacity > 0 (a fixed, e.g. pinned, buffer); else `vec` is resized.
+    bool decode(const FrameEntry& e, float* out, size_t capacity, std::vector<float>* vec, int& w, int& h, std::string& err) const {
+        if (e.depth_file.empty()) { err = "Error: missing filename"; return false; }
         gsdf_host::GrayImage img;
-        const std::string err = gsdf_host::read_png_gray(path_ + filename, img);
-        if (!err.empty()) {
-            std::cerr << "Error: empty depth image " << path_ + filename << " (" << err << ")" << std::endl;
-            return false;
-        }
-        depth_buf_.resize(img.px.size());
-        for (size_t i = 0; i < img.px.size(); ++i) depth_buf_[i] = (float)img.px[i] * unit_;
-        depth = cv::Mat(img.height, img.width, CV_32FC1, depth_buf_.data());
+        const std::string perr = gsdf_host::read_png_gray(path_ + e.depth_file, img);
+        if (!perr.empty()) { err = "Error: empty depth image " + path_ + e.depth_file + " (" + perr + ")"; return false; }
+        if (vec) { vec->resize(img.px.size()); out = vec->data(); }
+        else if (img.px.size() > capacity) { err = "Error: depth image " + path_ + e.depth_file + " is larger than the frame buffer"; return false; }
+        for (size_t i = 0; i < img.px.size(); ++i) out[i] = (float)img.px[i] * unit_;
+        w = img.width; h = img.height;
+        if (e.color_file.empty()) { err = "Error: missing filename"; return false; }
+        if (!readable(path_ + e.color_file)) { err = "Error: empty color image " + path_ + e.color_file; return false; }
         return true;
+    }
+
+    bool load_depth(const std::string& filename, cv::Mat& depth) {  // ImageLoader.h:159-175
+        FrameEntry e;
+        e.depth_file = filename;
+        e.color_file = filename;  // existence of the depth file itself: always true once it decoded
+        int w = 0, h = 0;
+        std::string err;
+        if (!decode(e, nullptr, 0, &depth_buf_, w, h, err)) { std::cerr << err << std::endl; return false; }
+        depth = cv::Mat(h, w, CV_32FC1, depth_buf_.data());
+        return true;
+    }
+
+    // The next frame of the sequence without decoding anything; false at the end.  load_next = next_entry + decode.
+    virtual bool next_entry(FrameEntry& e) = 0;
+
+    bool load_next(cv::Mat& color, cv::Mat& depth) {
+        FrameEntry e;
+        if (!next_entry(e)) return false;
+        return load_depth(e.depth_file, depth) && load_color(e.color_file, color);
     }
 
     bool load_color(const std::string& filename, cv::Mat& /*color*/) {  // ImageLoader.h:194-216 (existence only, see above)
@@ -105,7 +134,6 @@ public:
         return true;
     }
 
-    virtual bool load_next(cv::Mat& color, cv::Mat& depth) = 0;
     virtual void reset() = 0;
 };
 
@@ -115,16 +143,17 @@ class TumrgbdLoader : public ImageLoader {
 public:
     explicit TumrgbdLoader(const std::string& path) : ImageLoader(1.f / 5000, path, false) { assoc_file_.open(path_ + "associated.txt"); }
 
-    bool load_next(cv::Mat& color, cv::Mat& depth) override {  // TumrgbdLoader.h:78-101
-        std::string line = "#", rgb_filename, depth_filename;
+    bool next_entry(FrameEntry& e) override {  // TumrgbdLoader.h:78-101
+        std::string line = "#";
         while (line.empty() || line.at(0) == '#')
             if (!std::getline(assoc_file_, line)) return false;
         std::istringstream dss(line);
-        dss >> timestamp_rgb_ >> rgb_filename >> timestamp_depth_ >> depth_filename;
+        dss >> timestamp_rgb_ >> e.color_file >> timestamp_depth_ >> e.depth_file;
         std::cout << "load image " << timestamp_rgb_ << std::endl;
         timestamps_depth_.push_back(timestamp_depth_);
         timestamps_rgb_.push_back(timestamp_rgb_);
-        return load_depth(depth_filename, depth) && load_color(rgb_filename, color);
+        e.stamp_depth = timestamp_depth_; e.stamp_rgb = timestamp_rgb_;
+        return true;
     }
 
     void reset() override {
@@ -142,12 +171,13 @@ class SynthLoader : public ImageLoader {
 public:
     explicit SynthLoader(const std::string& path) : ImageLoader(1.f / 1000, path, true) {}
 
-    bool load_next(cv::Mat& color, cv::Mat& depth) override {  // SynthLoader.h:61-82
+    bool next_entry(FrameEntry& e) override {  // SynthLoader.h:61-82 (the counter advances per enumerated frame)
         std::stringstream ss;
         ss << std::setfill('0') << std::setw(3) << counter;
         timestamp_rgb_ = timestamp_depth_ = ss.str();
-        const std::string filename = timestamp_rgb_ + ".png";
-        if (!load_depth("depth/" + filename, depth) || !load_color("rgb/" + filename, color)) return false;
+        e.depth_file = "depth/" + timestamp_rgb_ + ".png";
+        e.color_file = "rgb/" + timestamp_rgb_ + ".png";
+        e.stamp_depth = e.stamp_rgb = timestamp_rgb_;
         ++counter;
         return true;
     }
@@ -161,12 +191,13 @@ class Printed3dLoader : public ImageLoader {
 public:
     explicit Printed3dLoader(const std::string& path) : ImageLoader(1.f / 1000, path, true) {}
 
-    bool load_next(cv::Mat& color, cv::Mat& depth) override {  // Printed3dLoader.h:61-82
+    bool next_entry(FrameEntry& e) override {  // Printed3dLoader.h:61-82
         std::stringstream ss;
         ss << std::setfill('0') << std::setw(6) << counter;
         timestamp_rgb_ = timestamp_depth_ = ss.str();
-        const std::string filename = timestamp_rgb_ + ".png";
-        if (!load_depth("depth_" + filename, depth) || !load_color("color_" + filename, color)) return false;
+        e.depth_file = "depth_" + timestamp_rgb_ + ".png";
+        e.color_file = "color_" + timestamp_rgb_ + ".png";
+        e.stamp_depth = e.stamp_rgb = timestamp_rgb_;
         ++counter;
         return true;
     }
@@ -198,18 +229,17 @@ class RedwoodLoader : public ImageLoader {
 public:
     explicit RedwoodLoader(const std::string& path) : ImageLoader(1.f / 1000, path, true) { init(); }
 
-    bool load_next(cv::Mat& color, cv::Mat& depth) override {  // RedwoodLoader.h:98-122
+    bool next_entry(FrameEntry& e) override {  // RedwoodLoader.h:98-122
         if (counter >= depth_filenames_.size() || counter >= rgb_filenames_.size()) return false;
-        std::string filename = depth_filenames_[counter];
-        timestamp_depth_ = filename;
-        timestamps_depth_.push_back(filename);
-        std::cout << "------load depth " << filename << ". " << std::endl;
-        if (!load_depth("depth/" + filename, depth)) return false;
-        filename = rgb_filenames_[counter];
-        timestamp_rgb_ = filename;
-        timestamps_rgb_.push_back(filename);
-        std::cout << "------load rgb " << filename << ". " << std::endl;
-        if (!load_color("rgb/" + filename, color)) return false;
+        timestamp_depth_ = depth_filenames_[counter];
+        timestamp_rgb_ = rgb_filenames_[counter];
+        timestamps_depth_.push_back(timestamp_depth_);
+        timestamps_rgb_.push_back(timestamp_rgb_);
+        std::cout << "------load depth " << timestamp_depth_ << ". " << std::endl;
+        std::cout << "------load rgb " << timestamp_rgb_ << ". " << std::endl;
+        e.depth_file = "depth/" + timestamp_depth_;
+        e.color_file = "rgb/" + timestamp_rgb_;
+        e.stamp_depth = timestamp_depth_; e.stamp_rgb = timestamp_rgb_;
         ++counter;
         return true;
     }

@@ -2,14 +2,16 @@
 // img_loader.h and writes
 //     <out>.f32   the depth frames, float32 metres, concatenated
 //     stdout      one line per frame: "<depth timestamp> <rgb timestamp> <width> <height>", then "K k00 ... k22"
-//   loader_probe <tum|synth|printed|rw> <dataset dir with trailing /> <out prefix>
+//   loader_probe <tum|synth|printed|rw> <dataset dir with trailing /> <out prefix> [threads [slots]]
+// With threads > 0 the frames go through FramePrefetcher (parallel decode, in-order delivery) instead of load_next.
 #include <cstdio>
 
-#include "img_loader.h"
+#include "prefetch.h"
 
 int main(int argc, char** argv) {
-    if (argc != 4) { std::fprintf(stderr, "usage: loader_probe <type> <dir/> <out prefix>\n"); return 2; }
+    if (argc < 4 || argc > 6) { std::fprintf(stderr, "usage: loader_probe <type> <dir/> <out prefix> [threads [slots]]\n"); return 2; }
     const std::string type = argv[1], dir = argv[2], out = argv[3];
+    const int threads = argc > 4 ? std::atoi(argv[4]) : 0, slots = argc > 5 ? std::atoi(argv[5]) : 6;
     ImageLoader* loader = nullptr;
     if (type == "tum") loader = new TumrgbdLoader(dir);
     else if (type == "synth") loader = new SynthLoader(dir);
@@ -21,6 +23,17 @@ int main(int argc, char** argv) {
     std::streambuf* keep = std::cout.rdbuf(std::cerr.rdbuf());  // the loaders chat on cout like the reference's: keep stdout clean
     cv::Mat color, depth;
     std::vector<std::string> lines;
+    if (threads > 0) {
+        FramePrefetcher pf(loader, threads, slots, (size_t)1 << 22);
+        std::vector<const FramePrefetcher::Frame*> held;  // frames are released late, as a GPU pipeline would
+        while (const FramePrefetcher::Frame* fr = pf.next()) {
+            std::fwrite(fr->data, sizeof(float), (size_t)fr->width * fr->height, f);
+            lines.push_back(fr->stamp_depth + " " + fr->stamp_rgb + " " + std::to_string(fr->width) + " " + std::to_string(fr->height));
+            held.push_back(fr);
+            if ((int)held.size() >= slots - 1) { pf.release(held.front()); held.erase(held.begin()); }
+        }
+        if (!pf.error().empty()) std::cerr << pf.error() << std::endl;
+    } else
     while (loader->load_next(color, depth)) {
         std::fwrite(depth.data, sizeof(float), (size_t)depth.rows * depth.cols, f);
         lines.push_back(loader->depth_timestamp() + " " + loader->rgb_timestamp() + " " + std::to_string(depth.cols) + " " +

@@ -10,14 +10,18 @@
 //     <input>/meta.txt         "width height n_frames"
 //     <input>/<pose-file>      optional, "timestamp tx ty tz qx qy qz qw" per line (ImageLoader.h:231-259)
 // --pipelined uses gsdf_scan_submit/collect (whole frames enqueued, no host round trip inside a frame).
+// --threads T (with --pipelined and a PNG dataset) decodes frames ahead on T host threads into pinned buffers
+// (prefetch.h): on real data the PNG decode, not the GPU, sets the frame rate.
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <deque>
 #include <fstream>
 #include <iomanip>
 #include <sstream>
 
 #include "img_loader.h"
+#include "prefetch.h"
 #include "sdf_tracker.h"
 
 namespace {
@@ -38,7 +42,7 @@ int main(int argc, char* argv[]) {
     size_t first = 0, last = std::numeric_limits<size_t>::max();
     float voxel_size = 0.01f, truncation_factor = 5.f;
     bool save_sdf = false, pipelined = false;
-    int log2_capacity = 17;
+    int log2_capacity = 17, threads = 0;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto next = [&](const char* name) -> std::string {
@@ -57,6 +61,7 @@ int main(int argc, char* argv[]) {
         else if (a == "--capacity-log2") log2_capacity = std::stoi(next("--capacity-log2"));
         else if (a == "--save-sdf") save_sdf = true;
         else if (a == "--pipelined") pipelined = true;
+        else if (a == "--threads") threads = std::stoi(next("--threads"));
         else { std::cerr << "unknown option " << a << std::endl; return 1; }
     }
     if (stype != "grad-sdf" && stype != "base-sdf") {  // main_scan_3d.cpp:105-114
@@ -141,7 +146,9 @@ int main(int argc, char* argv[]) {
         frames.read((char*)depth_buf.data(), (std::streamsize)(depth_buf.size() * sizeof(float)));
         return (size_t)frames.gcount() == depth_buf.size() * sizeof(float);
     };
-    for (size_t i = 0; i < first; ++i) load_next();
+    const bool prefetched = loader && pipelined && threads > 0 && !GT_pose;
+    if (!prefetched)
+        for (size_t i = 0; i < first; ++i) load_next();
 
     double t_track = 0., t_fuse = 0.;
     size_t n_tracked = 0, n_fused = 0;
@@ -162,6 +169,61 @@ int main(int argc, char* argv[]) {
         --pending;
     };
 
+    if (prefetched) {
+        // Frames are decoded ahead on `threads` host threads into pinned buffers and handed to the GPU pipeline in order;
+        // a buffer goes back to the pool when its frame has been collected (its upload is done by then).
+        const size_t max_pixels = (size_t)1 << 21;  // up to 1920 x 1080
+        FramePrefetcher pf(loader, threads, threads + 6, max_pixels,
+                           [](size_t n) { void* p = nullptr; return gsdf_host_alloc(n * sizeof(float), &p) == GSDF_OK ? (float*)p : nullptr; },
+                           [](float* p) { gsdf_host_free(p); });
+        std::deque<const FramePrefetcher::Frame*> inflight;
+        auto collect_frame = [&]() {
+            cur_stamp = inflight.front()->stamp_depth;
+            collect_one();
+            pf.release(inflight.front());
+            inflight.pop_front();
+        };
+        const auto t_begin = std::chrono::steady_clock::now();
+        size_t n_in = 0;
+        for (size_t i = 0; i <= last; ++i) {
+            const FramePrefetcher::Frame* f = pf.next();
+            if (!f) { if (!pf.error().empty()) std::cerr << pf.error() << std::endl; std::cerr << " -> Frame " << i << " could not be loaded!" << std::endl; break; }
+            if (i < first) { pf.release(f); continue; }
+            ++n_in;
+            if (i == first) {
+                width = f->width; height = f->height;
+                make_estimator();
+                depth = cv::Mat(height, width, CV_32FC1, f->data);
+                if (stype == "grad-sdf") tSDF = new MapGradPixelSdf(voxel_size, truncation);
+                else tSDF = new MapPixelSdf(voxel_size, truncation);
+                tSDF->set_capacity_log2(log2_capacity);
+                tSDF->setup(color, depth, K, NEst);
+                ++n_fused;
+                pOpt = new RigidPointOptimizer(tSDF);
+                cur_stamp = f->stamp_depth;
+                write_pose(i, pOpt->pose());
+                const SE3 start = pOpt->pose();
+                gsdf_scan_set_pose(tSDF->gpu(), start.data());
+                gsdf_scan_set_tracker(tSDF->gpu(), 25, 1e-3f, 1.f);
+                pf.release(f);
+                continue;
+            }
+            if (f->width != width || f->height != height) { std::cerr << "frame size changed" << std::endl; pf.release(f); break; }
+            if (pending == 4) collect_frame();
+            if (gsdf_scan_submit(tSDF->gpu(), f->data, nullptr, GSDF_SCAN_TRACK_FUSE) != GSDF_OK) {
+                std::cerr << gsdf_last_error(tSDF->gpu()) << std::endl;
+                return 2;
+            }
+            inflight.push_back(f);
+            pending_idx.push_back(i);
+            ++pending;
+            ++n_tracked;
+        }
+        while (pending) collect_frame();
+        const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+        std::cout << "prefetched loop: " << n_in << " frames in " << secs << " s = " << n_in / secs << " frames/s (decode on " << threads
+                  << " threads + upload + track + fuse)" << std::endl;
+    } else
     for (size_t i = first; i <= last; ++i) {
         std::cout << "Working on frame: " << i << std::endl;
         if (!load_next()) { std::cerr << " -> Frame " << i << " could not be loaded!" << std::endl; break; }

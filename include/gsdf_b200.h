@@ -15,6 +15,7 @@
 #ifndef GSDF_B200_H_
 #define GSDF_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -136,6 +137,12 @@ gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* di
  * rule assigns to this rank, so every rank may be given the whole list.  GSDF_ERR_CAPACITY if the block hash fills up. */
 gsdf_status gsdf_upload(gsdf_handle h, int64_t n, const int32_t* keys, const float* dist, const float* weight,
                         const float* grad);
+
+/* Pinned (page-locked) host memory for frames handed to gsdf_scan_submit / gsdf_scan_run, so that their uploads are
+ * asynchronous copies that overlap the GPU work; no counterpart in the reference (its frames live in cv::Mat).  Plain
+ * wrappers of the CUDA runtime for hosts that link only this library. */
+gsdf_status gsdf_host_alloc(size_t bytes, void** out);
+gsdf_status gsdf_host_free(void* p);
 
 /* -- the frame pipeline: main_scan_3d.cpp:208-266 without the host in the loop --------------------------------
  * The reference's loop body is "optimize(depth); if (converged) update(depth, pose())" with the pose living in the

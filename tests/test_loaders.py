@@ -28,9 +28,10 @@ def _write_depth(path, u16, compression=None):
     assert cv2.imwrite(str(path), u16, params)
 
 
-def _probe(kind, d, tmp_path):
-    out = tmp_path / f"probe_{kind}"
-    r = subprocess.run([str(PROBE), kind, str(d) + "/", str(out)], capture_output=True, text=True, timeout=120)
+def _probe(kind, d, tmp_path, threads=0, slots=6):
+    out = tmp_path / f"probe_{kind}_{threads}"
+    extra = [str(threads), str(slots)] if threads else []
+    r = subprocess.run([str(PROBE), kind, str(d) + "/", str(out)] + extra, capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [l.split() for l in r.stdout.strip().splitlines()]
     frames = [l for l in lines if l[0] != "K"]
@@ -155,3 +156,26 @@ def test_png_decoder_rejects_what_is_not_a_depth_map(probe_built, tmp_path):
     (d / "depth" / "001.png").write_bytes(raw[: len(raw) // 2])
     r = subprocess.run([str(PROBE), "synth", str(d) + "/", str(tmp_path / "o")], capture_output=True, text=True)
     assert r.stdout.strip() == "" and "Error: empty depth image" in r.stderr
+
+
+def test_parallel_prefetch_delivers_the_same_frames_in_order(probe_built, synth, tmp_path):
+    """FramePrefetcher (host/prefetch.h): frames enumerated in order, decoded by a thread pool, delivered in order and
+    held by the consumer while later ones are decoded — identical to the sequential loader; a frame that cannot be
+    loaded ends the sequence at that frame."""
+    unit = 1.0 / 1000
+    frames, poses, K, _ = synth.make_sequence(60, W, H, unit=unit)
+    frames = frames[:23]
+    d = tmp_path / "printed"
+    d.mkdir()
+    for i, fr in enumerate(frames):
+        _write_depth(d / f"depth_{i:06d}.png", _u16(fr, unit), compression=[1, 6, 9][i % 3])
+        (d / f"color_{i:06d}.png").write_bytes(b"x")
+    seq, _, data_seq = _probe("printed", d, tmp_path)
+    for threads, slots in ((1, 2), (4, 6), (8, 12)):
+        got, _, data = _probe("printed", d, tmp_path, threads=threads, slots=slots)
+        assert got == seq and len(got) == len(frames)
+        assert np.array_equal(data, data_seq)
+    assert np.array_equal(data_seq.reshape(len(frames), H, W), frames)
+    (d / "color_000015.png").unlink()
+    got, _, data = _probe("printed", d, tmp_path, threads=8, slots=12)
+    assert [g[0] for g in got] == [f"{i:06d}" for i in range(15)]
