@@ -78,7 +78,7 @@ public:
     // `out` must hold at least capacity floats if capacity > 0 (a fixed, e.g. pinned, buffer); else `vec` is resized.
     bool decode(const FrameEntry& e, float* out, size_t capacity, std::vector<float>* vec, int& w, int& h, std::string& err) const {
         if (e.depth_file.empty()) { err = "Error: missing filename"; return false; }
-        gsdf_host::GrayImage img;
+        static thread_local gsdf_host::GrayImage img;  // per decoding thread: its buffers are reused from frame to frame
         const std::string perr = gsdf_host::read_png_gray(path_ + e.depth_file, img);
         if (!perr.empty()) { err = "Error: empty depth image " + path_ + e.depth_file + " (" + perr + ")"; return false; }
         if (vec) { vec->resize(img.px.size()); out = vec->data(); }

@@ -18,19 +18,19 @@ int main(int argc, char** argv) {
     else if (type == "printed") loader = new Printed3dLoader(dir);
     else if (type == "rw" || type == "redwood") loader = new RedwoodLoader(dir);
     else { std::fprintf(stderr, "unknown dataset type\n"); return 2; }
-    FILE* f = std::fopen((out + ".f32").c_str(), "wb");
+    FILE* f = std::fopen(out == "-" ? "/dev/null" : (out + ".f32").c_str(), "wb");  // "-": timing runs, nothing kept
     if (!f) return 2;
     std::streambuf* keep = std::cout.rdbuf(std::cerr.rdbuf());  // the loaders chat on cout like the reference's: keep stdout clean
     cv::Mat color, depth;
     std::vector<std::string> lines;
     if (threads > 0) {
         FramePrefetcher pf(loader, threads, slots, (size_t)1 << 22);
-        std::vector<const FramePrefetcher::Frame*> held;  // frames are released late, as a GPU pipeline would
+        std::vector<const FramePrefetcher::Frame*> held;  // four frames are held back, as the GPU pipeline holds its frames in flight
         while (const FramePrefetcher::Frame* fr = pf.next()) {
             std::fwrite(fr->data, sizeof(float), (size_t)fr->width * fr->height, f);
             lines.push_back(fr->stamp_depth + " " + fr->stamp_rgb + " " + std::to_string(fr->width) + " " + std::to_string(fr->height));
             held.push_back(fr);
-            if ((int)held.size() >= slots - 1) { pf.release(held.front()); held.erase(held.begin()); }
+            if ((int)held.size() >= std::min(4, slots - 1)) { pf.release(held.front()); held.erase(held.begin()); }
         }
         if (!pf.error().empty()) std::cerr << pf.error() << std::endl;
     } else

@@ -21,6 +21,10 @@ namespace gsdf_host {
 struct GrayImage {
     int width = 0, height = 0, bit_depth = 0;  // bit_depth 8 or 16
     std::vector<uint16_t> px;                  // row-major sample values (an 8-bit file is widened, not rescaled)
+    // scratch kept between calls (file bytes, IDAT stream, inflated scanlines): a decoder thread that reuses one
+    // GrayImage allocates nothing per frame — fresh 600 kB vectors per frame are mmap/munmap pairs, and a pool of
+    // decoding threads then serialises on the process's address-space lock instead of inflating
+    std::vector<unsigned char> file, idat, raw, zero;
 };
 
 inline uint32_t be32(const unsigned char* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
@@ -29,7 +33,8 @@ inline uint32_t be32(const unsigned char* p) { return ((uint32_t)p[0] << 24) | (
 inline std::string read_png_gray(const std::string& path, GrayImage& out) {
     FILE* f = std::fopen(path.c_str(), "rb");
     if (!f) return "cannot open " + path;
-    std::vector<unsigned char> file;
+    std::vector<unsigned char>& file = out.file;
+    file.clear();
     unsigned char buf[1 << 16];
     size_t got;
     while ((got = std::fread(buf, 1, sizeof(buf), f)) > 0) file.insert(file.end(), buf, buf + got);
@@ -39,7 +44,8 @@ inline std::string read_png_gray(const std::string& path, GrayImage& out) {
     size_t pos = 8;
     bool have_ihdr = false, done = false;
     int colour_type = -1, interlace = -1;
-    std::vector<unsigned char> idat;
+    std::vector<unsigned char>& idat = out.idat;
+    idat.clear();
     while (!done) {
         if (pos + 12 > file.size()) return path + ": truncated chunk";
         const uint32_t len = be32(&file[pos]);
@@ -71,13 +77,15 @@ inline std::string read_png_gray(const std::string& path, GrayImage& out) {
 
     const size_t bpp = (size_t)out.bit_depth / 8;       // bytes per pixel = filter distance
     const size_t stride = (size_t)out.width * bpp;
-    std::vector<unsigned char> raw((stride + 1) * (size_t)out.height);
+    std::vector<unsigned char>& raw = out.raw;
+    raw.resize((stride + 1) * (size_t)out.height);
     uLongf raw_len = (uLongf)raw.size();
     const int zr = uncompress(raw.data(), &raw_len, idat.data(), (uLong)idat.size());
     if (zr != Z_OK || raw_len != raw.size()) return path + ": inflate failed (" + std::to_string(zr) + ")";
 
     // undo the scanline filters in place (PNG specification, section 9: None, Sub, Up, Average, Paeth)
-    std::vector<unsigned char> zero(stride, 0);
+    std::vector<unsigned char>& zero = out.zero;
+    zero.assign(stride, 0);
     for (int y = 0; y < out.height; ++y) {
         unsigned char* line = &raw[(stride + 1) * (size_t)y];
         const int ft = line[0];

@@ -183,7 +183,7 @@ int main(int argc, char* argv[]) {
             pf.release(inflight.front());
             inflight.pop_front();
         };
-        const auto t_begin = std::chrono::steady_clock::now();
+        auto t_begin = std::chrono::steady_clock::now();  // restarted once the first frame has created and initialised the map
         size_t n_in = 0;
         for (size_t i = 0; i <= last; ++i) {
             const FramePrefetcher::Frame* f = pf.next();
@@ -206,6 +206,8 @@ int main(int argc, char* argv[]) {
                 gsdf_scan_set_pose(tSDF->gpu(), start.data());
                 gsdf_scan_set_tracker(tSDF->gpu(), 25, 1e-3f, 1.f);
                 pf.release(f);
+                t_begin = std::chrono::steady_clock::now();
+                n_in = 0;
                 continue;
             }
             if (f->width != width || f->height != height) { std::cerr << "frame size changed" << std::endl; pf.release(f); break; }
@@ -221,8 +223,8 @@ int main(int argc, char* argv[]) {
         }
         while (pending) collect_frame();
         const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
-        std::cout << "prefetched loop: " << n_in << " frames in " << secs << " s = " << n_in / secs << " frames/s (decode on " << threads
-                  << " threads + upload + track + fuse)" << std::endl;
+        std::cout << "prefetched loop: " << n_in << " frames in " << secs << " s = " << n_in / secs << " frames/s after the first frame (decode on "
+                  << threads << " threads + upload + track + fuse)" << std::endl;
     } else
     for (size_t i = first; i <= last; ++i) {
         std::cout << "Working on frame: " << i << std::endl;

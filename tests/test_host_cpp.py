@@ -133,7 +133,7 @@ def test_scan3d_driver_reads_the_reference_dataset_conventions(synth, tmp_path):
     out = tmp_path / "res_prefetch"
     r = run(["--input", str(png), "--results", str(out), "--scan-type", "base-sdf", "--data-type", "synth", "--voxel-size",
              "0.01", "--trunc", "5", "--capacity-log2", "15", "--last", "5", "--pipelined", "--threads", "4"])
-    assert r.returncode == 0 and "prefetched loop: 6 frames" in r.stdout, r.stderr[-2000:]
+    assert r.returncode == 0 and "prefetched loop: 5 frames" in r.stdout, r.stderr[-2000:]
     res["prefetch"] = [l.split() for l in Path(str(out) + "_poses.txt").read_text().splitlines()]
     assert [l[0] for l in res["prefetch"]] == [f"{i + 1:03d}" for i in range(6)]
     c = np.array([[float(x) for x in l[1:]] for l in res["prefetch"]])
