@@ -45,3 +45,13 @@ def test_no_cpu_fallback(pkg):
     with pytest.raises(pkg.GsdfError) as e:
         pkg.MapGradPixelSdf(0.02, 0.1, nest, log2_capacity=10)
     assert e.value.status == 2  # GSDF_ERR_CUDA
+
+
+def test_header_is_plain_c():
+    """The boundary is a C ABI: the header must compile as C99 and as C++11 on its own (no torch, no CUDA types)."""
+    import subprocess
+    hdr = str(ROOT / "include" / "gsdf_b200.h")
+    for cmd in (["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", hdr],
+                ["g++", "-std=c++11", "-Wall", "-Werror", "-fsyntax-only", "-x", "c++", hdr]):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
