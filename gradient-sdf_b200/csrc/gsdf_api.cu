@@ -1234,8 +1234,11 @@ gsdf_status gsdf_synchronize(gsdf_handle h) {
 // Limit: one CTA per 256 sampled pixels and at most kStaticMaxTiles (4096) CTAs, i.e. at most 1,048,576 sampled
 // pixels per call (1280x720 at sampling 1 fits); larger frames are rejected with GSDF_ERR_INVALID.
 // Set-up: the array's name is only a host-side stand-in for the device symbol, so the first call on each device
-// resolves the real device address once with cudaGetSymbolAddress (that device current) and caches it; make
-// that first call before starting any stream capture.  All calls on a device share the one array and it keeps
+// resolves the real device address once with cudaGetSymbolAddress (that device current) and caches it.  That first
+// call — and, under CUDA's lazy module loading, the first launch of this kernel for each map variant — may load
+// the library's device code, which is driver work that can allocate and synchronise: make one warm-up call per
+// device and variant (grad-sdf / base-sdf) at start-up, before any stream capture and before the loop that must
+// not allocate.  After that a call issues one 4-byte memset and one kernel launch, nothing else.  All calls on a device share the one array and it keeps
 // the previous call's contents: the arrival ticket is cleared on the stream before every launch (the partial
 // sums are fully overwritten by each launch and need no clearing), and two calls whose kernels overlap on the
 // GPU (different handles/streams on the same device) race on it — serialise them.
@@ -1251,6 +1254,8 @@ extern "C" gsdf_status gsdf_accumulate_noalloc(gsdf_handle h, const float* R9, c
     if (!h || !R9 || !t3 || !out29_dev || sampling < 1) return GSDF_ERR_INVALID;
     if (!h->d_depth) { h->err = "no depth frame set"; return GSDF_ERR_NO_FRAME; }
     if (h->cfg.world_size > 1) { h->err = "gsdf_accumulate_noalloc: single-GPU maps only"; return GSDF_ERR_INVALID; }
+    // like gsdf_accumulate: refused while pipeline frames are pending (they own the current frame and the map)
+    if (gsdf_status idle = pipeline_idle(h); idle != GSDF_OK) return idle;
     const int dev = h->cfg.device;
     if (dev < 0 || dev >= kMaxDevices) { h->err = "gsdf_accumulate_noalloc: device ordinal out of range"; return GSDF_ERR_INVALID; }
     TrackIntr ti;

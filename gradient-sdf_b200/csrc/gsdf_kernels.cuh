@@ -1,7 +1,5 @@
 // Hand-written sm_100a kernels of the Scan3D hot path.  Included by gsdf_api.cu only.
-//   normals_kernel      cv::NormalEstimator<float>::compute          (normals/NormalEstimator.h:179-204)
-//   fuse_kernel<V>      Map{Grad,}PixelSdf::update                   (MapGradPixelSdfOmp.cpp:82-126,
-//                                                                     MapPixelSdfOmp.cpp:152-192)
+// (normals and fusion live in gsdf_pipeline.cuh: normals_tile, fuse_work)
 //   accumulate_kernel<V> RigidPointOptimizer per-pixel loop + sums   (RigidPointOptimizerOmp.cpp:69-91)
 //   query_kernel<V>     Sdf::weights / Sdf::tsdf                     (MapGradPixelSdf.h:109-125,
 //                                                                     MapPixelSdf.h:107-143, MapPixelSdfOmp.cpp:44-113)
@@ -24,152 +22,13 @@ struct Pose {
 };
 
 // ---------------------------------------------------------------------------------------------------------
-// Normal estimation (FALS).  One CTA computes a NT_W x NT_H tile of normals.  The masked reciprocal depth
-// times the three cached planes is staged through shared memory with an r-pixel REFLECT_101 halo; the window
-// sums follow the oracle's order exactly (double accumulation; rows left->right, then columns top->bottom,
-// one rounding to float), so the normals — and therefore the validity tests that decide the voxel key set —
-// are bit-identical to the reference build.
+// Normal estimation (FALS), tile geometry shared by the kernels in gsdf_pipeline.cuh.
 constexpr int NT_W = 32, NT_H = 16, N_MAXR = 7;
 
 __device__ __forceinline__ int reflect101(int p, int len) {
     if (len == 1) return 0;
     while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
     return p;
-}
-
-__global__ void __launch_bounds__(NT_W* NT_H)
-normals_kernel(const float* __restrict__ depth, const float* __restrict__ x0n, const float* __restrict__ y0n,
-               const float* __restrict__ nsi, const float* __restrict__ Q, /* 6 planes Q11,Q12,Q13,Q22,Q23,Q33 */
-               float* __restrict__ nx, float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int tw = NT_W + 2 * r, th = NT_H + 2 * r;
-    float* a = reinterpret_cast<float*>(smem_raw);                                             // [3][th][tw] products
-    double* rs = reinterpret_cast<double*>(smem_raw + ((sizeof(float) * 3 * tw * th + 7) & ~size_t(7)));  // [3][th][NT_W] row sums
-    const int tid = threadIdx.y * NT_W + threadIdx.x;
-    const int x_base = blockIdx.x * NT_W, y_base = blockIdx.y * NT_H;
-    const size_t n = (size_t)w * h;
-
-    for (int i = tid; i < tw * th; i += NT_W * NT_H) {
-        const int ly = i / tw, lx = i - ly * tw;
-        // rows/columns beyond the image on the far side are clamped first (tiles may overhang), then reflected
-        const int gx = reflect101(min(x_base + lx - r, w - 1 + r), w);
-        const int gy = reflect101(min(y_base + ly - r, h - 1 + r), h);
-        const size_t g = (size_t)gy * w + gx;
-        const float z = depth[g];
-        const float zi = z != 0.f ? __fdiv_rn(1.f, z) : 0.f;          // NormalEstimator.h:181-187
-        a[i] = __fmul_rn(x0n[g], zi);                                  // :191
-        a[tw * th + i] = __fmul_rn(y0n[g], zi);                        // :192
-        a[2 * tw * th + i] = __fmul_rn(nsi[g], zi);                    // :193
-    }
-    __syncthreads();
-    // row sums for the NT_W centre columns of every (halo) row
-    for (int i = tid; i < 3 * th * NT_W; i += NT_W * NT_H) {
-        const int p = i / (th * NT_W), rem = i - p * th * NT_W;
-        const int ly = rem / NT_W, lx = rem - ly * NT_W;
-        const float* row = a + p * tw * th + ly * tw + lx;
-        double s = 0.0;
-        for (int d = 0; d <= 2 * r; ++d) s = __dadd_rn(s, (double)row[d]);
-        rs[i] = s;
-    }
-    __syncthreads();
-    const int x = x_base + threadIdx.x, y = y_base + threadIdx.y;
-    if (x >= w || y >= h) return;
-    double s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    for (int d = 0; d <= 2 * r; ++d) {
-        const int j = (threadIdx.y + d) * NT_W + threadIdx.x;
-        s1 = __dadd_rn(s1, rs[j]);
-        s2 = __dadd_rn(s2, rs[th * NT_W + j]);
-        s3 = __dadd_rn(s3, rs[2 * th * NT_W + j]);
-    }
-    const float b1 = (float)s1, b2 = (float)s2, b3 = (float)s3;
-    const size_t g = (size_t)y * w + x;
-    const float q11 = Q[g], q12 = Q[n + g], q13 = Q[2 * n + g], q22 = Q[3 * n + g], q23 = Q[4 * n + g], q33 = Q[5 * n + g];
-    const float vx = __fadd_rn(__fadd_rn(__fmul_rn(b1, q11), __fmul_rn(b2, q12)), __fmul_rn(b3, q13));  // :195
-    const float vy = __fadd_rn(__fadd_rn(__fmul_rn(b1, q12), __fmul_rn(b2, q22)), __fmul_rn(b3, q23));  // :196
-    const float vz = __fadd_rn(__fadd_rn(__fmul_rn(b1, q13), __fmul_rn(b2, q23)), __fmul_rn(b3, q33));  // :197
-    const float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)), __fmul_rn(vz, vz)));  // :199
-    nx[g] = __fdiv_rn(vx, nn);  // :201-203
-    ny[g] = __fdiv_rn(vy, nn);
-    nz[g] = __fdiv_rn(vz, nn);
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// Fusion: one thread per pixel walks 2*factor+1 samples along its ray and scatters into the voxel blocks.
-template <int VARIANT>
-__global__ void __launch_bounds__(256)
-fuse_kernel(MapView m, FrameGeom g, Pose pose, const float* __restrict__ depth, const float* __restrict__ nx,
-            const float* __restrict__ ny, const float* __restrict__ nz, const float* __restrict__ x0,
-            const float* __restrict__ y0, const float* __restrict__ hom_inv, Counters* ctr) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    const int n = g.w * g.h;
-    bool valid = idx < n;
-    float z = 0.f, Rxy0 = 0.f, Rxy1 = 0.f, Rxy2 = 0.f, Rn0 = 0.f, Rn1 = 0.f, Rn2 = 0.f;
-    const float* R = pose.R;
-    if (valid) {
-        z = depth[idx];
-        valid = !(z <= g.z_min || z >= g.z_max);  // MapGradPixelSdfOmp.cpp:89
-    }
-    if (valid) {
-        const float hx = x0[idx], hy = y0[idx];
-        const float a = nx[idx], b = ny[idx], c = nz[idx];
-        Rxy0 = dot3_rn(R[0], R[1], R[2], hx, hy, 1.f);  // :93
-        Rxy1 = dot3_rn(R[3], R[4], R[5], hx, hy, 1.f);
-        Rxy2 = dot3_rn(R[6], R[7], R[8], hx, hy, 1.f);
-        Rn0 = dot3_rn(R[0], R[1], R[2], a, b, c);       // :95
-        Rn1 = dot3_rn(R[3], R[4], R[5], a, b, c);
-        Rn2 = dot3_rn(R[6], R[7], R[8], a, b, c);
-        const float nsq = dot3_rn(a, b, c, a, b, c);
-        const float d = dot3_rn(a, b, c, hx, hy, 1.f);
-        // the reference compares the float expressions against double literals (:97-100); a NaN compares false
-        // in both tests, exactly as there
-        if ((double)nsq < .1) valid = false;
-        else if ((double)__fmul_rn(__fmul_rn(d, d), hom_inv[idx]) < .25) valid = false;
-    }
-    unsigned int n_upd = 0;
-    if (valid) {
-        unsigned long long last_key = kEmptyKey;
-        int slot = -1;
-        for (int kk = -g.factor; kk <= g.factor; ++kk) {  // float k = -factor .. factor, :103
-            const float s = __fadd_rn(z, __fmul_rn((float)kk, g.vs));
-            const float px = __fadd_rn(__fmul_rn(s, Rxy0), pose.t[0]);  // :105
-            const float py = __fadd_rn(__fmul_rn(s, Rxy1), pose.t[1]);
-            const float pz = __fadd_rn(__fmul_rn(s, Rxy2), pose.t[2]);
-            const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
-            const float qx = __fsub_rn(__fmul_rn(g.vs, (float)vx), pose.t[0]);  // vox2float(vi) - t, :107
-            const float qy = __fsub_rn(__fmul_rn(g.vs, (float)vy), pose.t[1]);
-            const float qz = __fsub_rn(__fmul_rn(g.vs, (float)vz), pose.t[2]);
-            const float sdf = __fsub_rn(dot3_rn(R[2], R[5], R[8], qx, qy, qz), z);  // row 2 of R^T, :107-108
-            const float wgt = sdf_weight(sdf, g.T, g.inv_T);
-            if (wgt > 0.f) {
-                const unsigned long long key = block_key_of(vx, vy, vz);
-                const int keep = shard_keeps<VARIANT>(m.world, m.rank, key, vx, vy, vz);  // 3 on a single GPU
-                if (keep && key != last_key) {
-                    last_key = key;
-                    slot = map_find_or_insert(m, key, ctr);
-                    if (slot < 0) atomicAdd(&ctr->overflow, 1u);
-                }
-                if (keep && slot >= 0) {
-                    const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
-                    const float ws = wgt * sdf_truncate(sdf, g.T);
-                    if (VARIANT == 0) {
-                        atomicAdd(m.acc4 + addr, make_float4(ws, wgt * Rn0, wgt * Rn1, wgt * Rn2));  // :115-117
-                        atomicAdd(m.accW + addr, wgt);
-                    } else {
-                        atomicAdd(m.acc2 + addr, make_float2(wgt, ws));  // MapPixelSdfOmp.cpp:183-185
-                    }
-                    n_upd += keep >> 1;  // halo copies are not counted twice
-                }
-            }
-        }
-    }
-    // counters: warp-reduce, one atomic per warp
-    const unsigned int pts = __popc(__ballot_sync(0xffffffffu, valid));
-    n_upd = __reduce_add_sync(0xffffffffu, n_upd);
-    if ((threadIdx.x & 31) == 0 && (pts | n_upd)) {
-        Counters::Slot* sl = ctr->slot + (blockIdx.x & (kCounterSlots - 1));
-        atomicAdd(&sl->points, (unsigned long long)pts);
-        atomicAdd(&sl->updates, (unsigned long long)n_upd);
-    }
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -469,7 +469,11 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// FALS normals per 32x16 tile (same arithmetic and summation order as normals_kernel, so bit-identical), but
+// FALS normals (cv::NormalEstimator<float>::compute, normals/NormalEstimator.h:179-204) per 32x16 tile.  The masked
+// reciprocal depth times the three cached planes is staged through shared memory with an r-pixel REFLECT_101 halo; the
+// window sums follow the oracle's order exactly (double accumulation; rows left->right, then columns top->bottom, one
+// rounding to float), so the normals — and therefore the validity tests that decide the voxel key set — are
+// bit-identical to the reference build.
 //   * tiles whose interior holds no z-valid pixel are skipped (fusion never reads normals of invalid pixels);
 //   * the z_inv products are widened to double once, when staged, instead of once per window tap.
 __device__ __forceinline__ void normals_tile(const float* __restrict__ depth, const float* __restrict__ x0n,

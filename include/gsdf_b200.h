@@ -111,9 +111,14 @@ gsdf_status gsdf_track(gsdf_handle h, float* pose7, int32_t max_iters, float con
  * cudaMalloc/cudaFree and uses no handle-owned scratch: the reduction's per-CTA partial sums live in a static
  * 512 KiB device array inside the library.  Same sums as gsdf_accumulate, written to out29_dev (29 floats in
  * DEVICE memory, ready when the handle's stream reaches that point; gsdf_synchronize waits for it).
- * Limit: at most 1,048,576 sampled pixels ((width/sampling)*(height/sampling)), else GSDF_ERR_INVALID; single-GPU
- * maps only.  The first call on a device resolves the array's device address (do it before any stream capture).
- * All calls on a device share the array: calls that overlap on the GPU race — keep them on one stream. */
+ * Limit: at most 1,048,576 sampled pixels (ceil(width/sampling)*ceil(height/sampling), the sampled grid of
+ * RigidPointOptimizerOmp.cpp:70-71), else GSDF_ERR_INVALID; single-GPU maps only; refused (GSDF_ERR_INVALID) while
+ * frames submitted with gsdf_scan_submit are pending, like gsdf_accumulate.
+ * The first call on a device resolves the array's device address, and the first launch for each map variant may
+ * load the library's device code (CUDA loads modules lazily; that driver work can allocate and synchronise): make
+ * one warm-up call per device and variant at start-up, before any stream capture and before the loop that must
+ * not allocate.  All calls on a device share the array: calls that overlap on the GPU race — keep them on one
+ * stream. */
 gsdf_status gsdf_accumulate_noalloc(gsdf_handle h, const float* R9, const float* t3, int32_t sampling,
                                     float* out29_dev);
 

@@ -6,8 +6,9 @@ real-time scanning loop where cudaMalloc's device-wide synchronisation would sta
 library carries its reduction scratch as a static device array and this entry point uses only that, the handle's
 map and frame, and the caller's own output buffer.
 
-The test calls it through the C ABI and checks it against the regular entry point (gsdf_accumulate), twice in a row
-on different poses, because all calls share the one static array and it keeps whatever the last call left there.
+The test calls it through the C ABI and checks it against the regular entry point (gsdf_accumulate) AND against the
+CPU oracle's sums for the same map, frame and pose, twice in a row on different poses, because all calls share the one
+static array and it keeps whatever the last call left there.
 This file sorts last on purpose: if it fails under `pytest -x`, every other test has already run.
 """
 import ctypes as C
@@ -18,7 +19,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def test_noalloc_matches_regular_entry_point_twice(pkg, synth):
+def test_noalloc_matches_regular_entry_point_and_oracle_twice(pkg, po, synth):
     import torch
 
     W, H = 320, 240
@@ -26,8 +27,10 @@ def test_noalloc_matches_regular_entry_point_twice(pkg, synth):
     nest = pkg.NormalEstimator(W, H, K, 11)
     for cls in (pkg.MapGradPixelSdf, pkg.MapPixelSdf):
         sdf = cls(np.float32(0.01), np.float32(0.05), nest, log2_capacity=15)
+        orc = po.Oracle(0 if cls is pkg.MapGradPixelSdf else 1, np.float32(0.01), np.float32(5.0), W, H, K)
         for i in range(3):
             sdf.update(frames[i], poses[i])
+            orc.update(frames[i], poses[i])
         sdf.upload_frame(frames[3])
         out_dev = torch.zeros(32, dtype=torch.float32, device="cuda")  # caller-owned output, allocated up front
         torch.cuda.synchronize()
@@ -42,6 +45,18 @@ def test_noalloc_matches_regular_entry_point_twice(pkg, synth):
             assert np.abs(got[:6] - ref[:6]).max() <= 1e-4 * np.abs(ref[:6]).max(), call
             assert np.abs(got[6:27] - ref[6:27]).max() <= 1e-4 * np.abs(ref[6:27]).max(), call
             assert abs(got[27] - ref[27]) <= 1e-4 * abs(ref[27]), call
+            # and against the CPU oracle (RigidPointOptimizerOmp.cpp:69-91 restated), same bars
+            cpu = orc.accumulate(frames[3], R, pn[:3], sampling)
+            assert got[28] == cpu[28], (call, got[28], cpu[28])
+            assert np.abs(got[:6] - cpu[:6]).max() <= 1e-4 * np.abs(cpu[:6]).max(), call
+            assert np.abs(got[6:27] - cpu[6:27]).max() <= 1e-4 * np.abs(cpu[6:27]).max(), call
+            assert abs(got[27] - cpu[27]) <= 1e-4 * abs(cpu[27]), call
+        # refused while pipeline frames are pending, exactly like gsdf_accumulate
+        sdf.scan_submit(depth_host=frames[4], track=True)
+        with pytest.raises(pkg.GsdfError) as e:
+            sdf.accumulate_noalloc(R, pn[:3], out_dev.data_ptr(), 1)
+        assert e.value.status == 1
+        sdf.scan_collect()
         sdf.close()
 
 
