@@ -97,7 +97,7 @@ struct gsdf_map {
     int2* d_vlist[kRing] = {};              // compacted valid pixels, buffered like the normals
     int* d_nvalid = nullptr;                // [kRing] counts of the lists
     unsigned int* d_compact_flags = nullptr;  // [nseg] look-back flags {epoch, count} of compact_tiles_kernel
-    unsigned int* d_compact_flags2 = nullptr; // [normals tiles] same for normals_compact_kernel
+    unsigned long long* d_compact_flags2 = nullptr; // [tiles of normals_compact_kernel] look-back words {epoch, status, value}
     unsigned int compact_epoch = 0;
     int nseg = 0;                           // CTAs of the compaction (64 tiles of 8x4 pixels each)
     DeviceResult* d_res = nullptr;    // owns d_state and d_ctr
@@ -105,8 +105,10 @@ struct gsdf_map {
     Counters* d_ctr = nullptr;
     float* d_partials = nullptr;      // v1 accumulate / accumulate_list: [acc_blocks][32]
     int acc_blocks = 0;
-    float* d_track_partials = nullptr;  // track_kernel: [2][track_blocks][32]
+    unsigned long long* d_track_rows = nullptr;  // track_kernel: [2][track_blocks][32] tagged words of the grid-level exchange
+    unsigned int track_tag = 0;         // tags handed out so far (every launch gets a fresh range)
     int track_blocks = 0;
+    int track_threads = kTrackThreadsMax;  // 768 (one CTA per SM) or 384 (two): GSDF_TRACK_THREADS
     Pose* d_pose = nullptr;
     float* d_out29 = nullptr;
     unsigned long long* d_count2 = nullptr;
@@ -122,7 +124,8 @@ struct gsdf_map {
     cudaEvent_t ev_main = nullptr;    // orders the side streams after earlier synchronous-API work on `stream`
     int64_t seq_submitted = 0, seq_collected = 0;
     int sync_slot = 0;                // ring slot used by gsdf_upload_frame
-    TrackParams scan_tp{25, 1e-6f, 1.f};
+    TrackParams scan_tp{25, 1e-6f, 1.f, 0};
+    unsigned int poll_ns = 0;         // GSDF_POLL_NS: pause between polls of the tracker's grid-level exchange (measured: no effect)
     unsigned long long last_points = 0, last_updates = 0;  // cumulative counters at the last report
     int sm_count = 148;
     int64_t launches = 0;
@@ -135,11 +138,10 @@ struct gsdf_map {
     bool merged_side = true;    // GSDF_MERGED_SIDE=0: compaction and normals as two launches
     bool serial = false;        // GSDF_SERIAL=1: frame-only kernels on the main stream instead of the side stream
     int batch_frames = kMaxBatch;  // GSDF_BATCH_FRAMES=1..4: frames per tracker launch in gsdf_scan_run
-    bool shadow_side = true;    // GSDF_SHADOW_SIDE=0: frame-only kernel always at full occupancy
     unsigned long long* d_dbg = nullptr;  // tracker phase stamps (gsdf_debug_track_timers)
     unsigned long long* d_flog = nullptr; // [kFlogFrames][4] kernel spans per pipeline frame (gsdf_debug_frame_log)
     // NVLink peer exchange of the sharded tracker (gsdf_p2p_export / gsdf_p2p_connect)
-    void* d_p2p = nullptr;            // [2][world][32] 64-bit {tag, float} words, then one error word
+    void* d_p2p = nullptr;            // [4][world][32] 64-bit {tag, float} words, then one error word
     PeerExchange px{};
     bool p2p_connected = false;
     unsigned int p2p_launches = 0;
@@ -267,8 +269,8 @@ TrackIntr make_intr(const gsdf_map* h, int sampling) {
     return ti;
 }
 
-size_t normals_smem(const gsdf_map* h) {
-    const int r = h->cfg.normal_window / 2, tw = NT_W + 2 * r, th = NT_H + 2 * r;
+size_t normals_smem(const gsdf_map* h, int tile_h = NT_H) {
+    const int r = h->cfg.normal_window / 2, tw = NT_W + 2 * r, th = tile_h + 2 * r;
     return sizeof(double) * 3 * tw * th + sizeof(double) * 3 * th * NT_W;
 }
 
@@ -296,21 +298,17 @@ gsdf_status launch_prepare(gsdf_map* h, const float* depth, int buf, cudaStream_
     return check_launch(h, "compact_tiles_kernel");
 }
 
-// One CTA of the frame-only kernel per SM when it runs in the shadow of the tracker (requested through the dynamic
-// shared-memory size: more than half an SM's 227 KB).  At full occupancy its 600 CTAs are ONE wave that lives as long
-// as the kernel (~10 us) and holds every register file, so the next cooperative tracker launch waits for it; with
-// one 512-thread, 32-register CTA per SM the two 384-thread tracker CTAs always fit beside it.
-constexpr size_t kShadowSmem = 116 * 1024;
-
-// compaction + normals of a frame in one launch (the pipeline's frame-only work)
-gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cudaStream_t stream, bool shadow = false,
-                                   int64_t seq = -1) {
+// compaction + normals of a frame in one launch (the pipeline's frame-only work).  In the pipeline it runs in the shadow
+// of the tracker: the tracker's 768 threads x 64 registers leave room for two of its 256-thread, 32-register CTAs per SM,
+// which fill the issue slots the latency-bound tracker leaves idle; its CTAs live a few microseconds, so a cooperative
+// tracker launch that arrives while more of them are resident (tracker absent) waits only that long.
+gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cudaStream_t stream, int64_t seq = -1) {
     const int w = h->cfg.width, ht = h->cfg.height, r = h->cfg.normal_window / 2;
     const size_t n = (size_t)w * ht;
-    dim3 grid((w + NT_W - 1) / NT_W, (ht + NT_H - 1) / NT_H), block(NT_W, NT_H);
+    dim3 grid((w + NT_W - 1) / NT_W, (ht + NC_H - 1) / NC_H), block(NT_W, NC_H);
     float* nrm = h->d_normals[buf];
     h->compact_epoch = (h->compact_epoch + 1) & 0x7FFFFu;
-    normals_compact_kernel<<<grid, block, shadow ? std::max(kShadowSmem, normals_smem(h)) : normals_smem(h), stream>>>(
+    normals_compact_kernel<<<grid, block, normals_smem(h, NC_H), stream>>>(
         depth, h->d_planes + 2 * n, h->d_planes + 3 * n, h->d_planes + 4 * n, h->d_planes + 5 * n, nrm, nrm + n,
         nrm + 2 * n, w, ht, r, h->geom.z_min, h->geom.z_max, h->d_compact_flags2, h->compact_epoch, h->d_vlist[buf],
         h->d_nvalid + buf, h->d_flog ? h->d_flog + 4 * ((seq < 0 ? h->seq_submitted : seq) % kFlogFrames) : nullptr);
@@ -377,8 +375,11 @@ gsdf_status launch_track_batch(gsdf_map* h, const TrackParams& tp, const int* bu
             FrameGeom geom = h->geom;
             TrackIntr ti_ = ti;
             FrameState* st = h->d_state;
-            float* partials = h->d_track_partials;
+            unsigned long long* rows = h->d_track_rows;
+            unsigned int tag0 = h->track_tag;
+            h->track_tag += (unsigned int)(nb * tp.max_iters);
             TrackParams tp_ = tp;
+            tp_.poll_ns = h->poll_ns;
             const float* planes = h->d_planes;
             Counters* ctr = h->d_ctr;
             FrameBatch fb = {};
@@ -392,11 +393,13 @@ gsdf_status launch_track_batch(gsdf_map* h, const TrackParams& tp, const int* bu
             }
             PeerExchange px = h->px;  // world <= 1 unless gsdf_p2p_connect succeeded
             if (px.world > 1 && tp.max_iters > 63) { h->err = "sharded tracking over NVLink supports at most 63 iterations"; return GSDF_ERR_INVALID; }
-            if (px.world > 1) px.epoch0 = (++h->p2p_launches) * 256u;  // <= kMaxBatch * 63 passes per launch
-            void* args[] = {&view, &geom, &ti_, &st, &partials, &tp_, &planes, &ctr, &fb, &px};
-            // cooperative launch: the driver guarantees that all CTAs are resident together (grid_barrier relies on it)
-            cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_kernel<decltype(V)::value>, dim3(h->track_blocks),
-                                                        dim3(kTrackThreads), args, 0, stream);
+            if (px.world > 1) { px.launch = ++h->p2p_launches; px.epoch0 = px.launch * 256u; }  // <= kMaxBatch * 63 passes per launch
+            void* args[] = {&view, &geom, &ti_, &st, &rows, &tag0, &tp_, &planes, &ctr, &fb, &px};
+            // cooperative launch: the driver guarantees that all CTAs are resident together (the exchange and grid_barrier
+            // rely on it)
+            const void* fn = h->track_threads == 384 ? (const void*)track_kernel<decltype(V)::value, 384>
+                                                     : (const void*)track_kernel<decltype(V)::value, 768>;
+            cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(h->track_blocks), dim3(h->track_threads), args, 0, stream);
             if (e != cudaSuccess) { h->err = std::string("launch of track_kernel: ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
             return check_launch(h, "track_kernel");
         });
@@ -468,7 +471,7 @@ void free_all(gsdf_map* h) {
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
     cudaFree(h->d_planes); cudaFree(h->d_res);
     for (int i = 0; i < kRing; ++i) { cudaFree(h->d_normals[i]); cudaFree(h->d_vlist[i]); }
-    cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_compact_flags2); cudaFree(h->d_track_partials);
+    cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_compact_flags2); cudaFree(h->d_track_rows);
     cudaFree(h->d_dbg); cudaFree(h->d_flog);
     cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
@@ -526,22 +529,32 @@ gsdf_status create_impl(gsdf_map* h) {
     h->nseg = (ntiles + kTilesPerBlock - 1) / kTilesPerBlock;
     CUDA_TRY(h, cudaMalloc(&h->d_compact_flags, sizeof(unsigned int) * h->nseg));
     CUDA_TRY(h, cudaMemset(h->d_compact_flags, 0, sizeof(unsigned int) * h->nseg));
-    const int n_ntiles = ((c.width + NT_W - 1) / NT_W) * ((c.height + NT_H - 1) / NT_H);
-    CUDA_TRY(h, cudaMalloc(&h->d_compact_flags2, sizeof(unsigned int) * n_ntiles));
-    CUDA_TRY(h, cudaMemset(h->d_compact_flags2, 0, sizeof(unsigned int) * n_ntiles));
+    const int n_ntiles = ((c.width + NT_W - 1) / NT_W) * ((c.height + NC_H - 1) / NC_H);
+    CUDA_TRY(h, cudaMalloc(&h->d_compact_flags2, sizeof(unsigned long long) * n_ntiles));
+    CUDA_TRY(h, cudaMemset(h->d_compact_flags2, 0, sizeof(unsigned long long) * n_ntiles));
     CUDA_TRY(h, cudaMalloc(&h->d_res, sizeof(DeviceResult)));
     h->d_state = &h->d_res->st;
     h->d_ctr = &h->d_res->ctr;
     h->acc_blocks = h->sm_count * 2;
     CUDA_TRY(h, cudaMalloc(&h->d_partials, sizeof(float) * kAccStride * h->sm_count * 4));
-    // persistent tracker: two CTAs per SM, all co-resident (cooperative launch; grid_barrier relies on it)
-    int per_sm = 0;
-    if (c.variant == GSDF_GRAD_SDF) CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<0>, kTrackThreads, 0));
-    else CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<1>, kTrackThreads, 0));
-    if (per_sm < 1) { h->err = "track_kernel does not fit on an SM"; return GSDF_ERR_CUDA; }
-    h->track_blocks = h->sm_count * (per_sm >= 2 ? 2 : 1);
-    if (const char* e = std::getenv("GSDF_TRACK_CTAS_PER_SM")) h->track_blocks = h->sm_count * (e[0] == '1' ? 1 : (per_sm >= 2 ? 2 : 1));
-    CUDA_TRY(h, cudaMalloc(&h->d_track_partials, sizeof(float) * 2 * kAccStride * h->track_blocks));
+    // persistent tracker: 768 threads per SM (one CTA, or two of 384), all co-resident (cooperative launch)
+    if (const char* e = std::getenv("GSDF_POLL_NS")) h->poll_ns = (unsigned int)std::max(0, std::atoi(e));
+    if (const char* e = std::getenv("GSDF_TRACK_THREADS")) h->track_threads = std::atoi(e) == 384 ? 384 : 768;
+    {
+        const bool two = h->track_threads == 384;
+        const void* fn = c.variant == GSDF_GRAD_SDF ? (two ? (const void*)track_kernel<0, 384> : (const void*)track_kernel<0, 768>)
+                                                    : (two ? (const void*)track_kernel<1, 384> : (const void*)track_kernel<1, 768>);
+        // Shadow mode needs an SM whose L1/shared split already leaves room for the frame-only kernel's 116 KB when its CTA
+        // arrives: the split is chosen when a kernel lands on an EMPTY SM, and the tracker alone would ask for a few KB, after
+        // which no frame-only CTA fits beside it until the SM drains (measured: the two kernels then simply alternate).
+        CUDA_TRY(h, cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        int per_sm = 0;
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, h->track_threads, 0));
+        if (per_sm < 1) { h->err = "track_kernel does not fit on an SM"; return GSDF_ERR_CUDA; }
+        h->track_blocks = h->sm_count * ((two && per_sm >= 2) ? 2 : 1);
+    }
+    CUDA_TRY(h, cudaMalloc(&h->d_track_rows, sizeof(unsigned long long) * 2 * kAccStride * h->track_blocks));
+    CUDA_TRY(h, cudaMemset(h->d_track_rows, 0, sizeof(unsigned long long) * 2 * kAccStride * h->track_blocks));
     CUDA_TRY(h, cudaMalloc(&h->d_pose, sizeof(Pose)));
     CUDA_TRY(h, cudaMalloc(&h->d_out29, sizeof(float) * kAccStride));
     CUDA_TRY(h, cudaMalloc(&h->d_count2, sizeof(unsigned long long) * 4));
@@ -562,8 +575,11 @@ gsdf_status create_impl(gsdf_map* h) {
     CUDA_TRY(h, cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
     if (normals_smem(h) > 48 * 1024)
         CUDA_TRY(h, cudaFuncSetAttribute(normals_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)normals_smem(h)));
-    CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)std::max(kShadowSmem, normals_smem(h))));
+    if (normals_smem(h, NC_H) > 48 * 1024)
+        CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)normals_smem(h, NC_H)));
+    CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
     build_normal_cache(c, h->h_planes);
     CUDA_TRY(h, cudaMemcpyAsync(h->d_planes, h->h_planes.data(), sizeof(float) * n * 11, cudaMemcpyHostToDevice, h->stream));
     return clear_map(h);
@@ -655,7 +671,6 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     }
     gsdf_map* h = new gsdf_map();
     h->cfg = c;
-    if (const char* e = std::getenv("GSDF_SHADOW_SIDE")) h->shadow_side = e[0] == '1';
     if (const char* e = std::getenv("GSDF_BATCH_FRAMES")) h->batch_frames = std::min(kMaxBatch, std::max(1, std::atoi(e)));
     if (const char* e = std::getenv("GSDF_SERIAL")) h->serial = e[0] == '1';
     if (const char* e = std::getenv("GSDF_MERGED_SIDE")) h->merged_side = e[0] == '1';
@@ -1043,8 +1058,7 @@ gsdf_status submit_frames(gsdf_map* h, const float* const* host, const float* co
             if (s != GSDF_OK) return s;
             s = launch_normals(h, frame, nbuf, side, true);
         } else {
-            // frames already in flight: this one's frame-only work is not on the critical path, keep its footprint small
-            s = launch_normals_compact(h, frame, nbuf, side, h->shadow_side && !idle, seq);
+            s = launch_normals_compact(h, frame, nbuf, side, seq);
         }
         if (s != GSDF_OK) return s;
         trace_mark(h, "side:normals", side);
@@ -1295,12 +1309,14 @@ extern "C" {
 
 // Debug: %globaltimer stamps of the next gsdf_track's phases per CTA and pass: out[n_ctas][4][6] nanoseconds
 // (0 lookups begin, 1 lookups end, 2 CTA reduce end, 3 grid barrier passed, 4 grid reduce end, 5 solve end).
-// Call once with out = NULL to arm (allocates), run gsdf_track, then call with a buffer of *n_ctas * 24 values.
+// Then out[n_ctas][4] whole-launch stamps (entry, Gauss-Newton loop left, fusion done, exit) and out[n_ctas * 24][8]
+// per-warp fusion stamps (see fuse_work; warp id = warp_in_cta * n_ctas + cta).
+// Call once with out = NULL to arm (allocates), run gsdf_track, then call with a buffer of *n_ctas * 220 values.
 gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int32_t* n_ctas) {
     if (!h || !n_ctas) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
     *n_ctas = h->track_blocks;
-    const size_t bytes = sizeof(unsigned long long) * h->track_blocks * 28;
+    const size_t bytes = sizeof(unsigned long long) * h->track_blocks * (28 + 24 * 8);
     if (!h->d_dbg) {
         CUDA_TRY(h, cudaMalloc(&h->d_dbg, bytes));
         CUDA_TRY(h, cudaMemset(h->d_dbg, 0, bytes));
@@ -1398,7 +1414,7 @@ void* gsdf_stream(gsdf_handle h) { return h ? (void*)h->stream : nullptr; }
 int64_t gsdf_launch_count(gsdf_handle h) { return h ? h->launches : 0; }
 
 // ---- NVLink peer exchange: the sharded tracker's all-reduce inside the cooperative launch --------------------------
-static size_t p2p_bytes(int world) { return sizeof(unsigned long long) * 2 * world * kAccStride + 64; }
+static size_t p2p_bytes(int world) { return sizeof(unsigned long long) * 4 * world * kAccStride + 64; }
 
 gsdf_status gsdf_p2p_export(gsdf_handle h, uint8_t handle64[64]) {
     if (!h || !handle64) return GSDF_ERR_INVALID;
@@ -1433,7 +1449,7 @@ gsdf_status gsdf_p2p_connect(gsdf_handle h, const uint8_t* handles /* world_size
     }
     h->px.world = world;
     h->px.rank = rank;
-    h->px.error = reinterpret_cast<int*>(reinterpret_cast<char*>(h->d_p2p) + sizeof(unsigned long long) * 2 * world * kAccStride);
+    h->px.error = reinterpret_cast<int*>(reinterpret_cast<char*>(h->d_p2p) + sizeof(unsigned long long) * 4 * world * kAccStride);
     h->p2p_connected = true;
     return GSDF_OK;
 }

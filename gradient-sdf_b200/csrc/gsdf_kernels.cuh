@@ -52,9 +52,10 @@ struct Lookup<0> {  // MapGradPixelSdf.h:109-125
         const int slot = cs;
         if (slot < 0) return 0.f;
         const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
+        // both loads issued before either is looked at: one memory round trip instead of two dependent ones
         const float W = m.accW[addr];
-        if (!(W > 0.f)) return 0.f;
         const float4 a = m.acc4[addr];
+        if (!(W > 0.f)) return 0.f;
         // phi and grad are tolerance-level quantities (sums of them are compared at 1e-4), not key-determining:
         // approximate reciprocal / rsqrt (<= 2 ulp) instead of IEEE division on the tracker's critical path
         const float dist = __fdividef(a.x, W);

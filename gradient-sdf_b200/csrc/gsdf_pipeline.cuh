@@ -195,13 +195,51 @@ __device__ __forceinline__ void track_pixel(const MapView& m, const FrameGeom& g
     }
 }
 
-constexpr int kTrackThreads = 384;
-constexpr int kTrackWarps = kTrackThreads / 32;
+// Same terms for the persistent tracker, which reduces every pixel's 29 products across the warp at once (the reduce-scatter
+// butterfly below) instead of carrying 29 accumulators per thread from pixel to pixel: v[0..31] = this pixel's products
+// (zeros if it does not contribute).
+template <int VARIANT>
+__device__ __forceinline__ void track_pixel_terms(const MapView& m, const FrameGeom& g, const TrackIntr& ti, const float* R,
+                                                  const float* t, bool has, int yx, float z, float* v,
+                                                  unsigned long long& ck, int& cs) {
+    const int y = yx >> 16, x = yx & 0xFFFF;
+    const float x0 = ((float)x - ti.cx) * ti.fx_inv, y0 = ((float)y - ti.cy) * ti.fy_inv;
+    const float cx_ = x0 * z, cy_ = y0 * z;
+    const float px = dot3_rn(R[0], R[1], R[2], cx_, cy_, z) + t[0];
+    const float py = dot3_rn(R[3], R[4], R[5], cx_, cy_, z) + t[1];
+    const float pz = dot3_rn(R[6], R[7], R[8], cx_, cy_, z) + t[2];
+    float phi = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f;
+    float w0 = 0.f;
+    if (has) w0 = Lookup<VARIANT>::eval(m, g, px, py, pz, phi, g0, g1, g2, ck, cs);
+    const bool on = w0 > 0.f;
+    if (!on) { phi = 0.f; g0 = g1 = g2 = 0.f; }
+    float J[6];
+    J[0] = g0; J[1] = g1; J[2] = g2;
+    J[3] = py * g2 - pz * g1;
+    J[4] = pz * g0 - px * g2;
+    J[5] = px * g1 - py * g0;
+    int o = 6;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+        v[a] = phi * J[a];
+#pragma unroll
+        for (int b = a; b < 6; ++b) v[o++] = J[a] * J[b];
+    }
+    v[27] = phi * phi;
+    v[28] = on ? 1.f : 0.f;
+    v[29] = v[30] = v[31] = 0.f;
+}
+
+// The persistent tracker runs either two 384-thread CTAs or one 768-thread CTA per SM (same threads per SM; the second
+// halves the rows of the grid-level exchange below).  64 registers per thread either way, so that one 512-thread,
+// 32-register CTA of the frame-only kernel fits beside it (shadow mode).
+constexpr int kTrackThreadsMax = 768;
 
 struct TrackParams {
     int max_iters;
     float thr_sq;
     float damping;
+    unsigned int poll_ns;  // pause between two polls of the grid-level exchange (0 = spin)
 };
 
 // Warp stage of the tree as a reduce-scatter butterfly: instead of 29 independent 5-step shuffle reductions
@@ -270,6 +308,89 @@ __device__ __forceinline__ void grid_reduce_29(const float* partials, int nblock
     }
 }
 
+// Grid-level stage of the persistent tracker: an all-to-all exchange of the CTA sums through tagged words, in place of
+// "write row, grid barrier, read all rows".  CTA b publishes its 29 sums as 64-bit words {pass tag, float bits} in
+// rows[tag & 1][b][0..28] (one store each, single-copy atomic: no fence, no separate flag, no arrival counter), and
+// every CTA polls ALL rows until each word carries this pass's tag, then adds them in row order: identical totals in
+// every CTA, bit-reproducible, ONE L2 round trip after the slowest CTA has published.  Two buffers suffice inside a
+// launch (a CTA can publish pass k+2 only after it has seen everyone's words of pass k+1, which they publish after they
+// have finished reading pass k); across launches the kernel boundary orders reuse, and tags never repeat (the host hands
+// every launch a fresh range).  A row that does not show up within 2 s sets barrier_timeout instead of hanging.
+__device__ __forceinline__ void st_word(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_word(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// CTA stage: lane L of every warp holds the warp's sum of term L -> the CTA's sums, returned in threads 0..28
+template <int NWARPS>
+__device__ __forceinline__ float block_sum_29(float mine, float (*sm)[kAccStride]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    sm[warp][lane] = mine;
+    __syncthreads();
+    float s = 0.f;
+    if (threadIdx.x < kAccTerms) {
+#pragma unroll
+        for (int wq = 0; wq < NWARPS; ++wq) s += sm[wq][threadIdx.x];
+    }
+    return s;
+}
+
+template <int NWARPS>
+__device__ __forceinline__ void exchange_29(unsigned long long* rows /* [2][gridDim.x][32] */, unsigned int tag, float mine,
+                                            float (*sm)[kAccStride] /* not the CTA stage's array */, float* tot,
+                                            Counters* ctr, unsigned int poll_ns) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nrows = gridDim.x;
+    unsigned long long* buf = rows + (size_t)(tag & 1u) * nrows * kAccStride;
+    const unsigned long long tg = (unsigned long long)tag << 32;
+    if (threadIdx.x < kAccTerms) st_word(buf + (size_t)blockIdx.x * kAccStride + threadIdx.x, tg | __float_as_uint(mine));
+    // warp w polls rows w, w + NWARPS, ...; lane = term.  All loads of a round are in flight together.
+    constexpr int kJ = 8;
+    float s = 0.f;
+    unsigned long long t0 = 0;
+    for (int r0 = warp; r0 < nrows; r0 += NWARPS * kJ) {
+        unsigned long long w[kJ];
+        unsigned int pend = 0;
+#pragma unroll
+        for (int j = 0; j < kJ; ++j)
+            if (lane < kAccTerms && r0 + j * NWARPS < nrows) pend |= 1u << j;
+        unsigned int spins = 0;
+        while (pend) {
+#pragma unroll
+            for (int j = 0; j < kJ; ++j)
+                if (pend & (1u << j)) w[j] = ld_word(buf + (size_t)(r0 + j * NWARPS) * kAccStride + lane);
+#pragma unroll
+            for (int j = 0; j < kJ; ++j)
+                if ((pend & (1u << j)) && (w[j] >> 32 << 32) == tg) pend &= ~(1u << j);
+            if (pend) {
+                // optional pause between polls (GSDF_POLL_NS; 0..800 ns measured: no effect on the frame rate, so the
+                // polling traffic is not what couples the tracker to the frame-only kernel beside it)
+                if (poll_ns) __nanosleep(poll_ns);
+                if ((++spins & 1023u) == 0) {
+                    const unsigned long long now = global_ns();
+                    if (t0 == 0) t0 = now;
+                    else if (now - t0 > 2000000000ull) { ctr->barrier_timeout = 1u; break; }
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kJ; ++j)
+            if (lane < kAccTerms && r0 + j * NWARPS < nrows) s += __uint_as_float((unsigned int)w[j]);
+    }
+    sm[warp][lane] = s;
+    __syncthreads();
+    if (threadIdx.x < kAccTerms) {
+        float r = 0.f;
+#pragma unroll
+        for (int wq = 0; wq < NWARPS; ++wq) r += sm[wq][threadIdx.x];
+        tot[threadIdx.x] = r;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Fusion over the compacted list: one lane per pixel walks its 2*factor+1 ray samples (MapGradPixelSdfOmp.cpp:103);
 // at every sample the warp merges the lanes that hit the SAME voxel (list entries of a warp come from the same
@@ -314,7 +435,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                                           const float* __restrict__ ny, const float* __restrict__ nz,
                                           const float* __restrict__ x0, const float* __restrict__ y0,
                                           const float* __restrict__ hom_inv, Counters* ctr, unsigned int& n_pts,
-                                          unsigned int& n_upd) {
+                                          unsigned int& n_upd, unsigned long long* fdbg = nullptr /* debug: [warp][8] stamps */) {
     const float* R = pose.R;
     const int lane = threadIdx.x & 31;
     const int S = 2 * g.factor + 1;
@@ -328,6 +449,12 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
     const int warps_total = (gridDim.x * blockDim.x) >> 5;
     const int wid = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     const int u1 = (int)(units * (wid + 1) / warps_total);
+    // debug stamps of this warp (lane 0): 0 entry, 1 first pixel data there, 2 first slot known, 3 first merge done, 4 first
+    // reductions issued, 5 all units done, 6 = units | probes << 32, 7 = reductions issued by the warp
+    unsigned long long* dbg = (fdbg && lane == 0) ? fdbg + (size_t)wid * 8 : nullptr;
+    unsigned int d_probes = 0, d_reds = 0;
+    bool d_first = true;
+    if (dbg) { dbg[0] = global_ns(); dbg[6] = (unsigned long long)(u1 - (int)(units * wid / warps_total)); }
     for (int u = (int)(units * wid / warps_total); u < u1;) {
         const int chunk = u / S, k_first = u - chunk * S;
         const int k_end = min(S, k_first + (u1 - u));  // exclusive
@@ -357,6 +484,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
             }
         }
         n_pts += (valid && k_first == 0) ? 1u : 0u;
+        if (dbg && d_first) dbg[1] = global_ns();
         unsigned long long last_key = kEmptyKey;
         int slot = -1;
         for (int kk = k_first - g.factor; kk < k_end - g.factor; ++kk) {               // :103
@@ -385,6 +513,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                         last_key = key;
                         slot = map_find_or_insert(m, key, ctr);
                         if (slot < 0) atomicAdd(&ctr->overflow, 1u);
+                        ++d_probes;
                     }
                     if (slot >= 0) {
                         has = true;
@@ -396,6 +525,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                     }
                 }
             }
+            if (dbg && d_first) dbg[2] = global_ns();
             if (!__any_sync(0xffffffffu, has)) continue;  // nothing to commit in this unit (outside the band / not ours)
             if (!has) {
 #pragma unroll
@@ -403,6 +533,8 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
             }
             bool leader;
             warp_merge_by_key<(VARIANT == 0 ? 5 : 2)>(vaddr, narrow, has, v, leader);
+            if (dbg && d_first) dbg[3] = global_ns();
+            if (fdbg) d_reds += __popc(__ballot_sync(0xffffffffu, leader));
             if (leader) {
                 if (VARIANT == 0) {
                     atomicAdd(m.acc4 + vaddr, make_float4(v[0], v[1], v[2], v[3]));    // :115-117
@@ -411,8 +543,10 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                     atomicAdd(m.acc2 + vaddr, make_float2(v[0], v[1]));                // MapPixelSdfOmp.cpp:183-185
                 }
             }
+            if (dbg && d_first) { dbg[4] = global_ns(); d_first = false; }
         }
     }
+    if (dbg) { dbg[5] = global_ns(); dbg[6] |= (unsigned long long)d_probes << 32; dbg[7] = d_reds; }
 }
 
 // statistics: warp -> CTA (shared-memory atomics) -> one slot per CTA; never thousands of warps on one word
@@ -469,31 +603,32 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// FALS normals (cv::NormalEstimator<float>::compute, normals/NormalEstimator.h:179-204) per 32x16 tile.  The masked
+// FALS normals (cv::NormalEstimator<float>::compute, normals/NormalEstimator.h:179-204) per 32 x TH tile.  The masked
 // reciprocal depth times the three cached planes is staged through shared memory with an r-pixel REFLECT_101 halo; the
 // window sums follow the oracle's order exactly (double accumulation; rows left->right, then columns top->bottom, one
 // rounding to float), so the normals — and therefore the validity tests that decide the voxel key set — are
 // bit-identical to the reference build.
 //   * tiles whose interior holds no z-valid pixel are skipped (fusion never reads normals of invalid pixels);
 //   * the z_inv products are widened to double once, when staged, instead of once per window tap.
+template <int TH /* tile height: 32 x TH threads */>
 __device__ __forceinline__ void normals_tile(const float* __restrict__ depth, const float* __restrict__ x0n,
                                              const float* __restrict__ y0n, const float* __restrict__ nsi,
                                              const float* __restrict__ Q, float* __restrict__ nx,
                                              float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r,
                                              float z_min, float z_max, int tile_x, int tile_y, int tix, int tiy,
                                              unsigned char* smem_raw) {
-    const int tw = NT_W + 2 * r, th = NT_H + 2 * r;
+    const int tw = NT_W + 2 * r, th = TH + 2 * r;
     double* a = reinterpret_cast<double*>(smem_raw);   // [3][th][tw] products, widened
     double* rs = a + 3 * tw * th;                      // [3][th][NT_W] row sums
     const int tid = tiy * NT_W + tix;
-    const int x_base = tile_x * NT_W, y_base = tile_y * NT_H;
+    const int x_base = tile_x * NT_W, y_base = tile_y * TH;
     const int x = x_base + tix, y = y_base + tiy;
     const size_t n = (size_t)w * h;
     const bool inside = x < w && y < h;
     const float zc = inside ? depth[(size_t)y * w + x] : 0.f;
     if (!__syncthreads_or(inside && z_valid(zc, z_min, z_max))) return;
 
-    for (int ly = tiy; ly < th; ly += NT_H) {
+    for (int ly = tiy; ly < th; ly += TH) {
         const int gy = reflect101(min(y_base + ly - r, h - 1 + r), h);
         for (int lx = tix; lx < tw; lx += NT_W) {
             const int gx = reflect101(min(x_base + lx - r, w - 1 + r), w);
@@ -508,7 +643,7 @@ __device__ __forceinline__ void normals_tile(const float* __restrict__ depth, co
     }
     __syncthreads();
     for (int p = 0; p < 3; ++p)
-        for (int ly = tiy; ly < th; ly += NT_H) {
+        for (int ly = tiy; ly < th; ly += TH) {
             const double* row = a + p * tw * th + ly * tw + tix;
             double s = 0.0;
             for (int d = 0; d <= 2 * r; ++d) s = __dadd_rn(s, row[d]);      // left -> right
@@ -540,8 +675,8 @@ normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x
                     const float* __restrict__ nsi, const float* __restrict__ Q, float* __restrict__ nx,
                     float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r, float z_min, float z_max) {
     extern __shared__ __align__(16) unsigned char smem_dyn[];
-    normals_tile(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
-                 threadIdx.y, smem_dyn);
+    normals_tile<NT_H>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
+                       threadIdx.y, smem_dyn);
 }
 
 // The frames one launch of track_kernel works through, in order (gsdf_scan_run hands it up to kMaxBatch frames whose
@@ -557,7 +692,7 @@ struct FrameBatch {
     float* normals[kMaxBatch];              // null: track only; else the 3 planes the fusion of frame f reads
     ResultSnapshot* snap[kMaxBatch];        // null, or where the result of frame f is left
     unsigned long long* flog[kMaxBatch];    // null, or frame f's entry of the debug frame log (words 2, 3)
-    unsigned long long* dbg;                // null, or [gridDim.x][4 passes][6] + [gridDim.x][4] %globaltimer stamps
+    unsigned long long* dbg;                // null, or [gridDim.x][4 passes][6] + [gridDim.x][4] + [warps][8] %globaltimer stamps
 };
 // element f of a kernel-parameter array without a runtime-indexed access (which would copy the array to local memory)
 template <typename T>
@@ -572,23 +707,34 @@ __device__ __forceinline__ T pick(T const (&a)[kMaxBatch], int f) {
 // whole-launch stamps, after the per-pass ones: [gridDim.x][4] = entry, Gauss-Newton loop left, fusion done, exit
 #define GSDF_STAMPX(i) do { if (fb.dbg && threadIdx.x == 0) fb.dbg[(size_t)gridDim.x * 24 + (size_t)blockIdx.x * 4 + (i)] = global_ns(); } while (0)
 
-// Frame-only work of the pipeline in ONE launch: each CTA compacts the z-valid pixels of its 32x16 tile (16 warps <->
-// its sixteen 8x4 sub-tiles, chained look-back over the CTAs for the exclusive prefix) and then computes the tile's
-// normals.  List order: 32x16 tiles row-major, 8x4 sub-tiles row-major inside, pixels row-major inside.
-__global__ void __launch_bounds__(NT_W* NT_H, 4)  // <= 32 registers: one CTA fits beside the resident tracker CTAs
+// Frame-only work of the pipeline in ONE launch: each CTA compacts the z-valid pixels of its 32 x 8 tile (8 warps <-> its
+// eight 8x4 sub-tiles) and then computes the tile's normals.  List order: 32x8 tiles row-major, 8x4 sub-tiles row-major
+// inside, pixels row-major inside.
+// 256-thread CTAs, not 512: beside the resident tracker (768 threads x 64 registers) the register file has room for 512
+// threads at 32 registers, and two independent CTAs hide each other's barriers and memory latency (the kernel is
+// latency-bound: ~10 % issue utilisation), where one 512-thread CTA stalls as a whole at every __syncthreads.
+// The exclusive prefix over CTAs is a decoupled look-back: a CTA publishes its count as {epoch, AGGREGATE, count}, looks
+// at its 32 predecessors at once, adds their counts back to the nearest one that already carries a PREFIX, and publishes
+// {epoch, PREFIX, inclusive sum} itself — one or two window reads instead of a poll of every lower-numbered CTA.
+// Lower-numbered CTAs are dispatched first and wait only on even lower ones, so the chain always makes progress; the
+// epoch makes clearing between launches unnecessary.
+constexpr int NC_H = 8;                                // tile height of normals_compact_kernel
+constexpr unsigned long long kLbPrefix = 1ull << 31;   // flag word = epoch << 32 | PREFIX bit | value (< 2^31)
+__global__ void __launch_bounds__(NT_W* NC_H, 8)  // <= 32 registers: two CTAs fit beside the resident tracker CTA
 normals_compact_kernel(const float* __restrict__ depth, const float* __restrict__ x0n, const float* __restrict__ y0n,
                        const float* __restrict__ nsi, const float* __restrict__ Q, float* __restrict__ nx,
                        float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r, float z_min, float z_max,
-                       unsigned int* __restrict__ flags, unsigned int epoch, int2* __restrict__ vlist,
+                       unsigned long long* __restrict__ flags, unsigned int epoch, int2* __restrict__ vlist,
                        int* __restrict__ n_valid_out, unsigned long long* flog) {
     extern __shared__ __align__(16) unsigned char smem_dyn[];
-    __shared__ int s_warp[NT_W * NT_H / 32];
+    constexpr int NWARP = NT_W * NC_H / 32;
+    __shared__ int s_warp[NWARP];
     __shared__ int s_base;
     const int tid = threadIdx.y * NT_W + threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) flog_enter(flog);
     const int cta = blockIdx.y * gridDim.x + blockIdx.x, ncta = gridDim.x * gridDim.y;
     const int px = blockIdx.x * NT_W + (warp & 3) * kTileW + (lane & 7);
-    const int py = blockIdx.y * NT_H + (warp >> 2) * kTileH + (lane >> 3);
+    const int py = blockIdx.y * NC_H + (warp >> 2) * kTileH + (lane >> 3);
     const bool in = px < w && py < h;
     const float z = in ? __ldg(depth + (size_t)py * w + px) : 0.f;
     const unsigned int mask = __ballot_sync(0xffffffffu, in && z_valid(z, z_min, z_max));
@@ -596,27 +742,37 @@ normals_compact_kernel(const float* __restrict__ depth, const float* __restrict_
     __syncthreads();
     int before = 0, total = 0;
 #pragma unroll
-    for (int q = 0; q < NT_W * NT_H / 32; ++q) { const int c = s_warp[q]; before += q < warp ? c : 0; total += c; }
-    if (tid == 0) atomicExch(flags + cta, (epoch << kFlagShift) | (unsigned)total);
-    if (total > 0 || cta == ncta - 1) {
-        if (warp == 0) {
-            int s = 0;
-            for (int b = lane; b < cta; b += 32) {
-                unsigned int f;
-                do { f = *reinterpret_cast<volatile unsigned int*>(flags + b); } while ((f >> kFlagShift) != epoch);
-                s += (int)(f & ((1u << kFlagShift) - 1));
+    for (int q = 0; q < NWARP; ++q) { const int c = s_warp[q]; before += q < warp ? c : 0; total += c; }
+    const unsigned long long ep = (unsigned long long)epoch << 32;
+    if (warp == 0) {
+        if (lane == 0) st_word(flags + cta, ep | (unsigned long long)total);
+        int excl = 0;
+        for (int look = cta - 1 - lane;; look -= 32) {     // window of 32 predecessors, nearest in lane 0
+            unsigned long long f = ep | kLbPrefix;          // before the first CTA: prefix 0
+            if (look >= 0) {
+                do { f = ld_word(flags + look); } while ((f >> 32) != epoch);
             }
-            s = __reduce_add_sync(0xffffffffu, s);
-            if (lane == 0) s_base = s;
+            const unsigned int pm = __ballot_sync(0xffffffffu, (f & kLbPrefix) != 0);
+            const int nearest = pm ? __ffs(pm) - 1 : 31;    // lanes beyond the nearest prefix do not count
+            excl += __reduce_add_sync(0xffffffffu, lane <= nearest ? (int)(f & (kLbPrefix - 1)) : 0);
+            if (pm) break;
         }
+        if (lane == 0) {
+            st_word(flags + cta, ep | kLbPrefix | (unsigned long long)(excl + total));
+            s_base = excl;
+            if (cta == ncta - 1) *n_valid_out = excl + total;
+        }
+    }
+    if (total > 0) {
         __syncthreads();
         if (mask & (1u << lane))
             vlist[s_base + before + __popc(mask & ((1u << lane) - 1))] = make_int2((py << 16) | px, __float_as_int(z));
-        if (cta == ncta - 1 && tid == 0) *n_valid_out = s_base + total;
+    } else {  // no valid pixel in the tile: fusion never reads its normals
+        if (tid == 0) flog_exit(flog);
+        return;
     }
-    if (total == 0) { if (tid == 0) flog_exit(flog); return; }  // no valid pixel in the tile: fusion never reads its normals
-    normals_tile(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
-                 threadIdx.y, smem_dyn);
+    normals_tile<NC_H>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
+                       threadIdx.y, smem_dyn);
     if (tid == 0) flog_exit(flog);
 }
 
@@ -645,23 +801,25 @@ __device__ __forceinline__ void grid_barrier(Counters* ctr, unsigned int target)
 }
 
 // Sharded maps: the all-reduce of the 29 sums INSIDE the tracker launch, over NVLink peer memory, with a
-// low-latency (flag-in-data) protocol: every rank owns an exchange buffer [2 parities][world][32] of 64-bit words;
+// low-latency (flag-in-data) protocol: every rank owns an exchange buffer [4][world][32] of 64-bit words;
 // after its grid-level reduction CTA 0 stores {pass tag, float bits} for each of its 29 sums into slot `rank` of EVERY
 // peer's buffer (one 8-byte store each, atomic, through the peer mapping) — no fence, no separate flag, so the cost
 // is ONE NVLink traversal.  All CTAs then spin on the words in their OWN memory until each carries the tag of this
 // pass and add the world partials in rank order: identical sums, hence identical poses and stopping decisions, on
-// every rank, with no NCCL launch and no host involvement inside the Gauss-Newton loop.  Parity double-buffering
-// suffices: a rank needs everyone's words of pass k+1 before it may publish pass k+2.
+// every rank, with no NCCL launch and no host involvement inside the Gauss-Newton loop.
 constexpr int kMaxPeers = 8;
 struct PeerExchange {
     unsigned long long* data[kMaxPeers];  // data[r]: rank r's exchange buffer (peer-mapped; data[rank] is local)
     int world, rank;                      // world <= 1: no exchange
     unsigned int epoch0;                  // pass k of this launch (counted over its frames) carries the tag epoch0 + k + 1
+    unsigned int launch;                  // launch counter (buffer parity across launches)
     int* error;                           // set to 1 if a peer did not show up in time
 };
 
 __device__ __forceinline__ void peer_allreduce_29(const PeerExchange& px, int k, float* s_tot) {
-    const int par = k & 1;
+    // four buffers: (launch parity, pass parity).  Inside a launch two suffice (see exchange_29); a rank that runs ahead
+    // into launch L+1 writes the other launch parity, and it can reach launch L+2 only after every peer has finished L.
+    const int par = ((int)(px.launch & 1u) << 1) | (k & 1);
     const unsigned long long ep = (unsigned long long)(px.epoch0 + (unsigned)k + 1u) << 32;
     __syncthreads();  // s_tot holds this rank's sums
     if (blockIdx.x == 0) {
@@ -690,19 +848,22 @@ __device__ __forceinline__ void peer_allreduce_29(const PeerExchange& px, int k,
     __syncthreads();
 }
 
-template <int VARIANT>
-__global__ void __launch_bounds__(512, 2)
+template <int VARIANT, int NT>
+__global__ void __launch_bounds__(NT == 384 ? 512 : 1024, NT == 384 ? 2 : 1)  // 64 registers per thread (see kTrackThreadsMax)
 track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
-             float* __restrict__ partials /* [2][gridDim.x][kAccStride] */, TrackParams tp,
-             const float* __restrict__ planes /* the 11 cached FALS planes */, Counters* ctr, FrameBatch fb,
+             unsigned long long* __restrict__ rows /* [2][gridDim.x][kAccStride] tagged words */, unsigned int tag0,
+             TrackParams tp, const float* __restrict__ planes /* the 11 cached FALS planes */, Counters* ctr, FrameBatch fb,
              PeerExchange px) {
+    constexpr int NW = NT / 32;
     unsigned int barriers = 0;  // grid barriers passed so far in this launch
-    int pass_id = 0;            // Gauss-Newton passes run so far in this launch (buffer parity, tags of the peer exchange)
+    int pass_id = 0;            // Gauss-Newton passes run so far in this launch (tags of both exchanges)
     __shared__ float s_pose7[8];
     __shared__ Pose s_pose;
     __shared__ float s_tot[kAccStride];
-    __shared__ float s_warp[kTrackWarps][kAccStride];
+    __shared__ float s_warp[NW][kAccStride];   // CTA stage of the reduction
+    __shared__ float s_part[NW][kAccStride];   // grid stage
     __shared__ int s_conv;
+    __shared__ float s_valid_sum;  // contributing pixels summed over the frame's passes (thread 0)
     GSDF_STAMPX(0);
     // pixel j of the list -> warp-sized chunk j/32 -> CTA (chunk % grid), warp (chunk / grid): a frame with fewer valid
     // pixels than resident threads (the usual case: ~90 k of 114 k) is spread over ALL SMs instead of filling the
@@ -725,48 +886,50 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
         if (f > 0) {
             // every CTA's fusion of the previous frame (and its statistics) is complete before anyone reads the map again
             grid_barrier(ctr, ++barriers * gridDim.x);
-            // CTA 0 publishes the previous frame; it does so before it arrives at this frame's first pass barrier, so no
-            // CTA can have added statistics of this frame yet
+            // CTA 0 publishes the previous frame; it does so before it publishes its sums of this frame's first pass, which
+            // every CTA waits for before it can reach this frame's fusion, so no statistics of this frame are in yet
             ResultSnapshot* prev = pick(fb.snap, f - 1);
             if (blockIdx.x == 0 && prev != nullptr) write_snapshot(st, ctr, prev, px.world > 1 ? px.error : nullptr);
         }
         if (threadIdx.x == 0 && flog) flog_enter(flog + 2);
         int converged = 0, k = 0;
-        float valid_sum = 0.f;
         unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
         int cs = -1;
         __syncthreads();
         if (threadIdx.x == 0) {
             quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
             s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+            s_valid_sum = 0.f;
         }
         __syncthreads();
-        const bool has0 = gtid < n_valid;
         for (k = 0; k < tp.max_iters; ++k, ++pass_id) {
-            float acc[kAccTerms];
-#pragma unroll
-            for (int i = 0; i < kAccTerms; ++i) acc[i] = 0.f;
             GSDF_STAMP(0);
-            if (has0) track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e0.x, __int_as_float(e0.y), acc, ck, cs);
-            for (int j = gtid + nthreads; j < n_valid; j += nthreads) {
-                const int2 e = __ldcg(vlist + j);
-                track_pixel<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e.x, __int_as_float(e.y), acc, ck, cs);
+            // every pixel's 29 products are reduced across the warp at once: lane L keeps the warp's running sum of term L
+            // (the loop bound is the chunk's first entry, so whole warps run it together)
+            float wsum = 0.f;
+#pragma unroll 1
+            for (int j = gtid; (j & ~31) < n_valid; j += nthreads) {
+                const bool has = j < n_valid;
+                const int2 e = j == gtid ? e0 : (has ? __ldcg(vlist + j) : make_int2(0, 0));
+                float v[32];
+                track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ck, cs);
+                wsum += warp_reduce_scatter_32(v);
             }
             GSDF_STAMP(1);
-            float* mine = partials + ((size_t)(pass_id & 1) * gridDim.x + blockIdx.x) * kAccStride;
-            block_reduce_29<kTrackWarps>(acc, s_warp, mine);
+            const float mine = block_sum_29<NW>(wsum, s_warp);
             GSDF_STAMP(2);
-            grid_barrier(ctr, ++barriers * gridDim.x);
+            exchange_29<NW>(rows, tag0 + (unsigned)pass_id + 1u, mine, s_part, s_tot, ctr, tp.poll_ns);
             GSDF_STAMP(3);
-            grid_reduce_29<kTrackWarps>(partials + (size_t)(pass_id & 1) * gridDim.x * kAccStride, gridDim.x, s_warp, s_tot);
             if (px.world > 1) peer_allreduce_29(px, pass_id, s_tot);
-            __syncthreads();
             GSDF_STAMP(4);
-            if (threadIdx.x == 0) {
-                valid_sum += s_tot[28];
-                s_conv = gauss_newton_step(s_tot, tp.damping, tp.thr_sq, s_pose7);
-                quat_to_R(s_pose7 + 3, s_pose.R);
-                s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+            if (threadIdx.x < 32) {  // (s_tot was written by threads 0..28 of this warp)
+                __syncwarp();
+                if (threadIdx.x == 0) {
+                    s_valid_sum += s_tot[28];
+                    s_conv = gauss_newton_step(s_tot, tp.damping, tp.thr_sq, s_pose7);
+                    quat_to_R(s_pose7 + 3, s_pose.R);
+                    s_pose.t[0] = s_pose7[0]; s_pose.t[1] = s_pose7[1]; s_pose.t[2] = s_pose7[2];
+                }
             }
             __syncthreads();
             GSDF_STAMP(5);
@@ -781,7 +944,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
                 st->converged = converged;
                 st->iters = converged ? k : tp.max_iters;
                 st->track_iters += (unsigned long long)(converged ? k + 1 : tp.max_iters);
-                st->track_valid += (unsigned long long)valid_sum;
+                st->track_valid += (unsigned long long)s_valid_sum;
             }
             __threadfence();  // the snapshot of this frame is read back from L2 (by other threads of this CTA, or by the last CTA)
         }
@@ -791,7 +954,8 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
             const size_t np = (size_t)g.w * g.h;
             unsigned int n_upd = 0, n_pts = 0;
             fuse_work<VARIANT, true>(m, g, s_pose, vlist, n_valid, fuse_normals, fuse_normals + np, fuse_normals + 2 * np,
-                                     planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd);
+                                     planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd,
+                                     fb.dbg ? fb.dbg + (size_t)gridDim.x * 28 : nullptr);
             fuse_stats_flush(ctr, n_pts, n_upd);
         }
         GSDF_STAMPX(2);

@@ -15,6 +15,18 @@ namespace gsdf {
 
 #define GSDF_HD __host__ __device__ __forceinline__
 
+// On the device the solve and the pose update sit on the critical path of every Gauss-Newton pass of the persistent
+// tracker (one thread per CTA, everyone else waits): fused multiply-adds and reciprocal-based divisions there.  These are
+// tolerance-level quantities (poses are compared at 1e-4 .. 2e-3), not key-determining ones; the host versions keep
+// Eigen's / Sophus' separate roundings (the library is compiled with -fmad=false, explicit fmaf still fuses).
+#ifdef __CUDA_ARCH__
+#define GSDF_FMA(a, b, c) fmaf((a), (b), (c))
+#define GSDF_DIV(a, b) __fdividef((a), (b))
+#else
+#define GSDF_FMA(a, b, c) ((a) * (b) + (c))
+#define GSDF_DIV(a, b) ((a) / (b))
+#endif
+
 GSDF_HD float dot3p(const float* a, const float* b) {
     const float p0 = a[0] * b[0], s = a[1] * b[1] + a[2] * b[2];  // Eigen: a0*b0 + (a1*b1 + a2*b2)
     return p0 + s;
@@ -23,9 +35,16 @@ GSDF_HD void matvec3p(const float* R, const float* v, float* o) {
     o[0] = dot3p(R, v); o[1] = dot3p(R + 3, v); o[2] = dot3p(R + 6, v);
 }
 GSDF_HD void quat_normalize(float* q) {  // Eigen sums the 4-float packet as (x^2 + z^2) + (y^2 + w^2)
-    const float len = sqrtf((q[0] * q[0] + q[2] * q[2]) + (q[1] * q[1] + q[3] * q[3]));
+    const float n2 = (q[0] * q[0] + q[2] * q[2]) + (q[1] * q[1] + q[3] * q[3]);
+#ifdef __CUDA_ARCH__
+    const float il = rsqrtf(n2);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) q[i] *= il;
+#else
+    const float len = sqrtf(n2);
 #pragma unroll
     for (int i = 0; i < 4; ++i) q[i] /= len;
+#endif
 }
 GSDF_HD void quat_to_R(const float* q, float* R) {
     const float x = q[0], y = q[1], z = q[2], w = q[3];
@@ -69,7 +88,7 @@ GSDF_HD void se3_exp(const float* a, float* q, float* tr) {
     } else {
         theta = sqrtf(theta_sq);
         const float half = 0.5f * theta;
-        imag = sinf(half) / theta;
+        imag = GSDF_DIV(sinf(half), theta);
         real = cosf(half);
     }
     q[0] = imag * om[0]; q[1] = imag * om[1]; q[2] = imag * om[2]; q[3] = real;
@@ -84,7 +103,7 @@ GSDF_HD void se3_exp(const float* a, float* q, float* tr) {
         quat_to_R(q, V);
     } else {
         const float tsq = theta * theta;
-        const float c1 = (1.f - cosf(theta)) / tsq, c2 = (theta - sinf(theta)) / (tsq * theta);
+        const float c1 = GSDF_DIV(1.f - cosf(theta), tsq), c2 = GSDF_DIV(theta - sinf(theta), tsq * theta);
 #pragma unroll
         for (int i = 0; i < 9; ++i) V[i] = ((i % 4 == 0 ? 1.f : 0.f) + c1 * O[i]) + c2 * O2[i];
     }
@@ -125,7 +144,7 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
         float x = A[6 * k + k];
 #pragma unroll
         for (int j = 0; j < 6; ++j)
-            if (j < k) x -= A[6 * k + j] * A[6 * k + j];
+            if (j < k) x = GSDF_FMA(-A[6 * k + j], A[6 * k + j], x);
         const bool good = ok && !(x <= 0.f);
 #ifdef __CUDA_ARCH__
         // on the device one MUFU.RSQ (2 ulp) replaces the IEEE square root and reciprocal (two ~60-cycle sequences on
@@ -137,14 +156,14 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
         const float ir = 1.f / r;
 #endif
         A[6 * k + k] = good ? r : A[6 * k + k];
-        inv[k] = good ? ir : 1.f / A[6 * k + k];
+        inv[k] = good ? ir : GSDF_DIV(1.f, A[6 * k + k]);
 #pragma unroll
         for (int i = 0; i < 6; ++i)
             if (i > k) {
                 float s = A[6 * i + k];
 #pragma unroll
                 for (int j = 0; j < 6; ++j)
-                    if (j < k) s -= A[6 * i + j] * A[6 * k + j];
+                    if (j < k) s = GSDF_FMA(-A[6 * i + j], A[6 * k + j], s);
                 A[6 * i + k] = good ? s * ir : A[6 * i + k];
             }
         ok = good;
@@ -154,7 +173,7 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
         float s = g6[i];
 #pragma unroll
         for (int j = 0; j < 6; ++j)
-            if (j < i) s -= A[6 * i + j] * y[j];
+            if (j < i) s = GSDF_FMA(-A[6 * i + j], y[j], s);
         y[i] = s * inv[i];
     }
 #pragma unroll
@@ -163,7 +182,7 @@ GSDF_HD void llt_solve6(const float* H36, const float* g6, float* xi6) {
         float s = y[i];
 #pragma unroll
         for (int j = 0; j < 6; ++j)
-            if (j > i) s -= A[6 * j + i] * x6[j];
+            if (j > i) s = GSDF_FMA(-A[6 * j + i], x6[j], s);
         x6[i] = s * inv[i];
     }
 #pragma unroll

@@ -28,11 +28,11 @@ n = C.c_int32(0)
 sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, None, C.byref(n)))
 opt.set_pose(poses[5])
 conv = opt.optimize(frames[6])
-raw = np.zeros(n.value * 28, np.uint64)
+raw = np.zeros(n.value * 220, np.uint64)
 sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, raw.ctypes.data, C.byref(n)))
 t = raw[: n.value * 24].reshape(n.value, 4, 6).astype(np.int64)
 print(variant, "ctas", n.value, "converged", conv, "iters", opt.last_iterations)
-names = ["lookups", "cta reduce", "grid barrier", "grid reduce", "solve"]
+names = ["lookups", "cta reduce", "exchange", "peer exch", "solve"]
 for k in range(min(4, opt.last_iterations + 1)):
     tk = t[:, k, :]
     ok = tk[:, 0] > 0
@@ -57,9 +57,10 @@ def anatomy(tag, inflight):
     for i in range(20, 20 + inflight):
         sdf.scan_submit(depth_host=frames[i], track=True)
     res = [sdf.scan_collect() for _ in range(inflight)]
-    raw = np.zeros(n.value * 28, np.uint64)
+    raw = np.zeros(n.value * 220, np.uint64)
     sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, raw.ctypes.data, C.byref(n)))
-    x = raw[n.value * 24:].reshape(n.value, 4).astype(np.int64)
+    x = raw[n.value * 24:n.value * 28].reshape(n.value, 4).astype(np.int64)
+    fw = raw[n.value * 28:].reshape(-1, 8).astype(np.int64)
     p = raw[: n.value * 24].reshape(n.value, 4, 6).astype(np.int64)
     t0 = x[:, 0].min()
     f = lambda a: f"first {(a.min() - t0) / 1e3:6.2f}  mean {(a.mean() - t0) / 1e3:6.2f}  last {(a.max() - t0) / 1e3:6.2f}"
@@ -70,6 +71,21 @@ def anatomy(tag, inflight):
     print("   loop left      ", f(x[:, 1]))
     print("   fusion done    ", f(x[:, 2]))
     print("   exit           ", f(x[:, 3]))
+    # per-warp anatomy of the fusion phase (warps that had work)
+    fw = fw[fw[:, 0] > 0]
+    if len(fw):
+        units, probes, reds = fw[:, 6] & 0xFFFFFFFF, fw[:, 6] >> 32, fw[:, 7]
+        busy = fw[units > 0]
+        d = lambda a, b: (busy[:, b] - busy[:, a]) / 1e3
+        print(f"   fusion per warp: {len(busy)} of {len(fw)} warps had units; units/warp {units.mean():.2f} (max {units.max()}), "
+              f"probes/warp {probes.mean():.2f}, reductions/warp {reds.mean():.1f}")
+        print(f"      warp total        mean {d(0, 5).mean():6.2f}  max {d(0, 5).max():6.2f} us")
+        print(f"      pixel data        mean {d(0, 1).mean():6.2f}  max {d(0, 1).max():6.2f} us")
+        print(f"      first slot known  mean {d(1, 2).mean():6.2f}  max {d(1, 2).max():6.2f} us")
+        print(f"      first merge       mean {d(2, 3).mean():6.2f}  max {d(2, 3).max():6.2f} us")
+        print(f"      first reds issued mean {d(3, 4).mean():6.2f}  max {d(3, 4).max():6.2f} us")
+        print(f"      remaining units   mean {d(4, 5).mean():6.2f}  max {d(4, 5).max():6.2f} us")
+        print(f"      entry spread {(fw[:, 0].max() - fw[:, 0].min()) / 1e3:.2f} us, end spread {(fw[:, 5].max() - fw[:, 5].min()) / 1e3:.2f} us")
 
 
 anatomy("one frame in flight", 1)
