@@ -37,21 +37,30 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=150)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--variant", default="base", choices=["base", "grad"])
+    ap.add_argument("--variant", default="grad", choices=["base", "grad"])
     ap.add_argument("--voxel-size", type=float, default=0.01)
     ap.add_argument("--trunc", type=float, default=5.0)
     ap.add_argument("--log2-capacity", type=int, default=17)
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=20.0, help="bound of the cpu_baseline leg")
     ap.add_argument("--ref-budget-s", type=float, default=150.0, help="bound of the --impl reference run")
-    ap.add_argument("--no-extra", action="store_true", help="skip the secondary grad-sdf measurement")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary measurement of the other variant")
+    ap.add_argument("--reps", type=int, default=9, help="timed repetitions of the K-step pass (the median is reported)")
     return ap.parse_args()
 
 
 def workload_name(variant, vs, trunc):
-    tag = "C2" if (variant == "base" and abs(vs - 0.01) < 1e-9) else "custom"
+    one_cm = abs(vs - 0.01) < 1e-9 and abs(trunc - 5.0) < 1e-9
+    tag = ("Target (north_star: grad-sdf track+fuse, 640x480, 1 cm)" if (variant == "grad" and one_cm)
+           else "C2" if (variant == "base" and one_cm) else "custom")
     return (f"{tag}: Scan3D {variant}-sdf track+fuse, synthetic 5-sphere RenderSpheres-style sequence, "
             f"{W_IMG}x{H_IMG} depth, {vs * 1000:g} mm voxels, trunc {trunc:g}")
+
+
+def bench_config(args):
+    """The `config` object: identical keys and values in both arms (ours and --impl reference)."""
+    return {"workload": workload_name(args.variant, args.voxel_size, args.trunc), "width": W_IMG, "height": H_IMG,
+            "voxel_size": args.voxel_size, "trunc": args.trunc, "variant": args.variant}
 
 
 def make_frames(n_needed):
@@ -258,8 +267,7 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": done, "requested_steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t_total / max(1, done), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args.variant, args.voxel_size, args.trunc), "width": W_IMG,
-                   "height": H_IMG, "voxel_size": args.voxel_size, "trunc": args.trunc, "variant": args.variant},
+        "config": bench_config(args),
         "cpu_baseline": base,
         "e2e": {"value": base["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -368,7 +376,9 @@ def run_ours(args):
             ptrs = [dev_frames[f].data_ptr() if mode == "dev" else host_np[f].ctypes.data for f in timed]
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(ext)
-            results = sdf.scan_run(ptrs, on_device=(mode == "dev"), track=True)
+            tw0 = time.perf_counter()
+            results = sdf.scan_run(ptrs, on_device=(mode == "dev"), track=True)  # returns with every result on the host
+            st["run_wall_s"] = time.perf_counter() - tw0
             e1.record(ext)
             events.append((e0, e1))
         else:
@@ -431,8 +441,16 @@ def run_ours(args):
         sdf = make_map(variant)
         sampler = make_sampler(local_rank) if rank == 0 else None
         run_pass(sdf, "dev", do_flush=False)       # discarded: first touch of every buffer, clocks ramp up
-        a = run_pass(sdf, "dev", do_flush=False)   # headline: pipelined, frames resident in HBM
-        b = run_pass(sdf, "host")                  # end to end from pinned host frames
+        # headline: pipelined, frames resident in HBM; and end to end from pinned host frames — `reps` passes each,
+        # interleaved, the MEDIAN pass is reported (one pass of 150 frames is a few milliseconds)
+        reps_a, reps_b = [], []
+        for _ in range(max(1, args.reps)):
+            reps_a.append(run_pass(sdf, "dev", do_flush=False))
+            reps_b.append(run_pass(sdf, "host"))
+        spans_a = sorted(max_over_ranks(r["span_ms"]) for r in reps_a)
+        walls_b = sorted(max_over_ranks(r["run_wall_s"]) for r in reps_b)
+        a = min(reps_a, key=lambda r: abs(r["span_ms"] - statistics.median(r2["span_ms"] for r2 in reps_a)))
+        b = min(reps_b, key=lambda r: abs(r["run_wall_s"] - statistics.median(r2["run_wall_s"] for r2 in reps_b)))
         a2 = run_pass(sdf, "dev", do_flush=True)   # conservative: one frame at a time, L2 flushed before each
         clocks = sampler.stop() if sampler else None
         a3 = run_pass(sdf, "dev", do_flush=False, flog=True)  # same as a, with the in-kernel span log armed
@@ -443,8 +461,9 @@ def run_ours(args):
         n_p, ms_p = sdf.profile_read(3)
         nv, nb = sdf.voxel_count()
         K_steps = args.steps
-        t_dev = max_over_ranks(a["span_ms"])       # no untimed gaps: first submit -> last result on the stream
-        t_host = max_over_ranks(b["span_ms"])
+        t_dev = statistics.median(spans_a)         # no untimed gaps: first submit -> last result on the stream
+        t_host = 1e3 * statistics.median(walls_b)  # HOST wall clock around gsdf_scan_run (the call a user makes)
+        t_host_span = max_over_ranks(b["span_ms"])
         t_dev_nf = max_over_ranks(a2["t_ms"])      # sum of the per-frame intervals (flush outside them)
         upd_total = sum_over_ranks(a["updates"])
         npx = W_IMG * H_IMG
@@ -456,7 +475,10 @@ def run_ours(args):
         nrm_bytes = n_n * npx * (4 + 36 + 12)
         res = {
             "variant": variant, "frames_per_s": 1e3 * K_steps / t_dev, "ms_per_step": t_dev / K_steps,
-            "e2e_frames_per_s": 1e3 * K_steps / t_host, "frames_per_s_l2_flushed": 1e3 * K_steps / t_dev_nf,
+            "e2e_frames_per_s": 1e3 * K_steps / t_host, "e2e_frames_per_s_event_span": 1e3 * K_steps / t_host_span,
+            "frames_per_s_l2_flushed": 1e3 * K_steps / t_dev_nf,
+            "reps": {"n": len(spans_a), "value_min": 1e3 * K_steps / spans_a[-1], "value_max": 1e3 * K_steps / spans_a[0],
+                     "e2e_min": K_steps / walls_b[-1], "e2e_max": K_steps / walls_b[0]},
             "track_iters": c["track_iters"], "nrm_bytes": nrm_bytes, "voxel_updates_per_s": 1e3 * c["updates"] / max(ms_f, 1e-9),
             "updates_per_frame": upd_total / max(1, a["conv"]), "converged_steps": a["conv"],
             "gn_iterations": a["iters"], "launches": a["launches"], "voxels": nv, "blocks": nb,
@@ -505,9 +527,14 @@ def run_ours(args):
                  f"{main['track_iters'] / max(1, n_a):.2f} passes, + the fusion)")
         per_launch_bytes, per_launch_ms = main["fused_bytes_per_frame"] * fpl, an["track_fuse_kernel"] * fpl / 1e3
     achieved = per_launch_bytes / max(per_launch_ms, 1e-12) / 1e6  # GB/s
+    # DRAM traffic from the ncu capture of this kernel (profiles/ncu_traffic.json): captured on a 4-frame launch, scaled
+    # to the frames per launch this run actually timed
+    traffic = ncu_traffic(kname.split(" ")[0])
+    if traffic is not None and an and world == 1:
+        traffic = traffic * (args.steps / max(1, main["launches"] - args.steps)) / 4.0
     step_ms = main["ms_per_step"] * args.steps
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "peak_source": peak_src,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(kname.split(" ")[0]),
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "algorithmic_bytes_per_launch": per_launch_bytes, "us_per_launch": 1e3 * per_launch_ms,
                 "kernel_share_of_step": {"fuse": ms_f / step_ms, "track": ms_a / step_ms, "normals": ms_n / step_ms},
                 "pipeline_anatomy_us": an,
@@ -527,27 +554,29 @@ def run_ours(args):
         "metric": "scan3d_track_fuse_frames_per_s", "value": main["frames_per_s"], "unit": "frames/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": main["ms_per_step"],
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args.variant, args.voxel_size, args.trunc), "width": W_IMG,
-                   "height": H_IMG, "voxel_size": args.voxel_size, "trunc": args.trunc, "variant": args.variant,
-                   "parallelism": "single GPU" if world == 1 else f"voxel-block hash sharded over {world} GPUs, 29-float "
-                   "all-reduce per Gauss-Newton pass " + ("inside the tracker launch over NVLink peer memory"
-                                                           if os.environ.get("GSDF_P2P", "1") == "1" else "with NCCL"),
-                   "l2": f"inputs larger than L2: {n_needed} distinct frames = {n_needed * npx * 4 / 1e6:.0f} MB streamed "
-                         "once (L2 = 126 MB); the map is state carried from frame to frame by design; "
-                         "value_l2_flushed_unpipelined = one frame in flight, 256 MiB L2 flush before each",
-                   "timing": "K / device-timeline span (CUDA events on the library's stream) from the first timed submit "
-                             "to the last result, up to 12 frames in flight, no untimed gaps, max over ranks; every pass = "
-                             "reset map, frame 0 fused, W warm-up frames, K timed frames; one whole pass is run and "
-                             "discarded before the first timed one",
-                   "api": "gsdf_scan_run (the frame loop in C: up to 4 frames per tracker launch, uploads and frame-only "
-                          "kernels ahead of it)"},
+        "config": bench_config(args),
+        "notes": {"parallelism": "single GPU" if world == 1 else f"voxel-block hash sharded over {world} GPUs, 29-float "
+                  "all-reduce per Gauss-Newton pass " + ("inside the tracker launch over NVLink peer memory"
+                                                          if os.environ.get("GSDF_P2P", "1") == "1" else "with NCCL"),
+                  "l2": f"inputs larger than L2: {n_needed} distinct frames = {n_needed * npx * 4 / 1e6:.0f} MB streamed "
+                        "once per pass (L2 = 126 MB); the map is state carried from frame to frame by design; "
+                        "value_l2_flushed_unpipelined = one frame in flight, 256 MiB L2 flush before each",
+                  "timing": f"median of {args.reps} passes; value = K / device-timeline span (CUDA events on the library's "
+                            "stream) from the first timed submit to the last result, up to 12 frames in flight, no untimed "
+                            "gaps, max over ranks; every pass = reset map, frame 0 fused, W warm-up frames, K timed frames; "
+                            "one whole pass is run and discarded before the first timed one",
+                  "api": "gsdf_scan_run (the frame loop in C: up to 4 frames per tracker launch, uploads and frame-only "
+                         "kernels ahead of it)"},
         "voxel_updates_per_s": main["voxel_updates_per_s"], "updates_per_frame": main["updates_per_frame"],
         "converged_steps": main["converged_steps"], "gn_iterations_per_step": iters_per_step,
         "map": {"voxels": main["voxels"], "blocks": main["blocks"]},
         "e2e": {"value": main["e2e_frames_per_s"], "unit": "frames/s", "h2d_bytes_per_step": npx * 4,
                 "d2h_bytes_per_step": 224,
-                "timing": "K / device-timeline span from the first submit to the last result, pinned host frames, "
-                          "uploads on the copy stream overlapped with the previous frame, no L2 flush, no gaps"},
+                "event_span_value": main["e2e_frames_per_s_event_span"],
+                "timing": "K / HOST wall clock around the one gsdf_scan_run call (returns when the last result is on the "
+                          "host), pinned host frames, uploads on the copy stream overlapped with the previous frames; "
+                          "median of the repetitions; event_span_value = the same passes by CUDA events"},
+        "repetitions": main["reps"],
         "value_l2_flushed_unpipelined": main["frames_per_s_l2_flushed"],
         "gpu_launches": main["launches"], "clocks": main["clocks"], "roofline": roofline, "cpu_baseline": cpu_base,
         "kernel_ms_total": main["kernel_ms"],
