@@ -36,7 +36,7 @@ EXPORTS = [
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
     "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_scan_run", "gsdf_upload", "gsdf_host_alloc", "gsdf_host_free", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_debug_frame_log", "gsdf_p2p_export", "gsdf_p2p_connect", "gsdf_comm_unique_id", "gsdf_comm_init",
-    "gsdf_version",
+    "gsdf_extract_mesh", "gsdf_version",
 ]
 
 
@@ -97,6 +97,7 @@ def lib() -> C.CDLL:
     L.gsdf_query.argtypes = [H, _f32p, C.c_int64, _f32p, _f32p, _f32p]
     L.gsdf_voxel_count.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gsdf_download.argtypes = [H, C.c_int64, _i32p, _f32p, _f32p, _f32p, C.POINTER(C.c_int64)]
+    L.gsdf_extract_mesh.argtypes = [H, C.c_int64, _f32p, C.POINTER(C.c_int64)]
     L.gsdf_pose_matrix.restype = None
     L.gsdf_pose_matrix.argtypes = [_f32p, _f32p, _f32p]
     L.gsdf_pose_apply_increment.restype = None
@@ -421,6 +422,16 @@ class Sdf:
             order = np.lexsort((keys[:, 2], keys[:, 1], keys[:, 0]))
             keys, dist, weight, grad = keys[order], dist[order], weight[order], grad[order]
         return keys, dist, weight, grad
+
+    def extract_mesh(self):
+        """Sdf::extract_mesh (marching cubes, MapGradPixelSdfOmp.cpp:132-183): triangles as an (n, 3, 3) float array in the
+        reference's order; vertex i of the reference's PLY is .reshape(-1, 3)[i], face f is (3f, 3f+1, 3f+2)."""
+        n = C.c_int64(0)
+        self._check(self.L.gsdf_extract_mesh(self.h, 0, None, C.byref(n)))
+        v = np.zeros((n.value, 3, 3), np.float32)
+        if n.value:
+            self._check(self.L.gsdf_extract_mesh(self.h, n.value, _fp(v), C.byref(n)))
+        return v
 
 
 class MapGradPixelSdf(Sdf):

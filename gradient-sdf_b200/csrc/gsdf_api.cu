@@ -10,6 +10,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -19,6 +20,7 @@
 #include <vector>
 
 #include "gsdf_pipeline.cuh"
+#include "gsdf_mesh.cuh"
 
 using namespace gsdf;
 
@@ -977,6 +979,70 @@ gsdf_status gsdf_upload(gsdf_handle h, int64_t n, const int32_t* keys, const flo
         s = check_overflow(h);
     } while (0);
     cudaFree(d_keys); cudaFree(d_f);
+    return s;
+}
+
+// Sdf::extract_mesh (MapGradPixelSdfOmp.cpp:132-183, MapPixelSdfOmp.cpp:197-248): marching cubes over the block hash on the
+// device (gsdf_mesh.cuh), triangles returned in the reference's sweep order.
+gsdf_status gsdf_extract_mesh(gsdf_handle h, int64_t max_triangles, float* vertices9, int64_t* n_triangles) {
+    if (!h || !n_triangles || max_triangles < 0) return GSDF_ERR_INVALID;
+    *n_triangles = 0;
+    if (h->cfg.world_size > 1) { h->err = "gsdf_extract_mesh: single-GPU maps only (merge the shards with gsdf_download / gsdf_upload first)"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    int* d_box = nullptr;
+    unsigned long long* d_keys = nullptr;
+    float* d_verts = nullptr;
+    CUDA_TRY(h, cudaMalloc(&d_box, sizeof(int) * 6 + sizeof(unsigned long long) * 2));
+    unsigned long long* d_total = reinterpret_cast<unsigned long long*>(d_box + 6);
+    const int grid = (int)std::min<size_t>(h->cap, (size_t)h->sm_count * 16);
+    do {
+        const int init[6] = {INT_MAX, INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MIN};
+        int box6[6];
+        if (cudaMemcpyAsync(d_box, init, sizeof(init), cudaMemcpyHostToDevice, h->stream) != cudaSuccess ||
+            cudaMemsetAsync(d_total, 0, sizeof(unsigned long long) * 2, h->stream) != cudaSuccess) { h->err = "extract_mesh: init failed"; s = GSDF_ERR_CUDA; break; }
+        s = by_variant(h, [&](auto V) {
+            mesh_bbox_kernel<decltype(V)::value><<<h->sm_count * 8, 256, 0, h->stream>>>(h->view, d_box);
+            return check_launch(h, "mesh_bbox_kernel");
+        });
+        if (s != GSDF_OK) break;
+        if (cudaMemcpyAsync(box6, d_box, sizeof(box6), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaStreamSynchronize(h->stream) != cudaSuccess) { h->err = "extract_mesh: bounding box failed"; s = GSDF_ERR_CUDA; break; }
+        if (box6[0] == INT_MAX) break;  // empty map: no triangles
+        MeshBox box;
+        for (int c = 0; c < 3; ++c) { box.min[c] = box6[c]; box.dim[c] = box6[3 + c] - box6[c] + 1; }
+        s = by_variant(h, [&](auto V) {
+            mesh_kernel<decltype(V)::value, false><<<grid, 256, 0, h->stream>>>(h->view, box, h->geom.vs, d_total, 0, nullptr, nullptr);
+            return check_launch(h, "mesh_kernel(count)");
+        });
+        if (s != GSDF_OK) break;
+        unsigned long long total = 0;
+        if (cudaMemcpyAsync(&total, d_total, sizeof(total), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaStreamSynchronize(h->stream) != cudaSuccess) { h->err = "extract_mesh: count failed"; s = GSDF_ERR_CUDA; break; }
+        *n_triangles = (int64_t)total;
+        if (!vertices9 || total == 0) break;  // count only
+        if ((int64_t)total > max_triangles) { h->err = "gsdf_extract_mesh: max_triangles too small"; s = GSDF_ERR_INVALID; break; }
+        if (cudaMalloc(&d_keys, sizeof(unsigned long long) * total) != cudaSuccess ||
+            cudaMalloc(&d_verts, sizeof(float) * 9 * total) != cudaSuccess) { h->err = "extract_mesh: cudaMalloc failed"; s = GSDF_ERR_CUDA; break; }
+        s = by_variant(h, [&](auto V) {
+            mesh_kernel<decltype(V)::value, true><<<grid, 256, 0, h->stream>>>(h->view, box, h->geom.vs, d_total + 1, (long long)total,
+                                                                               d_keys, d_verts);
+            return check_launch(h, "mesh_kernel(emit)");
+        });
+        if (s != GSDF_OK) break;
+        std::vector<unsigned long long> keys(total);
+        std::vector<float> verts(9 * total);
+        if (cudaMemcpyAsync(keys.data(), d_keys, sizeof(unsigned long long) * total, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaMemcpyAsync(verts.data(), d_verts, sizeof(float) * 9 * total, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaStreamSynchronize(h->stream) != cudaSuccess) { h->err = "extract_mesh: copy failed"; s = GSDF_ERR_CUDA; break; }
+        // the reference's order: cells in its sweep order (z, y, x), triangles of a cell in case-table order
+        std::vector<uint32_t> order(total);
+        for (size_t i = 0; i < total; ++i) order[i] = (uint32_t)i;
+        std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+        for (size_t i = 0; i < total; ++i) std::memcpy(vertices9 + 9 * i, verts.data() + 9 * (size_t)order[i], sizeof(float) * 9);
+    } while (0);
+    cudaFree(d_box); cudaFree(d_keys); cudaFree(d_verts);
     return s;
 }
 

@@ -6,6 +6,7 @@
 #define GSDF_HOST_MAT_H_
 
 #include <cstddef>
+#include <cmath>
 #include <cstring>
 
 #include "gsdf_b200.h"
@@ -55,11 +56,42 @@ public:
     }
     // a stored pose "tx ty tz qx qy qz qw" with a unit quaternion (no renormalisation)
     static SE3 fromStored(const float* pose7) { SE3 s; std::memcpy(s.p_, pose7, sizeof(s.p_)); return s; }
+    // rotationMatrix() / matrix().topLeftCorner(3,3): Eigen's toRotationMatrix of the STORED unit quaternion (Sophus does
+    // not renormalise here)
     Mat3f rotationMatrix() const {
         Mat3f R;
-        float pn[7];
-        gsdf_pose_matrix(p_, R.m, pn);
+        const float x = p_[3], y = p_[4], z = p_[5], w = p_[6];
+        const float tx = 2.f * x, ty = 2.f * y, tz = 2.f * z;
+        const float twx = tx * w, twy = ty * w, twz = tz * w;
+        const float txx = tx * x, txy = ty * x, txz = tz * x, tyy = ty * y, tyz = tz * y, tzz = tz * z;
+        R.m[0] = 1.f - (tyy + tzz); R.m[1] = txy - twz; R.m[2] = txz + twy;
+        R.m[3] = txy + twz; R.m[4] = 1.f - (txx + tzz); R.m[5] = tyz - twx;
+        R.m[6] = txz - twy; R.m[7] = tyz + twx; R.m[8] = 1.f - (txx + tyy);
         return R;
+    }
+    // Eigen::Quaternion<float> q(R) (Eigen/src/Geometry/Quaternion.h, quaternionbase_assign_impl<Other,3,3>): what
+    // main_scan_3d.cpp:275-276 writes into <results>_poses.txt; out = (x, y, z, w)
+    static void quaternionFromMatrix(const Mat3f& m, float* out) {
+        float t = m(0, 0) + (m(1, 1) + m(2, 2));
+        if (t > 0.f) {
+            t = std::sqrt(t + 1.f);
+            out[3] = 0.5f * t;
+            t = 0.5f / t;
+            out[0] = (m(2, 1) - m(1, 2)) * t;
+            out[1] = (m(0, 2) - m(2, 0)) * t;
+            out[2] = (m(1, 0) - m(0, 1)) * t;
+        } else {
+            int i = 0;
+            if (m(1, 1) > m(0, 0)) i = 1;
+            if (m(2, 2) > m(i, i)) i = 2;
+            const int j = (i + 1) % 3, k = (j + 1) % 3;
+            t = std::sqrt(m(i, i) - m(j, j) - m(k, k) + 1.f);
+            out[i] = 0.5f * t;
+            t = 0.5f / t;
+            out[3] = (m(k, j) - m(j, k)) * t;
+            out[j] = (m(j, i) + m(i, j)) * t;
+            out[k] = (m(k, i) + m(i, k)) * t;
+        }
     }
     Vec3f translation() const { return Vec3f(p_[0], p_[1], p_[2]); }
     static SE3 exp(const Vec6f& xi) {  // se3.hpp:761-782

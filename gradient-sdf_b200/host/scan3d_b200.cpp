@@ -153,9 +153,12 @@ int main(int argc, char* argv[]) {
     double t_track = 0., t_fuse = 0.;
     size_t n_tracked = 0, n_fused = 0;
     auto write_pose = [&](size_t i, const SE3& p) {  // main_scan_3d.cpp:268-280
+        // the reference goes through the 4x4 matrix and back: Eigen::Quaternion<float> q(R) (main_scan_3d.cpp:274-276)
         const float* d = p.data();
+        float q[4];
+        SE3::quaternionFromMatrix(p.rotationMatrix(), q);
         pose_file << (loader ? cur_stamp : (i < stamps.size() ? stamps[i] : std::to_string(i))) << " " << d[0] << " " << d[1] << " " << d[2] << " "
-                  << d[3] << " " << d[4] << " " << d[5] << " " << d[6] << "\n";
+                  << q[0] << " " << q[1] << " " << q[2] << " " << q[3] << "\n";
     };
     int pending = 0;
     std::vector<size_t> pending_idx;

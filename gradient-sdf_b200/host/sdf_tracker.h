@@ -3,7 +3,7 @@
 //   normals/NormalEstimator.h:49-212        cv::NormalEstimator<float>
 //   sdf_tracker/Sdf.h:50-149                Sdf
 //   sdf_tracker/MapGradPixelSdf.h:51-152    MapGradPixelSdf   (+ writers MapGradPixelSdfOmp.cpp:186-303)
-//   sdf_tracker/MapPixelSdf.h:52-155        MapPixelSdf
+//   sdf_tracker/MapPixelSdf.h:52-155        MapPixelSdf       (+ writers MapPixelSdfOmp.cpp:250-351)
 //   sdf_tracker/RigidOptimizer.h:49-112     RigidOptimizer
 //   sdf_tracker/RigidPointOptimizer.h:48-73 RigidPointOptimizer
 // Same argument meaning and error behaviour: update() reports on std::cerr and returns, optimize() returns the
@@ -180,7 +180,25 @@ public:
         return v;
     }
 
-    virtual bool extract_mesh(std::string /*filename*/ = "mesh.ply") { return false; }  // marching cubes: out of scope
+    // extract_mesh, MapGradPixelSdfOmp.cpp:132-183 / MapPixelSdfOmp.cpp:197-248: marching cubes on the device
+    // (gsdf_extract_mesh), ascii PLY exactly as LayeredMarchingCubesNoColor::savePly (mesh/LayeredMarchingCubesNoColor.cpp:
+    // 719-757): three unshared vertices per face, false if there is nothing to write
+    virtual bool extract_mesh(std::string filename = "mesh.ply") {
+        if (!gpu_) return false;
+        int64_t n = 0;
+        if (gsdf_extract_mesh(gpu_, 0, nullptr, &n) != GSDF_OK || n == 0) return false;
+        std::vector<float> v((size_t)9 * n);
+        if (gsdf_extract_mesh(gpu_, n, v.data(), &n) != GSDF_OK) { std::cerr << gsdf_last_error(gpu_) << std::endl; return false; }
+        std::ofstream ply(filename.c_str());
+        if (!ply.is_open()) return false;
+        ply << "ply" << std::endl << "format ascii 1.0" << std::endl << "element vertex " << 3 * n << std::endl
+            << "property float x" << std::endl << "property float y" << std::endl << "property float z" << std::endl
+            << "element face " << (int)n << std::endl << "property list uchar int vertex_indices" << std::endl
+            << "end_header" << std::endl;
+        for (int64_t i = 0; i < 3 * n; ++i) ply << v[3 * i] << " " << v[3 * i + 1] << " " << v[3 * i + 2] << "\n";
+        for (int64_t f = 0; f < n; ++f) ply << "3 " << (int)(3 * f) << " " << (int)(3 * f + 1) << " " << (int)(3 * f + 2) << "\n";
+        return true;
+    }
 
     // extract_pc, MapGradPixelSdfOmp.cpp:186-233: voxels with weight >= 5 whose surface point lies inside the voxel
     virtual bool extract_pc(std::string filename = "cloud.ply") {
@@ -209,7 +227,10 @@ public:
     }
 
     // save_sdf, MapGradPixelSdfOmp.cpp:235-303: <prefix>_grid_info.txt, _sdf_d.txt, _sdf_weight.txt, _sdf_n{0,1,2}.txt
-    virtual bool save_sdf(std::string filename = "sdf.txt") {
+    virtual bool save_sdf(std::string filename = "sdf.txt") { return save_sdf_files(filename, true); }
+
+protected:
+    bool save_sdf_files(const std::string& filename, bool with_normals) {
         HostMap m;
         if (!download(m)) return false;
         int lo[3] = {std::numeric_limits<int>::max(), std::numeric_limits<int>::max(), std::numeric_limits<int>::max()};
@@ -224,8 +245,11 @@ public:
              << "voxel min: " << lo[0] << " " << lo[1] << " " << lo[2] << std::endl
              << "voxel max: " << hi[0] << " " << hi[1] << " " << hi[2] << std::endl;
         std::ofstream fd((filename + "_sdf_d.txt").c_str()), fw((filename + "_sdf_weight.txt").c_str());
-        std::ofstream n0((filename + "_sdf_n0.txt").c_str()), n1((filename + "_sdf_n1.txt").c_str()), n2((filename + "_sdf_n2.txt").c_str());
-        if (!fd.is_open() || !fw.is_open() || !n0.is_open() || !n1.is_open() || !n2.is_open()) {
+        std::ofstream n0, n1, n2;
+        if (with_normals) {
+            n0.open((filename + "_sdf_n0.txt").c_str()); n1.open((filename + "_sdf_n1.txt").c_str()); n2.open((filename + "_sdf_n2.txt").c_str());
+        }
+        if (!fd.is_open() || !fw.is_open() || (with_normals && (!n0.is_open() || !n1.is_open() || !n2.is_open()))) {
             std::cerr << "couldn't save sdf or sdf weight file!" << std::endl;
             return false;
         }
@@ -233,9 +257,11 @@ public:
             const int lin = dim[0] * dim[1] * (m.keys[3 * i + 2] - lo[2]) + dim[0] * (m.keys[3 * i + 1] - lo[1]) + m.keys[3 * i] - lo[0];
             fd << lin << " " << m.dist[i] << "\n";
             fw << lin << " " << m.weight[i] << "\n";
-            n0 << lin << " " << m.grad[3 * i] << "\n";
-            n1 << lin << " " << m.grad[3 * i + 1] << "\n";
-            n2 << lin << " " << m.grad[3 * i + 2] << "\n";
+            if (with_normals) {
+                n0 << lin << " " << m.grad[3 * i] << "\n";
+                n1 << lin << " " << m.grad[3 * i + 1] << "\n";
+                n2 << lin << " " << m.grad[3 * i + 2] << "\n";
+            }
         }
         return true;
     }
@@ -253,6 +279,27 @@ public:
     MapPixelSdf() : Sdf(GSDF_BASE_SDF, 0.02f, 0.05f) {}
     explicit MapPixelSdf(float voxel_size) : Sdf(GSDF_BASE_SDF, voxel_size, 0.05f) {}
     MapPixelSdf(float voxel_size, float T) : Sdf(GSDF_BASE_SDF, voxel_size, T) {}
+
+    // extract_pc, MapPixelSdfOmp.cpp:250-288: voxel centres (xyz only, 7-line header) of the voxels with weight >= 5 and
+    // |dist| < sqrt(3) * voxel_size (the comparison is in double there: std::sqrt(3) * voxel_size_)
+    bool extract_pc(std::string filename = "cloud.ply") override {
+        HostMap m;
+        if (!download(m)) return false;
+        std::vector<int64_t> keep;
+        for (int64_t i = 0; i < m.n; ++i)
+            if (!(m.weight[i] < 5) && (double)std::fabs(m.dist[i]) < std::sqrt(3.0) * (double)voxel_size_) keep.push_back(i);
+        std::ofstream ply(filename.c_str());
+        if (!ply.is_open()) return false;
+        ply << "ply\nformat ascii 1.0\nelement vertex " << keep.size()
+            << "\nproperty float x\nproperty float y\nproperty float z\nend_header\n";
+        for (int64_t i : keep)  // vox2float, MapPixelSdf.h:74-76
+            ply << voxel_size_ * (float)m.keys[3 * i] << " " << voxel_size_ * (float)m.keys[3 * i + 1] << " "
+                << voxel_size_ * (float)m.keys[3 * i + 2] << "\n";
+        return true;
+    }
+
+    // save_sdf, MapPixelSdfOmp.cpp:290-351: <prefix>_grid_info.txt, _sdf_d.txt, _sdf_weight.txt — and no normal files
+    bool save_sdf(std::string filename = "sdf.txt") override { return save_sdf_files(filename, false); }
 };
 
 class RigidOptimizer {

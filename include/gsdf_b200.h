@@ -135,6 +135,16 @@ gsdf_status gsdf_voxel_count(gsdf_handle h, int64_t* n_voxels, int64_t* n_blocks
 gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* dist, float* weight, float* grad,
                           int64_t* n_out);
 
+/* Sdf::extract_mesh (sdf_tracker/MapGradPixelSdfOmp.cpp:132-183, MapPixelSdfOmp.cpp:197-248 ->
+ * mesh/LayeredMarchingCubesNoColor.cpp:354-719): marching cubes at iso value 0 over the voxels with weight > 0, with the
+ * reference's rules (a cell is meshed only if all 8 corners have weight != 0; its corner / edge numbering, case table and
+ * interpolate(); degenerate triangles dropped; vertices not shared between triangles).  vertices9 receives 9 floats per
+ * triangle (three xyz points, world coordinates) in the reference's order — cells swept z, then y, then x over the map's
+ * bounding box, triangles of a cell in case-table order — so that vertex i of the reference's PLY is point i here and face
+ * f is (3f, 3f+1, 3f+2) (savePly, LayeredMarchingCubesNoColor.cpp:719-757).  vertices9 == NULL (or max_triangles == 0):
+ * only counts.  *n_triangles = triangles in the map; GSDF_ERR_INVALID if max_triangles is smaller.  Single-GPU maps. */
+gsdf_status gsdf_extract_mesh(gsdf_handle h, int64_t max_triangles, float* vertices9, int64_t* n_triangles);
+
 /* Checkpoint / resume, no counterpart in the reference (which can only dump the final map as text, save_sdf): sets the
  * listed voxels to the given state — the arrays are what gsdf_download returns (grad may be NULL for base-sdf); voxels
  * with weight <= 0 are skipped.  Into an empty map (gsdf_reset) this restores a downloaded one: same key set, same

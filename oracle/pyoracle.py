@@ -227,6 +227,9 @@ class RefScan(_Base):
         L.gsdf_ref_pose_matrix.argtypes = [_f32p, _f32p, _f32p]
         L.gsdf_ref_apply_increment.argtypes = [_f32p, _f32p, _f32p]
         L.gsdf_ref_llt_solve.argtypes = [_f32p, _f32p, _f32p]
+        L.gsdf_ref_write.restype = C.c_int
+        L.gsdf_ref_write.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
+        L.gsdf_ref_upload.argtypes = [C.c_void_p, C.c_longlong, _i32p, _f32p, _f32p, _f32p]
         self.variant, self.w, self.h = variant, w, h
         self.K = _f32(K).reshape(9)
         self.handle = L.gsdf_ref_create(variant, voxel_size, trunc_factor, w, h, _fp(self.K), normal_win,
@@ -242,6 +245,16 @@ class RefScan(_Base):
             self.close()
         except Exception:
             pass
+
+    def write(self, which, filename):
+        """The reference's own writers on the current map: which = 'mesh' | 'pc' | 'sdf' (extract_mesh, extract_pc,
+        save_sdf); returns their bool."""
+        return bool(self.L.gsdf_ref_write(self.handle, {"mesh": 0, "pc": 1, "sdf": 2}[which], str(filename).encode()))
+
+    def upload(self, keys, dist, weight, grad):
+        """Replace the reference's hash by the given voxels (arrays as download() returns them)."""
+        k = np.ascontiguousarray(keys, np.int32); d = _f32(dist); w = _f32(weight); g = _f32(grad)
+        self.L.gsdf_ref_upload(self.handle, len(d), k.ctypes.data_as(_i32p), _fp(d), _fp(w), _fp(g))
 
     def normal_cache(self):
         out = np.zeros((11, self.h, self.w), np.float32)

@@ -260,4 +260,29 @@ void gsdf_ref_llt_solve(const float* H36, const float* g6, float* xi6) {
     for (int i = 0; i < 6; ++i) xi6[i] = xi[i];
 }
 
+// The reference's own output writers (MapGradPixelSdfOmp.cpp:132-303, MapPixelSdfOmp.cpp:197-351; marching cubes:
+// mesh/LayeredMarchingCubesNoColor.cpp:354-757) on the map built so far: which = 0 extract_mesh, 1 extract_pc, 2 save_sdf.
+int gsdf_ref_write(void* h, int which, const char* filename) {
+    RefScan* s = (RefScan*)h;
+    Quiet q(s->quiet);
+    const std::string f(filename);
+    if (which == 0) return s->sdf->extract_mesh(f) ? 1 : 0;
+    if (which == 1) return s->sdf->extract_pc(f) ? 1 : 0;
+    return s->sdf->save_sdf(f) ? 1 : 0;
+}
+
+// Upload a map (what gsdf_ref_download returns) into the reference's hash, so that its writers can be run on ANY map
+// — e.g. the one the GPU built — and file-level differences are then differences of the writers alone.
+void gsdf_ref_upload(void* h, long long n, const int32_t* keys, const float* dist, const float* weight, const float* grad) {
+    RefScan* s = (RefScan*)h;
+    VoxelMap& m = const_cast<VoxelMap&>(voxel_map(s));
+    m.clear();
+    for (long long i = 0; i < n; ++i) {
+        SdfVoxel v;
+        v.dist = dist[i]; v.weight = weight[i];
+        v.grad = Vec3f(grad[3 * i], grad[3 * i + 1], grad[3 * i + 2]);
+        m[Vec3i(keys[3 * i], keys[3 * i + 1], keys[3 * i + 2])] = v;
+    }
+}
+
 }  // extern "C"
