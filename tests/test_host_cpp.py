@@ -78,7 +78,12 @@ def test_scan3d_driver_matches_python_binding(pkg, synth, tmp_path, stype):
         assert d[:, 0].max() < dims[0] * dims[1] * dims[2]
         ply = Path(str(out) + "gradient_sdf_cloud_final.ply").read_text().splitlines()
         nvert = int(ply[2].split()[-1])
-        assert ply[0] == "ply" and (nvert > 100 if stype == "grad-sdf" else nvert >= 0) and len(ply) == 10 + nvert
+        # grad-sdf: xyz + normal (10 header lines, MapGradPixelSdfOmp.cpp:205-219); base-sdf: xyz only (7, MapPixelSdfOmp.cpp:272-281)
+        assert ply[0] == "ply" and (nvert > 100 if stype == "grad-sdf" else nvert >= 0)
+        assert len(ply) == (10 if stype == "grad-sdf" else 7) + nvert
+        assert Path(str(out) + "gradient_sdf_sdf_n0.txt").exists() == (stype == "grad-sdf")
+        mesh = Path(str(out) + "gradient_sdf_mesh_final.ply").read_text().splitlines()
+        assert mesh[0] == "ply" and int(mesh[2].split()[-1]) == 3 * int(mesh[6].split()[-1]) > 0
 
 
 @pytest.mark.gpu

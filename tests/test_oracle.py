@@ -3,7 +3,7 @@ own OMP build, and — where oracle/_ref exists — against that build directly,
 import numpy as np
 import pytest
 
-from conftest import load_golden
+from conftest import ROOT, load_golden
 
 GOLDENS = ["grad_160x120_2cm_t5", "base_160x120_2cm_t5", "grad_160x120_1cm_t10"]
 
@@ -130,3 +130,29 @@ def test_synth_generator_is_seeded(synth):
     b = synth.make_sequence(50, 64, 48)[0][:2]
     assert np.array_equal(a, b)
     assert (a > 0).mean() > 0.05
+
+
+def test_marching_cubes_case_table_equals_the_reference_builds(po):
+    """The nibble-packed case table in csrc/gsdf_mesh.cuh, row by row, against the triTable inside the reference build
+    (mesh/LayeredMarchingCubesNoColor.cpp:96-352), and the rule that replaces its edgeTable (:67-94)."""
+    import ctypes as C
+    import re
+    if not po.have_ref():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    text = (ROOT / "gradient-sdf_b200" / "csrc" / "gsdf_mesh.cuh").read_text()
+    body = text[text.index("kTriTable[256] = {"):]
+    body = body[:body.index("};")]
+    rows = [int(x, 16) for x in re.findall(r"0x([0-9a-f]{16})ull", body)]
+    assert len(rows) == 256
+    L = C.CDLL(str(po.REF_SO))
+    tri = (C.c_int * (256 * 16)).in_dll(L, "_ZN27LayeredMarchingCubesNoColor8triTableE")
+    edge = (C.c_int * 256).in_dll(L, "_ZN27LayeredMarchingCubesNoColor9edgeTableE")
+    corners = [(0, 1), (1, 2), (2, 3), (3, 0), (4, 5), (5, 6), (6, 7), (7, 4), (0, 4), (1, 5), (2, 6), (3, 7)]
+    for c in range(256):
+        ref = [tri[16 * c + i] for i in range(16)]
+        n = ref.index(-1)
+        assert rows[c] >> 60 == n and n % 3 == 0
+        assert [(rows[c] >> (4 * i)) & 0xF for i in range(n)] == ref[:n]
+        mask = sum(1 << e for e, (a, b) in enumerate(corners) if ((c >> a) & 1) != ((c >> b) & 1))
+        assert mask == edge[c]
+        assert all(mask >> e & 1 for e in ref[:n])  # a case's triangles only name edges that cross the surface
