@@ -146,3 +146,94 @@ def make_sequence(n_frames: int, width: int = 640, height: int = 480, n_spheres:
             z = add_kinect_noise(z, rng)
         frames[k] = quantise(z, unit)
     return frames, poses.astype(np.float32), K.astype(np.float32), spheres
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# Room-scale scene (BASELINE.json configs[3], "TUM fr1-style"): the camera moves inside a 6 x 6 x 3 m box room that holds
+# ~20 spheres (furniture stand-ins), on a smooth hand-held-like path (<= 3 cm and <= 1.5 degrees between frames at 2000
+# frames per lap).  Rendering works on numpy arrays or on torch tensors (pass xp=torch and a device) so that thousands of
+# frames can be produced on the GPU for the bench; the arithmetic is the same analytic ray casting as render_depth.
+ROOM_HALF = np.array([3.0, 3.0, 1.5])
+ROOM_SEED = 4242
+
+
+def room_scene(n_spheres: int = 20, seed: int = ROOM_SEED) -> np.ndarray:
+    """Spheres [cx cy cz r] standing in the outer part of the room (between 1.6 m and 2.6 m from the vertical axis), not
+    intersecting each other."""
+    rng = np.random.default_rng(seed)
+    out = []
+    while len(out) < n_spheres:
+        ang, rad = rng.uniform(0, 2 * np.pi), rng.uniform(1.6, 2.6)
+        r = rng.uniform(0.2, 0.5)
+        c = np.array([rad * np.cos(ang), rad * np.sin(ang), rng.uniform(-1.5 + r * 0.5, 0.9)])
+        if all(np.linalg.norm(c - s[:3]) > s[3] + r + 0.05 for s in out):
+            out.append(np.array([c[0], c[1], c[2], r]))
+    return np.stack(out)
+
+
+def room_trajectory(n_frames: int, laps: float = 1.0, frames_per_lap: int = 2000) -> np.ndarray:
+    """Camera-to-world poses: the camera walks a 0.6 m circle about the room's axis looking outward, bobbing +-0.15 m and
+    pitching +-12 degrees: 0.18 degrees and ~2 mm per frame at 2000 frames per lap."""
+    poses = np.zeros((n_frames, 7))
+    for k in range(n_frames):
+        th = 2 * np.pi * k / frames_per_lap * laps
+        pitch = np.deg2rad(12.0) * np.sin(5 * th)
+        c = np.array([0.6 * np.cos(th), 0.6 * np.sin(th), 0.15 * np.sin(3 * th)])
+        fwd = np.array([np.cos(th) * np.cos(pitch), np.sin(th) * np.cos(pitch), np.sin(pitch)])
+        poses[k, :3] = c
+        poses[k, 3:] = rot_to_quat(_look_at(c, c + fwd))
+    return poses
+
+
+def render_room(spheres: np.ndarray, pose7: np.ndarray, K: np.ndarray = K_KINECT, width: int = 640, height: int = 480,
+                xp=np, device=None):
+    """Noise-free z-depth of the box room + spheres seen from pose7 (float64; every pixel hits a wall)."""
+    kw = {} if xp is np else {"device": device, "dtype": xp.float64}
+    if xp is np:
+        u, v = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+    else:
+        u, v = xp.meshgrid(xp.arange(width, **kw), xp.arange(height, **kw), indexing="xy")
+    cu = (u - float(K[0, 2])) / float(K[0, 0])
+    cv = (v - float(K[1, 2])) / float(K[1, 1])
+    R = quat_to_rot(np.asarray(pose7[3:], np.float64))
+    o = np.asarray(pose7[:3], np.float64)
+    inf = float("inf")
+    depth = None
+    for axis in range(3):
+        # world-space ray direction per unit z-depth: R @ [cu, cv, 1]
+        dirn = R[axis, 0] * cu + R[axis, 1] * cv + R[axis, 2]
+        for sign in (-1.0, 1.0):
+            z = (sign * ROOM_HALF[axis] - o[axis]) / dirn
+            z = xp.where(z > 0, z, xp.full_like(z, inf)) if xp is not np else np.where(z > 0, z, inf)
+            depth = z if depth is None else (xp.minimum(depth, z))
+    A = cu * cu + cv * cv + 1.0
+    c = (spheres[:, :3] - o) @ R
+    for s in range(spheres.shape[0]):
+        B = -2.0 * (cu * c[s, 0] + cv * c[s, 1] + c[s, 2])
+        C = float(c[s] @ c[s] - spheres[s, 3] ** 2)
+        disc = B * B - 4.0 * A * C
+        if xp is np:
+            z = np.where(disc >= 0, 0.5 * (-B - np.sqrt(np.maximum(disc, 0))) / A, inf)
+            z = np.where(z > 0, z, inf)
+        else:
+            z = xp.where(disc >= 0, 0.5 * (-B - xp.sqrt(disc.clamp(min=0))) / A, xp.full_like(A, inf))
+            z = xp.where(z > 0, z, xp.full_like(z, inf))
+        depth = xp.minimum(depth, z)
+    return depth
+
+
+def make_room_sequence(n_frames: int, width: int = 640, height: int = 480, noise: bool = True, laps: float = 1.0,
+                       frames_per_lap: int = 2000, start: int = 0, noise_seed: int = NOISE_SEED, unit: float = 1.0 / 1000.0):
+    """(depth [n,h,w] float32, poses [n,7] float32, K float32, spheres) of the room scene, frames start .. start+n-1 of the
+    lap (numpy; for a few frames — the bench renders its frames with render_room on the GPU)."""
+    K = scaled_intrinsics(width, height)
+    spheres = room_scene()
+    poses = room_trajectory(start + n_frames, laps, frames_per_lap)[start:]
+    rng = np.random.default_rng(noise_seed)
+    frames = np.zeros((n_frames, height, width), dtype=np.float32)
+    for k in range(n_frames):
+        z = render_room(spheres, poses[k], K, width, height)
+        if noise:
+            z = add_kinect_noise(z, rng)
+        frames[k] = quantise(z, unit)
+    return frames, poses.astype(np.float32), K.astype(np.float32), spheres

@@ -23,7 +23,7 @@ torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 W, H = 320, 240
 frames, poses, K, _ = synth.make_sequence(800, W, H, noise=False)
-frames = frames[:8]
+frames, poses = frames[:8], poses[:8]
 dev_frames = torch.from_numpy(frames).cuda()
 nest = pkg.NormalEstimator(W, H, K, 11)
 vs, T = np.float32(0.01), np.float32(0.05)
@@ -103,10 +103,31 @@ def check_variant(cls, tag):
     nref = single.voxel_count()[0]
     assert abs(int(n) - nref) <= 1e-3 * nref, (tag, int(n), nref)
     dist.barrier()
-    return int(n), nref
+    # pose-injected fusion: the union of the ranks' key sets must EQUAL the single-GPU key set and the CPU oracle's, key by
+    # key (free-running maps differ at the truncation boundary because the poses differ in the last bits)
+    single.reset()
+    sharded.reset()
+    po = gsdf_loader.load_oracle()
+    orc = po.Oracle(cls.variant, vs, np.float32(5), W, H, K)
+    for i in range(4):
+        single.update(frames[i], poses[i])
+        sharded.update(frames[i], poses[i])
+        if rank == 0:
+            orc.update(frames[i], poses[i])
+    mine = sharded.download()[0]
+    parts = [None] * world
+    dist.all_gather_object(parts, mine)
+    union = np.concatenate(parts)
+    union = union[np.lexsort((union[:, 2], union[:, 1], union[:, 0]))]
+    want = single.download()[0]
+    assert union.shape == want.shape and np.array_equal(union, want), (tag, "key set of the shards' union differs from one GPU's")
+    if rank == 0:
+        assert np.array_equal(union, orc.download()[0]), (tag, "key set of the shards' union differs from the oracle's")
+    dist.barrier()
+    return int(n), nref, len(union)
 
 
 res = {tag: check_variant(cls, tag) for tag, cls in (("grad", pkg.MapGradPixelSdf), ("base", pkg.MapPixelSdf))}
 if rank == 0:
-    print("MULTIGPU OK", world, "ranks; voxels (sharded union, single GPU):", res)
+    print("MULTIGPU OK", world, "ranks; voxels (free-running sharded union, free-running single GPU, pose-injected union == single == oracle):", res)
 dist.destroy_process_group()

@@ -90,6 +90,47 @@ def test_golden_kernel_level(pkg, po, name):
     assert dp[:3].max() < 1e-4 and dp[3:].max() < 1e-4, dp
 
 
+@pytest.mark.parametrize("variant,vs,trunc", [(0, 0.01, 5), (1, 0.01, 5), (0, 0.02, 10)])
+def test_kernel_level_against_the_reference_build_live(pkg, po, synth, variant, vs, trunc):
+    """The same checks as against the golden dumps, but with the reference's own OMP translation units (oracle/_ref,
+    built by build() where /root/reference exists and shipped to the GPU box) running LIVE beside the GPU on fresh
+    seeded inputs: cached planes and normals bit-identical, key set bit-exact after pose-injected fusion, values in
+    tolerance, point queries, and one free optimize() from the same start."""
+    if not po.have_ref():
+        pytest.skip("oracle/_ref not built (needs /root/reference where build() runs)")
+    W, H = 320, 240
+    frames, poses, K, _ = synth.make_sequence(150, W, H, scene_seed=777, noise_seed=31)
+    vs, trunc = np.float32(vs), np.float32(trunc)
+    nest = pkg.NormalEstimator(W, H, K, 11)
+    cls = pkg.MapGradPixelSdf if variant == 0 else pkg.MapPixelSdf
+    sdf = cls(vs, trunc * vs, nest, log2_capacity=16)
+    ref = po.RefScan(variant, vs, trunc, W, H, K)
+    assert np.array_equal(bits(sdf.normal_cache()), bits(ref.normal_cache()))
+    sdf.upload_frame(frames[0])
+    n0, nr = sdf.compute_normals(), ref.normals(frames[0])
+    assert ((bits(n0) == bits(nr)) | (np.isnan(n0) & np.isnan(nr))).all()
+    for i in range(4):
+        sdf.update(frames[i], poses[i])
+        ref.update(frames[i], poses[i])
+    got, want = sdf.download(), ref.download()
+    check_map(got, want, float(trunc * vs), variant)
+    rng = np.random.default_rng(5)
+    pts = (got[0][rng.integers(0, len(got[0]), 4000)].astype(np.float32) + rng.uniform(-0.5, 0.5, (4000, 3)).astype(np.float32)) * vs
+    phi, grad, w = sdf.query(pts)
+    phi_r, grad_r, w_r = ref.query(pts)
+    assert np.array_equal(w > 0, w_r > 0) and np.allclose(w, w_r, rtol=1e-5)
+    assert np.abs(phi - phi_r).max() <= 1e-5
+    assert np.abs(grad - grad_r).max() <= (1e-4 if variant == 0 else 4e-5 / float(vs))
+    opt = pkg.RigidPointOptimizer(sdf)
+    opt.set_pose(poses[3])
+    ref.set_pose(poses[3])
+    conv = opt.optimize(frames[4])
+    conv_r, it_r = ref.optimize(frames[4])
+    dp = np.abs(opt.pose() - ref.get_pose())
+    assert dp[:3].max() < 2e-3 and dp[3:].max() < 1e-3, dp
+    sdf.close()
+
+
 @pytest.mark.parametrize("name", GOLDENS[:2])
 def test_golden_free_running(pkg, po, name):
     """main_scan_3d.cpp:208-266: frame 0 fused at identity, then track each frame, fuse if converged."""
@@ -128,14 +169,31 @@ def test_fusion_vs_oracle_seeded(pkg, po, synth, variant, vs, trunc, W, H):
     assert nv == orc.voxel_count() and nb == len({tuple(x) for x in (orc.download()[0] >> 3)})
 
 
-@pytest.mark.parametrize("variant,vs,trunc", [(1, 0.01, 5), (0, 0.02, 10)])
-def test_fusion_and_tracker_sums_vs_oracle_at_baseline_sizes(pkg, po, synth, variant, vs, trunc):
-    """BASELINE.json configs C2 (base-sdf, 1 cm, trunc 5) and C1 (grad-sdf, 2 cm, trunc 10) at the full 640x480: the
-    oracle still finishes in seconds for three frames, so the key set is compared bit for bit at the bench's size too,
-    and the 29 tracker sums of the next frame against the oracle's."""
-    W, H = 640, 480
-    frames, poses, K, _ = synth.make_sequence(100, W, H)
-    sdf, orc = make_pair(pkg, po, variant, vs, trunc, W, H, K, log2cap=17)
+def baseline_scene(synth, name):
+    """The synthetic inputs of BASELINE.json's configurations at their full image sizes."""
+    if name in ("C1", "C2"):       # 5-sphere orbit, Kinect noise
+        return synth.make_sequence(100, 640, 480)
+    if name == "C3":               # object-scale turntable: 6 spheres within ~0.3 m, camera at 0.7 m, 500 frames per turn
+        return synth.make_sequence(5, 640, 480, n_spheres=6, extent=0.28, rmin=0.035, rmax=0.09, radius=0.7,
+                                   turn=2 * np.pi * 5 / 500)
+    if name == "C4":               # room scale: 6 x 6 x 3 m box room with 20 spheres, hand-held-like path, every pixel valid
+        return synth.make_room_sequence(4, 640, 480)
+    if name == "C5-1280x720":      # sweep corner: largest resolution, smallest voxels
+        return synth.make_sequence(5, 1280, 720, turn=2 * np.pi * 5 / 100)  # the first 5 frames of a 100-frame orbit
+    raise KeyError(name)
+
+
+@pytest.mark.parametrize("config,variant,vs,trunc,cap", [("C2", 1, 0.01, 5, 17), ("C1", 0, 0.02, 10, 17), ("C3", 0, 0.005, 5, 18),
+                                                         ("C4", 0, 0.01, 5, 18), ("C5-1280x720", 0, 0.004, 5, 19),
+                                                         ("C5-1280x720", 1, 0.004, 5, 19)])
+def test_fusion_and_tracker_sums_vs_oracle_at_baseline_sizes(pkg, po, synth, config, variant, vs, trunc, cap):
+    """Every configuration BASELINE.json names, at its full image size: C2 (base-sdf, 1 cm), C1 (grad-sdf, 2 cm, trunc 10),
+    C3 (object-scale turntable, 5 mm), C4 (room scale, 1 cm, all 307 200 pixels valid), and the 1280x720 / 4 mm corner of
+    the C5 sweep.  The oracle still finishes in seconds for three frames, so the key set is compared bit for bit at these
+    sizes too, and the 29 tracker sums of the next frame against the oracle's."""
+    frames, poses, K, _ = baseline_scene(synth, config)
+    H, W = frames.shape[1:]
+    sdf, orc = make_pair(pkg, po, variant, vs, trunc, W, H, K, log2cap=cap)
     T = float(np.float32(trunc) * np.float32(vs))
     for i in range(3):
         pts, upd, _ = sdf.update(frames[i], poses[i])
