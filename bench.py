@@ -410,7 +410,7 @@ def run_ours(args):
             st["track_valid"] += r.track_valid
         st["launches"] = sdf.launch_count - launches0
         if flog:
-            log = np.zeros((256, 4), np.uint64)
+            log = np.zeros((256, 8), np.uint64)
             sdf._check(sdf.L.gsdf_debug_frame_log(sdf.h, log.ctypes.data))
             t = log[(log[:, 3] > 0) & (log[:, 1] > 0)].astype(np.int64)
             t = t[np.argsort(t[:, 2])][5:-2]

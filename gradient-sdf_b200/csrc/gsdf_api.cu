@@ -141,7 +141,8 @@ struct gsdf_map {
     bool serial = false;        // GSDF_SERIAL=1: frame-only kernels on the main stream instead of the side stream
     int batch_frames = kMaxBatch;  // GSDF_BATCH_FRAMES=1..4: frames per tracker launch in gsdf_scan_run
     unsigned long long* d_dbg = nullptr;  // tracker phase stamps (gsdf_debug_track_timers)
-    unsigned long long* d_flog = nullptr; // [kFlogFrames][4] kernel spans per pipeline frame (gsdf_debug_frame_log)
+    int64_t dbg_only_seq = -1;            // >= 0: only the launch that holds this frame writes stamps (GSDF_DBG_SKIP)
+    unsigned long long* d_flog = nullptr; // [kFlogFrames][8] kernel spans per pipeline frame (gsdf_debug_frame_log)
     // NVLink peer exchange of the sharded tracker (gsdf_p2p_export / gsdf_p2p_connect)
     void* d_p2p = nullptr;            // [4][world][32] 64-bit {tag, float} words, then one error word
     PeerExchange px{};
@@ -313,7 +314,7 @@ gsdf_status launch_normals_compact(gsdf_map* h, const float* depth, int buf, cud
     normals_compact_kernel<<<grid, block, normals_smem(h, NC_H), stream>>>(
         depth, h->d_planes + 2 * n, h->d_planes + 3 * n, h->d_planes + 4 * n, h->d_planes + 5 * n, nrm, nrm + n,
         nrm + 2 * n, w, ht, r, h->geom.z_min, h->geom.z_max, h->d_compact_flags2, h->compact_epoch, h->d_vlist[buf],
-        h->d_nvalid + buf, h->d_flog ? h->d_flog + 4 * ((seq < 0 ? h->seq_submitted : seq) % kFlogFrames) : nullptr);
+        h->d_nvalid + buf, h->d_flog ? h->d_flog + 8 * ((seq < 0 ? h->seq_submitted : seq) % kFlogFrames) : nullptr);
     return check_launch(h, "normals_compact_kernel");
 }
 
@@ -385,13 +386,14 @@ gsdf_status launch_track_batch(gsdf_map* h, const TrackParams& tp, const int* bu
             const float* planes = h->d_planes;
             Counters* ctr = h->d_ctr;
             FrameBatch fb = {};
-            fb.n = nb; fb.fuse_mode = fuse_mode; fb.dbg = h->d_dbg;
+            fb.n = nb; fb.fuse_mode = fuse_mode;
+            fb.dbg = (h->dbg_only_seq < 0 || (seq0 <= h->dbg_only_seq && h->dbg_only_seq < seq0 + nb)) ? h->d_dbg : nullptr;
             for (int i = 0; i < nb; ++i) {
                 fb.vlist[i] = h->d_vlist[bufs[i]];
                 fb.n_valid[i] = h->d_nvalid + bufs[i];
                 fb.normals[i] = fuse_mode ? h->d_normals[bufs[i]] : nullptr;
                 fb.snap[i] = snaps[i];
-                fb.flog[i] = (h->d_flog && snaps[i]) ? h->d_flog + 4 * ((seq0 + i) % kFlogFrames) : nullptr;
+                fb.flog[i] = (h->d_flog && snaps[i]) ? h->d_flog + 8 * ((seq0 + i) % kFlogFrames) : nullptr;
             }
             PeerExchange px = h->px;  // world <= 1 unless gsdf_p2p_connect succeeded
             if (px.world > 1 && tp.max_iters > 63) { h->err = "sharded tracking over NVLink supports at most 63 iterations"; return GSDF_ERR_INVALID; }
@@ -1386,6 +1388,10 @@ gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int3
     if (!h->d_dbg) {
         CUDA_TRY(h, cudaMalloc(&h->d_dbg, bytes));
         CUDA_TRY(h, cudaMemset(h->d_dbg, 0, bytes));
+        // GSDF_DBG_SKIP=n: stamps only from the launch that holds the n-th frame submitted from now on (a launch in the
+        // middle of a long gsdf_scan_run, with the frame-only kernels of later frames running beside it)
+        const char* e = std::getenv("GSDF_DBG_SKIP");
+        h->dbg_only_seq = e ? h->seq_submitted + std::max(0, std::atoi(e)) : -1;
     }
     if (out) {
         CUDA_TRY(h, cudaStreamSynchronize(h->stream));
@@ -1396,14 +1402,14 @@ gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int3
     return GSDF_OK;
 }
 
-gsdf_status gsdf_debug_frame_log(gsdf_handle h, unsigned long long* out /* null: arm; else kFlogFrames * 4 words */) {
+gsdf_status gsdf_debug_frame_log(gsdf_handle h, unsigned long long* out /* null: arm; else kFlogFrames * 8 words */) {
     if (!h) return GSDF_ERR_INVALID;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
-    const size_t bytes = sizeof(unsigned long long) * 4 * kFlogFrames;
+    const size_t bytes = sizeof(unsigned long long) * 8 * kFlogFrames;
     if (!out) {
         if (!h->d_flog) CUDA_TRY(h, cudaMalloc(&h->d_flog, bytes));
-        std::vector<unsigned long long> init(4 * kFlogFrames);
-        for (int i = 0; i < kFlogFrames; ++i) { init[4 * i] = init[4 * i + 2] = ~0ull; init[4 * i + 1] = init[4 * i + 3] = 0; }
+        std::vector<unsigned long long> init(8 * kFlogFrames, 0ull);
+        for (int i = 0; i < kFlogFrames; ++i) init[8 * i] = init[8 * i + 2] = ~0ull;
         CUDA_TRY(h, cudaDeviceSynchronize());
         CUDA_TRY(h, cudaMemcpy(h->d_flog, init.data(), bytes, cudaMemcpyHostToDevice));
         return GSDF_OK;

@@ -154,6 +154,19 @@ __device__ __forceinline__ int map_find_or_insert(const MapView& m, unsigned lon
     return -1;
 }
 
+// Fire-and-forget vector reductions into the voxel accumulators, spelled as PTX `red` so that the SASS is REDG (no return
+// path) whatever the surrounding code looks like; atomicAdd(float4*) with an unused result came out as ATOMG ... PT, RZ
+// inside the fusion loop.
+__device__ __forceinline__ void red_add_f4(float4* p, float a, float b, float c, float d) {
+    asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void red_add_f2(float2* p, float a, float b) {
+    asm volatile("red.relaxed.gpu.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void red_add_f1(float* p, float a) {
+    asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" ::"l"(p), "f"(a) : "memory");
+}
+
 // Eigen fixed-size 3-term reduction: a0*b0 + (a1*b1 + a2*b2), each product and sum rounded, no FMA.
 __device__ __forceinline__ float dot3_rn(float a0, float a1, float a2, float b0, float b1, float b2) {
     return __fadd_rn(__fmul_rn(a0, b0), __fadd_rn(__fmul_rn(a1, b1), __fmul_rn(a2, b2)));

@@ -537,10 +537,10 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
             if (fdbg) d_reds += __popc(__ballot_sync(0xffffffffu, leader));
             if (leader) {
                 if (VARIANT == 0) {
-                    atomicAdd(m.acc4 + vaddr, make_float4(v[0], v[1], v[2], v[3]));    // :115-117
-                    atomicAdd(m.accW + vaddr, v[4]);
+                    red_add_f4(m.acc4 + vaddr, v[0], v[1], v[2], v[3]);                // :115-117
+                    red_add_f1(m.accW + vaddr, v[4]);
                 } else {
-                    atomicAdd(m.acc2 + vaddr, make_float2(v[0], v[1]));                // MapPixelSdfOmp.cpp:183-185
+                    red_add_f2(m.acc2 + vaddr, v[0], v[1]);                            // MapPixelSdfOmp.cpp:183-185
                 }
             }
             if (dbg && d_first) { dbg[4] = global_ns(); d_first = false; }
@@ -610,29 +610,36 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
 // bit-identical to the reference build.
 //   * tiles whose interior holds no z-valid pixel are skipped (fusion never reads normals of invalid pixels);
 //   * the z_inv products are widened to double once, when staged, instead of once per window tap.
-template <int TH /* tile height: 32 x TH threads */>
+//   * RC > 0 fixes the window radius at compile time (RC = 5: the 11 x 11 window main_scan_3d.cpp:183 always uses): the tap
+//     loops unroll, a thread's three planes run as three independent chains and all loads of a chain are in flight together
+//     (with a runtime radius every tap cost a load, an add and three loop instructions: 2.4x the instructions);
+//   * pixels outside the depth range get no normal (the pipeline's fusion reads normals of list entries only), and tiles
+//     that do not touch the image border skip the reflection arithmetic.
+template <int TH /* tile height: 32 x TH threads */, int RC /* window radius, 0 = runtime */>
 __device__ __forceinline__ void normals_tile(const float* __restrict__ depth, const float* __restrict__ x0n,
                                              const float* __restrict__ y0n, const float* __restrict__ nsi,
                                              const float* __restrict__ Q, float* __restrict__ nx,
-                                             float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r,
+                                             float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r_arg,
                                              float z_min, float z_max, int tile_x, int tile_y, int tix, int tiy,
                                              unsigned char* smem_raw) {
+    const int r = RC ? RC : r_arg;
     const int tw = NT_W + 2 * r, th = TH + 2 * r;
     double* a = reinterpret_cast<double*>(smem_raw);   // [3][th][tw] products, widened
     double* rs = a + 3 * tw * th;                      // [3][th][NT_W] row sums
-    const int tid = tiy * NT_W + tix;
     const int x_base = tile_x * NT_W, y_base = tile_y * TH;
     const int x = x_base + tix, y = y_base + tiy;
     const size_t n = (size_t)w * h;
     const bool inside = x < w && y < h;
     const float zc = inside ? depth[(size_t)y * w + x] : 0.f;
-    if (!__syncthreads_or(inside && z_valid(zc, z_min, z_max))) return;
+    const bool wanted = inside && z_valid(zc, z_min, z_max);
+    if (!__syncthreads_or(wanted)) return;
 
+    const bool interior = x_base >= r && y_base >= r && x_base + NT_W + r <= w && y_base + TH + r <= h;
     for (int ly = tiy; ly < th; ly += TH) {
-        const int gy = reflect101(min(y_base + ly - r, h - 1 + r), h);
+        const int gy = interior ? y_base + ly - r : reflect101(min(y_base + ly - r, h - 1 + r), h);
         for (int lx = tix; lx < tw; lx += NT_W) {
-            const int gx = reflect101(min(x_base + lx - r, w - 1 + r), w);
-            const size_t gi = (size_t)gy * w + gx;
+            const int gx = interior ? x_base + lx - r : reflect101(min(x_base + lx - r, w - 1 + r), w);
+            const int gi = gy * w + gx;
             const float z = depth[gi];
             const float zi = z != 0.f ? __fdiv_rn(1.f, z) : 0.f;           // NormalEstimator.h:181-187
             const int i = ly * tw + lx;
@@ -642,21 +649,45 @@ __device__ __forceinline__ void normals_tile(const float* __restrict__ depth, co
         }
     }
     __syncthreads();
-    for (int p = 0; p < 3; ++p)
-        for (int ly = tiy; ly < th; ly += TH) {
-            const double* row = a + p * tw * th + ly * tw + tix;
-            double s = 0.0;
-            for (int d = 0; d <= 2 * r; ++d) s = __dadd_rn(s, row[d]);      // left -> right
-            rs[(p * th + ly) * NT_W + tix] = s;
+    for (int ly = tiy; ly < th; ly += TH) {
+        const double* row = a + ly * tw + tix;
+        double s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        if (RC) {
+#pragma unroll
+            for (int d = 0; d <= 2 * RC; ++d) {                             // left -> right
+                s1 = __dadd_rn(s1, row[d]);
+                s2 = __dadd_rn(s2, row[tw * th + d]);
+                s3 = __dadd_rn(s3, row[2 * tw * th + d]);
+            }
+        } else {
+            for (int d = 0; d <= 2 * r; ++d) {
+                s1 = __dadd_rn(s1, row[d]);
+                s2 = __dadd_rn(s2, row[tw * th + d]);
+                s3 = __dadd_rn(s3, row[2 * tw * th + d]);
+            }
         }
+        rs[ly * NT_W + tix] = s1;
+        rs[(th + ly) * NT_W + tix] = s2;
+        rs[(2 * th + ly) * NT_W + tix] = s3;
+    }
     __syncthreads();
-    if (!inside) return;
+    if (!wanted) return;
     double s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    for (int d = 0; d <= 2 * r; ++d) {                                      // top -> bottom
-        const int j = (tiy + d) * NT_W + tix;
-        s1 = __dadd_rn(s1, rs[j]);
-        s2 = __dadd_rn(s2, rs[th * NT_W + j]);
-        s3 = __dadd_rn(s3, rs[2 * th * NT_W + j]);
+    if (RC) {
+#pragma unroll
+        for (int d = 0; d <= 2 * RC; ++d) {                                 // top -> bottom
+            const int j = (tiy + d) * NT_W + tix;
+            s1 = __dadd_rn(s1, rs[j]);
+            s2 = __dadd_rn(s2, rs[th * NT_W + j]);
+            s3 = __dadd_rn(s3, rs[2 * th * NT_W + j]);
+        }
+    } else {
+        for (int d = 0; d <= 2 * r; ++d) {
+            const int j = (tiy + d) * NT_W + tix;
+            s1 = __dadd_rn(s1, rs[j]);
+            s2 = __dadd_rn(s2, rs[th * NT_W + j]);
+            s3 = __dadd_rn(s3, rs[2 * th * NT_W + j]);
+        }
     }
     const float b1 = (float)s1, b2 = (float)s2, b3 = (float)s3;
     const size_t gi = (size_t)y * w + x;
@@ -675,8 +706,10 @@ normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x
                     const float* __restrict__ nsi, const float* __restrict__ Q, float* __restrict__ nx,
                     float* __restrict__ ny, float* __restrict__ nz, int w, int h, int r, float z_min, float z_max) {
     extern __shared__ __align__(16) unsigned char smem_dyn[];
-    normals_tile<NT_H>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
-                       threadIdx.y, smem_dyn);
+    if (r == 5) normals_tile<NT_H, 5>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
+                                      threadIdx.y, smem_dyn);
+    else normals_tile<NT_H, 0>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
+                               threadIdx.y, smem_dyn);
 }
 
 // The frames one launch of track_kernel works through, in order (gsdf_scan_run hands it up to kMaxBatch frames whose
@@ -691,7 +724,7 @@ struct FrameBatch {
     int* n_valid[kMaxBatch];
     float* normals[kMaxBatch];              // null: track only; else the 3 planes the fusion of frame f reads
     ResultSnapshot* snap[kMaxBatch];        // null, or where the result of frame f is left
-    unsigned long long* flog[kMaxBatch];    // null, or frame f's entry of the debug frame log (words 2, 3)
+    unsigned long long* flog[kMaxBatch];    // null, or frame f's entry of the debug frame log (words 2 .. 6)
     unsigned long long* dbg;                // null, or [gridDim.x][4 passes][6] + [gridDim.x][4] + [warps][8] %globaltimer stamps
 };
 // element f of a kernel-parameter array without a runtime-indexed access (which would copy the array to local memory)
@@ -771,8 +804,10 @@ normals_compact_kernel(const float* __restrict__ depth, const float* __restrict_
         if (tid == 0) flog_exit(flog);
         return;
     }
-    normals_tile<NC_H>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
-                       threadIdx.y, smem_dyn);
+    if (r == 5) normals_tile<NC_H, 5>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
+                                      threadIdx.y, smem_dyn);
+    else normals_tile<NC_H, 0>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
+                               threadIdx.y, smem_dyn);
     if (tid == 0) flog_exit(flog);
 }
 
@@ -933,9 +968,14 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
             }
             __syncthreads();
             GSDF_STAMP(5);
+            if (k == 0 && threadIdx.x == 0 && flog) atomicMax(flog + 4, global_ns());  // first pass done (last CTA)
             if (s_conv) { converged = 1; ++pass_id; break; }
         }
         GSDF_STAMPX(1);
+        if (threadIdx.x == 0 && flog) {  // Gauss-Newton loop left (last CTA), passes run
+            atomicMax(flog + 5, global_ns());
+            if (blockIdx.x == 0) flog[6] = (unsigned long long)(converged ? k + 1 : k);
+        }
         if (blockIdx.x == 0) {
             if (threadIdx.x < 7) st->pose7[threadIdx.x] = s_pose7[threadIdx.x];
             if (threadIdx.x < kAccTerms) st->sums[threadIdx.x] = s_tot[threadIdx.x];

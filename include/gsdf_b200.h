@@ -233,9 +233,9 @@ int64_t gsdf_trace_dump(gsdf_handle h, char* buf, int64_t size);
 /* Debug aid: per-CTA %globaltimer stamps of the tracker's phases (see gsdf_api.cu); not for production use. */
 gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int32_t* n_ctas);
 /* Debug aid, no reference counterpart: device-clock spans of the pipeline's two kernels per submitted frame.
- * out == NULL arms the log; otherwise out receives 256 x {frame-only kernel first entry, last exit, track+fuse kernel
- * first entry, last exit} in ns of %globaltimer (entry = ~0 / exit = 0 where nothing ran), frame seq modulo 256, and
- * the log is released. */
+ * out == NULL arms the log; otherwise out receives 256 x 8 words per frame (frame seq modulo 256): {frame-only kernel first
+ * entry, last exit, track+fuse first entry, last exit, first Gauss-Newton pass done, Gauss-Newton loop left (fusion starts),
+ * passes run, spare} in ns of %globaltimer (entry = ~0 / the others 0 where nothing ran), and the log is released. */
 gsdf_status gsdf_debug_frame_log(gsdf_handle h, unsigned long long* out);
 /* Multi-GPU: rank 0 calls gsdf_comm_unique_id, the 128 bytes are distributed by the caller (any transport),
  * then every rank calls gsdf_comm_init on its handle (cfg.world_size/rank).  Needed only for world_size > 1. */

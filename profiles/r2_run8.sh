@@ -1,0 +1,9 @@
+#!/bin/bash
+out=gpurun_out; mkdir -p $out; tag=${1:-r2h}
+timeout 1200 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest.log 2>&1; echo "rc=$?" >> $out/${tag}_pytest.log
+tail -n 4 $out/${tag}_pytest.log
+for v in grad base; do
+  timeout 300 python profiles/frame_log.py $v dev > $out/${tag}_frame_log_${v}.txt 2>&1; tail -n 2 $out/${tag}_frame_log_${v}.txt
+done
+GSDF_SERIAL=1 timeout 300 python profiles/frame_log.py grad dev > $out/${tag}_frame_log_grad_serial.txt 2>&1; tail -n 2 $out/${tag}_frame_log_grad_serial.txt
+timeout 200 python profiles/quick_fps.py grad; timeout 200 python profiles/quick_fps.py base

@@ -90,3 +90,33 @@ def anatomy(tag, inflight):
 
 anatomy("one frame in flight", 1)
 anatomy("four frames in flight (stamps of the last)", 4)
+
+
+# the same stamps from a launch in the MIDDLE of a long gsdf_scan_run (GSDF_DBG_SKIP): steady state, the frame-only kernels of
+# later frames run beside the tracker
+import os  # noqa: E402
+import torch  # noqa: E402
+if "steady" in sys.argv:
+    os.environ["GSDF_DBG_SKIP"] = "50"  # read by the library when the stamps are armed
+    dev = torch.from_numpy(frames[:100]).cuda()
+    sdf.reset()
+    sdf.scan_set_pose(np.array([0, 0, 0, 0, 0, 0, 1], np.float32))
+    sdf.scan_submit(depth_dev=dev[0].data_ptr(), track=False)
+    sdf.scan_collect()
+    sdf.scan_run([dev[i].data_ptr() for i in range(1, 10)], on_device=True)
+    sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, None, C.byref(n)))
+    res = sdf.scan_run([dev[i].data_ptr() for i in range(10, 100)], on_device=True)
+    raw = np.zeros(n.value * 220, np.uint64)
+    sdf._check(sdf.L.gsdf_debug_track_timers(sdf.h, raw.ctypes.data, C.byref(n)))
+    t = raw[: n.value * 24].reshape(n.value, 4, 6).astype(np.int64)
+    print("steady state (launch in the middle of a 90-frame run), passes of the launch's last frame:")
+    for k in range(4):
+        tk = t[:, k, :]
+        ok = tk[:, 0] > 0
+        if not ok.any():
+            continue
+        t0 = tk[ok, 0].min()
+        print(f" pass {k}: begin spread {(tk[ok, 0].max() - t0) / 1e3:.2f} us; pass length {(tk[ok, 5].max() - t0) / 1e3:.2f} us")
+        for i, nm in enumerate(names):
+            d = (tk[ok, i + 1] - tk[ok, i]) / 1e3
+            print(f"   {nm:12s} mean {d.mean():6.2f}  max {d.max():6.2f} us   (phase ends at {(tk[ok, i + 1].max() - t0) / 1e3:6.2f} us)")
