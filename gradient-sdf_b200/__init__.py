@@ -36,7 +36,7 @@ EXPORTS = [
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
     "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_scan_run", "gsdf_upload", "gsdf_host_alloc", "gsdf_host_free", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_debug_frame_log", "gsdf_p2p_export", "gsdf_p2p_connect", "gsdf_comm_unique_id", "gsdf_comm_init",
-    "gsdf_extract_mesh", "gsdf_version",
+    "gsdf_extract_mesh", "gsdf_vis_enable", "gsdf_vis_download", "gsdf_version",
 ]
 
 
@@ -98,6 +98,8 @@ def lib() -> C.CDLL:
     L.gsdf_voxel_count.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gsdf_download.argtypes = [H, C.c_int64, _i32p, _f32p, _f32p, _f32p, C.POINTER(C.c_int64)]
     L.gsdf_extract_mesh.argtypes = [H, C.c_int64, _f32p, C.POINTER(C.c_int64)]
+    L.gsdf_vis_enable.argtypes = [H, C.c_int64]
+    L.gsdf_vis_download.argtypes = [H, C.c_int64, _i32p, _i32p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gsdf_pose_matrix.restype = None
     L.gsdf_pose_matrix.argtypes = [_f32p, _f32p, _f32p]
     L.gsdf_pose_apply_increment.restype = None
@@ -422,6 +424,23 @@ class Sdf:
             order = np.lexsort((keys[:, 2], keys[:, 1], keys[:, 0]))
             keys, dist, weight, grad = keys[order], dist[order], weight[order], grad[order]
         return keys, dist, weight, grad
+
+    def vis_enable(self, max_entries: int):
+        """Start recording vis_ (MapGradPixelSdfOmp.cpp:118-120): which update() calls touched which voxel."""
+        self._check(self.L.gsdf_vis_enable(self.h, max_entries))
+
+    def get_vis(self):
+        """get_vis() (MapGradPixelSdf.h:140-142) as arrays: keys (n, 3) int32, frames (n,) int32 — one row per (voxel, frame)
+        pair, sorted by key then frame — and counter_ (frames fused so far)."""
+        n, nf = C.c_int64(0), C.c_int64(0)
+        self._check(self.L.gsdf_vis_download(self.h, 0, None, None, C.byref(n), C.byref(nf)))
+        keys, frames = np.zeros((n.value, 3), np.int32), np.zeros(n.value, np.int32)
+        if n.value:
+            self._check(self.L.gsdf_vis_download(self.h, n.value, keys.ctypes.data_as(_i32p), frames.ctypes.data_as(_i32p),
+                                                 C.byref(n), C.byref(nf)))
+            o = np.lexsort((frames, keys[:, 2], keys[:, 1], keys[:, 0]))
+            keys, frames = keys[o], frames[o]
+        return keys, frames, nf.value
 
     def extract_mesh(self):
         """Sdf::extract_mesh (marching cubes, MapGradPixelSdfOmp.cpp:132-183): triangles as an (n, 3, 3) float array in the

@@ -453,6 +453,7 @@ gsdf_status clear_map(gsdf_map* h) {
         CUDA_TRY(h, cudaMemsetAsync(h->view.acc2, 0, sizeof(float2) * h->cap * kBlockVoxels, h->stream));
     }
     CUDA_TRY(h, cudaMemsetAsync(h->d_ctr, 0, sizeof(Counters), h->stream));
+    if (h->view.vis_stamp) CUDA_TRY(h, cudaMemsetAsync(h->view.vis_stamp, 0, sizeof(unsigned int) * h->cap * kBlockVoxels, h->stream));
     FrameState zero;
     std::memset(&zero, 0, sizeof(zero));
     zero.pose7[6] = 1.f;
@@ -473,6 +474,7 @@ void free_all(gsdf_map* h) {
         if (h->p2p_peer_base[r] && r != h->cfg.rank) cudaIpcCloseMemHandle(h->p2p_peer_base[r]);
     cudaFree(h->d_p2p);
     cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2);
+    cudaFree(h->view.vis_stamp); cudaFree(h->view.vis_log);
     cudaFree(h->d_planes); cudaFree(h->d_res);
     for (int i = 0; i < kRing; ++i) { cudaFree(h->d_normals[i]); cudaFree(h->d_vlist[i]); }
     cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_compact_flags2); cudaFree(h->d_track_rows);
@@ -1045,6 +1047,52 @@ gsdf_status gsdf_extract_mesh(gsdf_handle h, int64_t max_triangles, float* verti
         for (size_t i = 0; i < total; ++i) std::memcpy(vertices9 + 9 * i, verts.data() + 9 * (size_t)order[i], sizeof(float) * 9);
     } while (0);
     cudaFree(d_box); cudaFree(d_keys); cudaFree(d_verts);
+    return s;
+}
+
+// vis_ (MapGradPixelSdf.h:70, MapGradPixelSdfOmp.cpp:118-120; read by PhotoBA, main_photo_ba.cpp:300-301): which fused
+// frames touched which voxel.  Off by default (it costs 4 bytes per voxel slot plus 8 bytes per (voxel, frame) pair).
+gsdf_status gsdf_vis_enable(gsdf_handle h, int64_t max_entries) {
+    if (!h || max_entries <= 0) return GSDF_ERR_INVALID;
+    if (h->view.vis_stamp) { h->err = "gsdf_vis_enable: already enabled"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    unsigned int* stamp = nullptr;
+    unsigned long long* log = nullptr;
+    CUDA_TRY(h, cudaMalloc(&stamp, sizeof(unsigned int) * h->cap * kBlockVoxels));
+    if (cudaMalloc(&log, sizeof(unsigned long long) * (size_t)max_entries) != cudaSuccess) { cudaFree(stamp); h->err = "gsdf_vis_enable: cudaMalloc failed"; return GSDF_ERR_CUDA; }
+    CUDA_TRY(h, cudaMemset(stamp, 0, sizeof(unsigned int) * h->cap * kBlockVoxels));
+    h->view.vis_stamp = stamp; h->view.vis_log = log; h->view.vis_cap = (unsigned long long)max_entries;
+    return GSDF_OK;
+}
+
+gsdf_status gsdf_vis_download(gsdf_handle h, int64_t max_n, int32_t* keys, int32_t* frames, int64_t* n_out, int64_t* frames_fused) {
+    if (!h || !n_out || max_n < 0) return GSDF_ERR_INVALID;
+    *n_out = 0;
+    if (!h->view.vis_stamp) { h->err = "gsdf_vis_download: call gsdf_vis_enable first"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    if (frames_fused) *frames_fused = (int64_t)h->h_ctr->fused_frames;
+    if (h->h_ctr->vis_overflow) { h->err = "visibility log full: entries dropped; raise max_entries of gsdf_vis_enable"; return GSDF_ERR_CAPACITY; }
+    const int64_t n = (int64_t)h->h_ctr->vis_cursor;
+    *n_out = n;
+    if (n == 0 || !keys || !frames) return GSDF_OK;  // count only
+    if (n > max_n) { h->err = "gsdf_vis_download: max_n too small"; return GSDF_ERR_INVALID; }
+    int* d_k = nullptr;
+    CUDA_TRY(h, cudaMalloc(&d_k, sizeof(int) * 4 * n));
+    vis_decode_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->view, (long long)n, d_k, d_k + 3 * n);
+    s = check_launch(h, "vis_decode_kernel");
+    if (s == GSDF_OK) {
+        if (cudaMemcpyAsync(keys, d_k, sizeof(int) * 3 * n, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaMemcpyAsync(frames, d_k + 3 * n, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaStreamSynchronize(h->stream) != cudaSuccess) { h->err = "gsdf_vis_download: copy failed"; s = GSDF_ERR_CUDA; }
+    }
+    cudaFree(d_k);
     return s;
 }
 

@@ -34,6 +34,12 @@ struct MapView {
     float2* acc2;
     uint32_t cap_mask;
     int32_t world, rank;
+    // optional per-voxel frame visibility (the reference's vis_, MapGradPixelSdfOmp.cpp:118-120), off unless gsdf_vis_enable:
+    // vis_stamp[voxel] = 1 + the last fused-frame counter that touched the voxel, vis_log = one {voxel address << 24 | frame}
+    // word per (voxel, frame) pair, appended the first time a frame touches the voxel
+    unsigned int* vis_stamp;
+    unsigned long long* vis_log;
+    unsigned long long vis_cap;
 };
 
 // Statistics and tickets.  The per-frame counters are spread over kCounterSlots slots (one per CTA modulo the
@@ -47,6 +53,9 @@ struct Counters {
     unsigned int ticket_snap;     // last-block-done ticket of the frame-result snapshot
     unsigned int barrier;         // arrival counter of track_kernel's grid barrier (0 between launches)
     unsigned int barrier_timeout; // a grid barrier gave up waiting: GSDF_ERR_CUDA
+    unsigned int fused_frames;    // Sdf::counter_ (Sdf.h:65): frames integrated so far (increase_counter, MapGradPixelSdfOmp.cpp:128)
+    unsigned int vis_overflow;    // the visibility log is full: entries were dropped
+    unsigned long long vis_cursor;  // entries in the visibility log
     struct Slot {
         unsigned long long points;   // pixels that passed every validity test
         unsigned long long updates;  // committed (pixel,k) samples

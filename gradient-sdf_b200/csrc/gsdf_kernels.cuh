@@ -425,6 +425,22 @@ download_kernel(MapView m, unsigned long long* cursor, long long max_n, int* __r
     }
 }
 
+// Visibility log -> (voxel key, frame) pairs: entry = voxel address << 24 | frame; the address is slot * 512 + local index.
+__global__ void __launch_bounds__(256)
+vis_decode_kernel(MapView m, long long n, int* __restrict__ keys, int* __restrict__ frames) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long e = m.vis_log[i];
+    const unsigned long long vaddr = e >> 24;
+    const unsigned int slot = (unsigned int)(vaddr >> 9), v = (unsigned int)(vaddr & 511);
+    int bx, by, bz;
+    unpack_block(m.keys[slot], bx, by, bz);
+    keys[3 * i] = (bx << 3) | (v & 7);
+    keys[3 * i + 1] = (by << 3) | ((v >> 3) & 7);
+    keys[3 * i + 2] = (bz << 3) | (v >> 6);
+    frames[i] = (int)(e & 0xFFFFFFull);
+}
+
 // Restore voxels from a download (checkpoint / resume; no counterpart in the reference): one thread per listed voxel,
 // the block is found or inserted, the voxel's accumulators are SET to {dist * W, grad, W}.  A sharded map keeps only
 // what its ownership rule assigns to it (including base-sdf halo copies), so every rank may be handed the whole list.

@@ -439,6 +439,9 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
     const float* R = pose.R;
     const int lane = threadIdx.x & 31;
     const int S = 2 * g.factor + 1;
+    // Sdf::counter_ of this update(): constant while any CTA is still fusing (it is advanced after the grid barrier /
+    // by the launch's last CTA)
+    const unsigned int frame_no = m.vis_stamp != nullptr ? __ldcg(&ctr->fused_frames) : 0u;
     // Work unit = (32-pixel chunk of the list, one ray sample); every warp takes an equal, CONTIGUOUS range of the
     // chunk-major unit sequence (sizes differ by at most one unit; before, whole (chunk, sample-group) items were
     // dealt round-robin and a warp had 3 or 4 of them: the 4-item CTAs finished 6 us after the others), so a warp
@@ -543,6 +546,21 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                     red_add_f2(m.acc2 + vaddr, v[0], v[1]);                            // MapPixelSdfOmp.cpp:183-185
                 }
             }
+            if (m.vis_stamp != nullptr) {  // vis_[vi] gets `true` at this frame's counter (MapGradPixelSdfOmp.cpp:118-120)
+                bool fresh = false;
+                if (leader) fresh = atomicExch(m.vis_stamp + vaddr, frame_no + 1u) != frame_no + 1u;  // first touch in this frame
+                const unsigned int fm = __ballot_sync(0xffffffffu, fresh);
+                if (fm) {
+                    unsigned long long base = 0;
+                    if (lane == __ffs(fm) - 1) base = atomicAdd(&ctr->vis_cursor, (unsigned long long)__popc(fm));
+                    base = __shfl_sync(0xffffffffu, base, __ffs(fm) - 1);
+                    if (fresh) {
+                        const unsigned long long o = base + __popc(fm & ((1u << lane) - 1));
+                        if (o < m.vis_cap) m.vis_log[o] = (vaddr << 24) | (unsigned long long)(frame_no & 0xFFFFFFu);
+                        else ctr->vis_overflow = 1u;
+                    }
+                }
+            }
             if (dbg && d_first) { dbg[4] = global_ns(); d_first = false; }
         }
     }
@@ -592,13 +610,17 @@ fuse_list_kernel(MapView m, FrameGeom g, Pose pose_arg, int pose_src, const int2
     unsigned int n_upd = 0, n_pts = 0;
     fuse_work<VARIANT, false>(m, g, pose, vlist, n_valid, nx, ny, nz, x0, y0, hom_inv, ctr, n_pts, n_upd);
     fuse_stats_flush(ctr, n_pts, n_upd);
-    if (snap != nullptr) {
+    {   // the last CTA advances Sdf::counter_ (increase_counter, MapGradPixelSdfOmp.cpp:128) and publishes the frame result
         __shared__ bool s_last;
         __threadfence();
         __syncthreads();
         if (threadIdx.x == 0) s_last = atomicInc(&ctr->ticket_snap, gridDim.x - 1) == gridDim.x - 1;
         __syncthreads();
-        if (s_last) { __threadfence(); write_snapshot(st, ctr, snap); }
+        if (s_last) {
+            __threadfence();
+            if (threadIdx.x == 0) ctr->fused_frames += 1u;
+            if (snap != nullptr) write_snapshot(st, ctr, snap);
+        }
     }
 }
 
@@ -891,6 +913,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
              PeerExchange px) {
     constexpr int NW = NT / 32;
     unsigned int barriers = 0;  // grid barriers passed so far in this launch
+    bool fused_prev = false;    // the frame just finished was integrated (every CTA takes the same decision)
     int pass_id = 0;            // Gauss-Newton passes run so far in this launch (tags of both exchanges)
     __shared__ float s_pose7[8];
     __shared__ Pose s_pose;
@@ -925,6 +948,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
             // every CTA waits for before it can reach this frame's fusion, so no statistics of this frame are in yet
             ResultSnapshot* prev = pick(fb.snap, f - 1);
             if (blockIdx.x == 0 && prev != nullptr) write_snapshot(st, ctr, prev, px.world > 1 ? px.error : nullptr);
+            if (blockIdx.x == 0 && threadIdx.x == 0 && fused_prev) ctr->fused_frames += 1u;  // increase_counter()
         }
         if (threadIdx.x == 0 && flog) flog_enter(flog + 2);
         int converged = 0, k = 0;
@@ -990,7 +1014,8 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
         }
         // main_scan_3d.cpp:261-264: integrate the frame at the pose just found, iff the optimisation converged — in the
         // same launch (every CTA holds the final pose in shared memory; the map is not read by anyone else meanwhile)
-        if (fuse_normals != nullptr && (fb.fuse_mode == 1 || (fb.fuse_mode == 2 && converged))) {
+        fused_prev = fuse_normals != nullptr && (fb.fuse_mode == 1 || (fb.fuse_mode == 2 && converged));
+        if (fused_prev) {
             const size_t np = (size_t)g.w * g.h;
             unsigned int n_upd = 0, n_pts = 0;
             fuse_work<VARIANT, true>(m, g, s_pose, vlist, n_valid, fuse_normals, fuse_normals + np, fuse_normals + 2 * np,
@@ -1009,7 +1034,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
         __syncthreads();
         if (s_last) {
             __threadfence();
-            if (threadIdx.x == 0) ctr->barrier = 0u;
+            if (threadIdx.x == 0) { ctr->barrier = 0u; if (fused_prev) ctr->fused_frames += 1u; }
             ResultSnapshot* snap = pick(fb.snap, fb.n - 1);
             if (snap != nullptr) write_snapshot(st, ctr, snap, px.world > 1 ? px.error : nullptr);
         }

@@ -16,7 +16,9 @@
 #include <cstdint>
 #include <fstream>
 #include <iostream>
+#include <array>
 #include <limits>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -272,6 +274,24 @@ public:
     MapGradPixelSdf() : Sdf(GSDF_GRAD_SDF, 0.02f, 0.05f) {}
     explicit MapGradPixelSdf(float voxel_size) : Sdf(GSDF_GRAD_SDF, voxel_size, 0.05f) {}
     MapGradPixelSdf(float voxel_size, float T) : Sdf(GSDF_GRAD_SDF, voxel_size, T) {}
+
+    // vis_ / get_vis(), MapGradPixelSdf.h:70,140-142: per voxel, which update() calls touched it.  The reference always
+    // records it (only PhotoBA reads it); here it costs device memory, so it is recorded from record_vis() on: call it after
+    // the first update() (the volume exists from then on), max_entries = (voxel, frame) pairs to make room for.
+    bool record_vis(int64_t max_entries) { return gpu_ && gsdf_vis_enable(gpu_, max_entries) == GSDF_OK; }
+    std::map<std::array<int, 3>, std::vector<bool>> get_vis() const {
+        std::map<std::array<int, 3>, std::vector<bool>> out;
+        int64_t n = 0, nf = 0;
+        if (!gpu_ || gsdf_vis_download(gpu_, 0, nullptr, nullptr, &n, &nf) != GSDF_OK || n == 0) return out;
+        std::vector<int32_t> keys(3 * n), frames(n);
+        if (gsdf_vis_download(gpu_, n, keys.data(), frames.data(), &n, &nf) != GSDF_OK) return out;
+        for (int64_t i = 0; i < n; ++i) {
+            std::vector<bool>& v = out[{keys[3 * i], keys[3 * i + 1], keys[3 * i + 2]}];
+            if ((int64_t)v.size() <= frames[i]) v.resize(frames[i] + 1, false);  // vis.resize(counter_); push_back(true)
+            v[frames[i]] = true;
+        }
+        return out;
+    }
 };
 
 class MapPixelSdf : public Sdf {

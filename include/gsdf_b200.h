@@ -145,6 +145,18 @@ gsdf_status gsdf_download(gsdf_handle h, int64_t max_n, int32_t* keys, float* di
  * only counts.  *n_triangles = triangles in the map; GSDF_ERR_INVALID if max_triangles is smaller.  Single-GPU maps. */
 gsdf_status gsdf_extract_mesh(gsdf_handle h, int64_t max_triangles, float* vertices9, int64_t* n_triangles);
 
+/* vis_ — per-voxel frame visibility (sdf_tracker/MapGradPixelSdf.h:70,140-142 get_vis(); written by update(),
+ * MapGradPixelSdfOmp.cpp:118-120: vis_[vi] gets `true` at index counter_, the number of update() calls before this one; read
+ * only by PhotoBA, photometric_opt/src/main_photo_ba.cpp:300-301).  Off by default: gsdf_vis_enable reserves 4 bytes per voxel
+ * slot and 8 bytes per (voxel, frame) entry, up to max_entries; call it before the frames whose visibility is wanted
+ * (gsdf_reset clears the log and the frame counter).  gsdf_vis_download returns one entry per (voxel, frame) pair — keys
+ * max_n*3, frames max_n: voxel key and the counter_ value of an update() that touched it — in no particular order, and
+ * *frames_fused = counter_; the reference's std::vector<bool> of a voxel has `true` exactly at its entries' frames and size
+ * 1 + the largest of them.  keys == NULL: only counts.  GSDF_ERR_CAPACITY if entries were dropped. */
+gsdf_status gsdf_vis_enable(gsdf_handle h, int64_t max_entries);
+gsdf_status gsdf_vis_download(gsdf_handle h, int64_t max_n, int32_t* keys, int32_t* frames, int64_t* n_out,
+                              int64_t* frames_fused);
+
 /* Checkpoint / resume, no counterpart in the reference (which can only dump the final map as text, save_sdf): sets the
  * listed voxels to the given state — the arrays are what gsdf_download returns (grad may be NULL for base-sdf); voxels
  * with weight <= 0 are skipped.  Into an empty map (gsdf_reset) this restores a downloaded one: same key set, same

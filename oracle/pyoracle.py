@@ -230,6 +230,8 @@ class RefScan(_Base):
         L.gsdf_ref_write.restype = C.c_int
         L.gsdf_ref_write.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
         L.gsdf_ref_upload.argtypes = [C.c_void_p, C.c_longlong, _i32p, _f32p, _f32p, _f32p]
+        L.gsdf_ref_vis.restype = C.c_longlong
+        L.gsdf_ref_vis.argtypes = [C.c_void_p, _i32p, _i32p, C.POINTER(C.c_longlong)]
         self.variant, self.w, self.h = variant, w, h
         self.K = _f32(K).reshape(9)
         self.handle = L.gsdf_ref_create(variant, voxel_size, trunc_factor, w, h, _fp(self.K), normal_win,
@@ -250,6 +252,17 @@ class RefScan(_Base):
         """The reference's own writers on the current map: which = 'mesh' | 'pc' | 'sdf' (extract_mesh, extract_pc,
         save_sdf); returns their bool."""
         return bool(self.L.gsdf_ref_write(self.handle, {"mesh": 0, "pc": 1, "sdf": 2}[which], str(filename).encode()))
+
+    def get_vis(self):
+        """The reference's vis_ as (keys (n, 3), frames (n,)) sorted by key then frame, and the largest vector size."""
+        mx = C.c_longlong(0)
+        n = self.L.gsdf_ref_vis(self.handle, None, None, C.byref(mx))
+        keys, frames = np.zeros((n, 3), np.int32), np.zeros(n, np.int32)
+        if n:
+            self.L.gsdf_ref_vis(self.handle, keys.ctypes.data_as(_i32p), frames.ctypes.data_as(_i32p), C.byref(mx))
+            o = np.lexsort((frames, keys[:, 2], keys[:, 1], keys[:, 0]))
+            keys, frames = keys[o], frames[o]
+        return keys, frames, int(mx.value)
 
     def upload(self, keys, dist, weight, grad):
         """Replace the reference's hash by the given voxels (arrays as download() returns them)."""

@@ -9,6 +9,7 @@
 //   RigidPointOptimizer::optimize         (cpp/include/sdf_tracker/RigidPointOptimizerOmp.cpp:44-106)
 // The per-frame ordering of main_scan_3d.cpp:208-266 (track, then fuse if converged) is driven by the
 // caller (Python) through these calls.  Nothing here is linked into libgsdf_b200.so.
+#include <algorithm>
 #include <cstddef>
 #include <cstdint>
 #include <cstring>
@@ -283,6 +284,25 @@ void gsdf_ref_upload(void* h, long long n, const int32_t* keys, const float* dis
         v.grad = Vec3f(grad[3 * i], grad[3 * i + 1], grad[3 * i + 2]);
         m[Vec3i(keys[3 * i], keys[3 * i + 1], keys[3 * i + 2])] = v;
     }
+}
+
+// vis_ (MapGradPixelSdf.h:70, get_vis() :140-142): one (voxel key, frame index) pair per `true` bit; returns the number of
+// pairs (call with keys == NULL to count); *max_size_out = the largest vector size (= 1 + last frame that touched a voxel).
+long long gsdf_ref_vis(void* h, int32_t* keys, int32_t* frames, long long* max_size_out) {
+    RefScan* s = (RefScan*)h;
+    if (s->variant != 0) return 0;
+    const auto vis = ((MapGradPixelSdf*)s->sdf)->get_vis();
+    long long n = 0, mx = 0;
+    for (const auto& el : vis) {
+        mx = std::max<long long>(mx, (long long)el.second.size());
+        for (size_t f = 0; f < el.second.size(); ++f)
+            if (el.second[f]) {
+                if (keys) { keys[3 * n] = el.first[0]; keys[3 * n + 1] = el.first[1]; keys[3 * n + 2] = el.first[2]; frames[n] = (int32_t)f; }
+                ++n;
+            }
+    }
+    if (max_size_out) *max_size_out = mx;
+    return n;
 }
 
 }  // extern "C"

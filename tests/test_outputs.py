@@ -169,3 +169,48 @@ def test_scan3d_output_files_against_the_reference_writers(pkg, po, synth, tmp_p
     pf = np.loadtxt(str(out) + "_poses.txt")
     assert pf.shape == (len(frames), 8) and np.allclose(np.linalg.norm(pf[:, 4:], axis=1), 1, atol=1e-5)
     assert np.abs(np.abs((pf[:, 4:] * poses[:, 3:]).sum(1)) - 1).max() < 1e-5 and np.abs(pf[:, 1:4] - poses[:, :3]).max() < 1e-5
+
+
+def test_voxel_visibility_against_the_reference(pkg, po, synth):
+    """vis_ (MapGradPixelSdfOmp.cpp:118-120): after the same pose-injected frames the (voxel, frame) pairs equal the `true`
+    bits of the reference's per-voxel vectors, pair for pair, also when a frame in between integrates nothing (counter_
+    still advances, MapGradPixelSdfOmp.cpp:128) and through the frame pipeline (fusion inside the tracker launch)."""
+    if not po.have_ref():
+        pytest.skip("oracle/_ref not built")
+    W, H = 320, 240
+    frames, poses, K, _ = synth.make_sequence(100, W, H)
+    vs, trunc = np.float32(0.01), np.float32(5)
+    nest = pkg.NormalEstimator(W, H, K, 11)
+    sdf = pkg.MapGradPixelSdf(vs, trunc * vs, nest, log2_capacity=16)
+    sdf.vis_enable(4_000_000)
+    ref = po.RefScan(0, vs, trunc, W, H, K)
+    seq = [frames[0], frames[1], np.zeros_like(frames[0]), frames[2], frames[3]]
+    pos = [poses[0], poses[1], poses[1], poses[2], poses[3]]
+    for f, p in zip(seq, pos):
+        sdf.update(f, p)
+        ref.update(f, p)
+    k, fr, nf = sdf.get_vis()
+    kr, frr, size = ref.get_vis()
+    assert nf == 5 and size == 5
+    assert k.shape == kr.shape and np.array_equal(k, kr) and np.array_equal(fr, frr)
+    assert 2 not in set(fr.tolist()) and set(fr.tolist()) == {0, 1, 3, 4}
+    # every voxel of the map has at least one entry, and only voxels of the map have entries
+    assert {tuple(x) for x in k} == {tuple(x) for x in sdf.download()[0]}
+    # the frame pipeline: frame 0 fused at identity, then tracked frames fused iff converged -> entries only at fused frames
+    sdf.reset()
+    ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+    sdf.scan_set_pose(ident)
+    sdf.scan_submit(depth_host=frames[0], track=False)
+    sdf.scan_collect()
+    res = sdf.scan_run([frames[i].ctypes.data for i in range(1, 7)], on_device=False)
+    k2, fr2, nf2 = sdf.get_vis()
+    assert nf2 == 1 + sum(r.fused for r in res)
+    assert set(fr2.tolist()) == set(range(nf2)) and {tuple(x) for x in k2} == {tuple(x) for x in sdf.download()[0]}
+    # log too small: reported, never silently truncated
+    small = pkg.MapGradPixelSdf(vs, trunc * vs, nest, log2_capacity=16)
+    small.vis_enable(1000)
+    small.update(frames[0], poses[0])
+    with pytest.raises(pkg.GsdfError) as e:
+        small.get_vis()
+    assert e.value.status == 3
+    sdf.close(); small.close()
