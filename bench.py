@@ -344,11 +344,23 @@ def room_scale_leg(args, pkg, torch, dist, world, rank, local_rank):
     torch.cuda.synchronize()
     ext = torch.cuda.ExternalStream(sdf.stream)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sdf._check(sdf.L.gsdf_debug_frame_log(sdf.h, None))  # in-kernel %globaltimer spans (nothing added to the streams)
     e0.record(ext)
     res = sdf.scan_run([frames[n_warm + i].data_ptr() for i in range(n_timed)], on_device=True)
     e1.record(ext)
     e1.synchronize()
     ms = e0.elapsed_time(e1)
+    log = np.zeros((256, 8), np.uint64)
+    sdf._check(sdf.L.gsdf_debug_frame_log(sdf.h, log.ctypes.data))
+    t = log[(log[:, 3] > 0) & (log[:, 1] > 0) & (log[:, 6] > 0)].astype(np.int64)
+    t = t[np.argsort(t[:, 2])][5:-2]
+    anatomy = None
+    if len(t) > 4:
+        anatomy = {"frames": int(len(t)), "period": float(np.diff(t[:, 2]).mean() / 1e3),
+                   "track_fuse_kernel": float((t[:, 3] - t[:, 2]).mean() / 1e3),
+                   "gauss_newton_loop": float((t[:, 5] - t[:, 2]).mean() / 1e3),
+                   "fusion_and_frame_end": float((t[:, 3] - t[:, 5]).mean() / 1e3),
+                   "frame_only_kernel_in_shadow": float((t[:, 1] - t[:, 0]).mean() / 1e3)}
     upd = float(sum(r.updates for r in res))
     valid = float(sum(r.track_valid for r in res))
     if world > 1:
@@ -374,7 +386,7 @@ def room_scale_leg(args, pkg, torch, dist, world, rank, local_rank):
             "voxel_updates_per_s": 1e3 * upd / ms, "updates_per_frame": upd / n_timed,
             "converged": int(sum(r.converged for r in res)), "frames": n_timed, "passes_per_frame": passes / n_timed,
             "max_translation_error_m": err, "voxels": int(nv), "blocks": int(nb), "voxels_after_build": int(nv0),
-            "build_frames": len(range(0, lap, stride)),
+            "build_frames": len(range(0, lap, stride)), "pipeline_anatomy_us_rank0": anatomy,
             "roofline": {"bound": "hbm", "achieved": alg_bytes / ms / 1e6, "peak": peak * world, "unit": "GB/s",
                          "frac": alg_bytes / ms / 1e6 / (peak * world), "peak_source": peak_src + (f" x {world} GPUs" if world > 1 else "")},
             "note": "10^8 voxels are not reachable at 1 cm / trunc 5 in a room of this size (about 1.5e7: 144 m^2 of wall and "

@@ -199,7 +199,7 @@ __device__ __forceinline__ void track_pixel(const MapView& m, const FrameGeom& g
 // butterfly below) instead of carrying 29 accumulators per thread from pixel to pixel: v[0..31] = this pixel's products
 // (zeros if it does not contribute).
 template <int VARIANT>
-__device__ __forceinline__ void track_pixel_terms(const MapView& m, const FrameGeom& g, const TrackIntr& ti, const float* R,
+__device__ __forceinline__ bool track_pixel_terms(const MapView& m, const FrameGeom& g, const TrackIntr& ti, const float* R,
                                                   const float* t, bool has, int yx, float z, float* v,
                                                   unsigned long long& ck, int& cs) {
     const int y = yx >> 16, x = yx & 0xFFFF;
@@ -228,6 +228,7 @@ __device__ __forceinline__ void track_pixel_terms(const MapView& m, const FrameG
     v[27] = phi * phi;
     v[28] = on ? 1.f : 0.f;
     v[29] = v[30] = v[31] = 0.f;
+    return on;
 }
 
 // The persistent tracker runs either two 384-thread CTAs or one 768-thread CTA per SM (same threads per SM; the second
@@ -971,8 +972,9 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
                 const bool has = j < n_valid;
                 const int2 e = j == gtid ? e0 : (has ? __ldcg(vlist + j) : make_int2(0, 0));
                 float v[32];
-                track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ck, cs);
-                wsum += warp_reduce_scatter_32(v);
+                const bool on = track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ck, cs);
+                // (a warp none of whose pixels contributes — off the surface, or another shard's super-block — adds nothing)
+                if (__any_sync(0xffffffffu, on)) wsum += warp_reduce_scatter_32(v);
             }
             GSDF_STAMP(1);
             const float mine = block_sum_29<NW>(wsum, s_warp);
