@@ -147,3 +147,64 @@ def test_scan3d_driver_reads_the_reference_dataset_conventions(synth, tmp_path):
     b = np.array([[float(x) for x in l[1:]] for l in res["synth"]])
     assert a.shape == b.shape == (6, 7) and np.abs(a - b).max() < 5e-5
     assert c.shape == (6, 7) and np.abs(a - c).max() < 5e-5
+
+
+REF_MAIN = ROOT / "gradient-sdf_b200" / "host" / "scan3d_ref_main"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("stype", ["grad-sdf", "base-sdf"])
+def test_the_references_own_driver_runs_on_the_library(synth, tmp_path, stype):
+    """cpp/depth_scanning/src/main_scan_3d.cpp of the reference, compiled UNMODIFIED (with its own loaders, mat.h, Timer.h,
+    Eigen, Sophus, CLI11) against the drop-in headers in gradient-sdf_b200/dropin and linked with libgsdf_b200.so — built by
+    build() where /root/reference exists, shipped as a binary — on a synth-format PNG dataset (img_loader/SynthLoader.h), next
+    to this repo's own driver on the same files: same pose file (labels and numbers), same clouds, same sdf dumps, a mesh."""
+    cv2 = pytest.importorskip("cv2")
+    if not REF_MAIN.exists():
+        pytest.skip("host/scan3d_ref_main not built (needs /root/reference where build() runs)")
+    W, H = 320, 240
+    noise = stype == "base-sdf"
+    frames, poses, K, _ = synth.make_sequence(400 if noise else 800, W, H, noise=noise)
+    frames = frames[:7]
+    data = tmp_path / "data"
+    (data / "depth").mkdir(parents=True)
+    (data / "rgb").mkdir()
+    np.savetxt(data / "intrinsics.txt", K.reshape(3, 3), fmt="%.9g")
+    for i, f in enumerate(frames):
+        assert cv2.imwrite(str(data / "depth" / f"{i + 1:03d}.png"), np.round(f.astype(np.float64) * 1000).astype(np.uint16))
+        assert cv2.imwrite(str(data / "rgb" / f"{i + 1:03d}.png"), np.zeros((H, W, 3), np.uint8))
+    outs = {}
+    for name, exe, extra in (("ref_main", REF_MAIN, []), ("ours", BIN, ["--capacity-log2", "17"])):
+        out = tmp_path / f"{name}_"
+        r = subprocess.run([str(exe), "--input", str(data) + "/", "--results", str(out), "--scan-type", stype, "--data-type", "synth",
+                            "--voxel-size", "0.01", "--trunc", "5", "--save-sdf"] + extra, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, (name, r.stderr[-1500:])
+        assert "points integrated into tSDF volume!" in r.stdout and "Could not save" not in r.stdout + r.stderr, name
+        outs[name] = str(out)
+    a = [l.split() for l in Path(outs["ref_main"] + "_poses.txt").read_text().splitlines()]
+    b = [l.split() for l in Path(outs["ours"] + "_poses.txt").read_text().splitlines()]
+    assert [l[0] for l in a] == [l[0] for l in b] == [f"{i + 1:03d}" for i in range(len(frames))]  # depth_timestamp()
+    pa, pb = np.array([[float(x) for x in l[1:]] for l in a]), np.array([[float(x) for x in l[1:]] for l in b])
+    assert pa.shape == pb.shape == (len(frames), 7) and np.abs(pa - pb).max() < (5e-5 if noise else 5e-4)
+    for suffix in ["gradient_sdf_grid_info.txt"]:
+        assert Path(outs["ref_main"] + suffix).read_text() == Path(outs["ours"] + suffix).read_text()
+    da, db = np.loadtxt(outs["ref_main"] + "gradient_sdf_sdf_d.txt"), np.loadtxt(outs["ours"] + "gradient_sdf_sdf_d.txt")
+    assert abs(len(da) - len(db)) <= 1e-3 * len(db)
+    for suffix in ["gradient_sdf_cloud_final.ply", "gradient_sdf_mesh_final.ply"]:
+        ha = Path(outs["ref_main"] + suffix).read_text().splitlines()
+        hb = Path(outs["ours"] + suffix).read_text().splitlines()
+        assert ha[:2] == hb[:2] and abs(int(ha[2].split()[-1]) - int(hb[2].split()[-1])) <= 0.01 * int(hb[2].split()[-1]) + 2
+    assert Path(outs["ref_main"] + "gradient_sdf_sdf_n0.txt").exists() == (stype == "grad-sdf")
+
+
+def test_the_references_own_driver_builds_against_the_drop_in_headers():
+    """CPU part: where /root/reference exists, build() has compiled the reference's unmodified main_scan_3d.cpp against
+    gradient-sdf_b200/dropin; its own argument checks (main_scan_3d.cpp:105-139) answer before any GPU call."""
+    if not Path("/root/reference/cpp/depth_scanning/src/main_scan_3d.cpp").exists() and not REF_MAIN.exists():
+        pytest.skip("no reference tree and no prebuilt binary")
+    assert REF_MAIN.exists(), "run __graft_entry__.build()"
+    r = subprocess.run([str(REF_MAIN), "--scan-type", "voxel-gp", "--data-type", "synth"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "Your specified scan type is not supported (yet)." in r.stderr
+    r = subprocess.run([str(REF_MAIN), "--scan-type", "grad-sdf", "--data-type", "synth", "--input", "/nonexistent/"],
+                       capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "No intrinsics file found" in r.stderr
