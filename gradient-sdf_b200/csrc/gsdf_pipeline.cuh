@@ -819,18 +819,19 @@ normals_compact_kernel(const float* __restrict__ depth, const float* __restrict_
             if (cta == ncta - 1) *n_valid_out = excl + total;
         }
     }
-    if (total > 0) {
-        __syncthreads();
-        if (mask & (1u << lane))
-            vlist[s_base + before + __popc(mask & ((1u << lane) - 1))] = make_int2((py << 16) | px, __float_as_int(z));
-    } else {  // no valid pixel in the tile: fusion never reads its normals
+    if (total == 0) {  // no valid pixel in the tile: fusion never reads its normals
         if (tid == 0) flog_exit(flog);
         return;
     }
+    // warps 1.. start staging the tile while warp 0 is still looking back (a quarter of this kernel's stall samples sat in
+    // that poll when every warp waited for it); the list entries are written afterwards — s_base is ordered before them by
+    // the barriers inside normals_tile
     if (r == 5) normals_tile<NC_H, 5>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
                                       threadIdx.y, smem_dyn);
     else normals_tile<NC_H, 0>(depth, x0n, y0n, nsi, Q, nx, ny, nz, w, h, r, z_min, z_max, blockIdx.x, blockIdx.y, threadIdx.x,
                                threadIdx.y, smem_dyn);
+    if (mask & (1u << lane))
+        vlist[s_base + before + __popc(mask & ((1u << lane) - 1))] = make_int2((py << 16) | px, __float_as_int(z));
     if (tid == 0) flog_exit(flog);
 }
 
@@ -972,9 +973,8 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
                 const bool has = j < n_valid;
                 const int2 e = j == gtid ? e0 : (has ? __ldcg(vlist + j) : make_int2(0, 0));
                 float v[32];
-                const bool on = track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ck, cs);
-                // (a warp none of whose pixels contributes — off the surface, or another shard's super-block — adds nothing)
-                if (__any_sync(0xffffffffu, on)) wsum += warp_reduce_scatter_32(v);
+                track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ck, cs);
+                wsum += warp_reduce_scatter_32(v);
             }
             GSDF_STAMP(1);
             const float mine = block_sum_29<NW>(wsum, s_warp);

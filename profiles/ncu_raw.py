@@ -13,7 +13,15 @@ want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "lts__t_sectors_op_red.sum", "lts__t_sectors_op_atom.sum", "lts__t_bytes.sum", "smsp__inst_executed.sum",
         "sm__cycles_elapsed.max", "smsp__cycles_active.avg", "l1tex__t_sectors_pipe_lsu_mem_global_op_red.sum",
         "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
-        "smsp__thread_inst_executed_per_inst_executed.ratio"]
+        "smsp__thread_inst_executed_per_inst_executed.ratio",
+        # atomics / reductions actually issued (the fusion's REDG traffic)
+        "smsp__inst_executed_op_global_red.sum", "smsp__inst_executed_op_global_atom.sum",
+        "l1tex__t_set_accesses_pipe_lsu_mem_global_op_red.sum", "l1tex__t_set_accesses_pipe_lsu_mem_global_op_atom.sum",
+        "l1tex__t_requests_pipe_lsu_mem_global_op_red.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_atom.sum",
+        "lts__t_requests_op_red.sum", "lts__t_requests_op_atom.sum", "lts__t_sectors_srcunit_tex_op_red.sum",
+        "smsp__warp_issue_stalled_barrier_per_warp_active.pct", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "smsp__inst_executed.avg.per_cycle_active", "launch__shared_mem_per_block_static", "launch__shared_mem_per_block_dynamic",
+        "smsp__inst_executed_pipe_lsu.sum", "smsp__inst_executed_pipe_fp64.sum", "sm__inst_executed_pipe_fp64.sum"]
 idx = {h: i for i, h in enumerate(hdr)}
 for r in rows[2:]:
     print("---", r[idx["Kernel Name"]][:90])
