@@ -16,7 +16,7 @@ def _last_line(name):
     return json.loads((ROOT / "profiles" / name).read_text().strip().splitlines()[-1])
 
 
-@pytest.mark.parametrize("name", ["r1f_bench_base.json", "r1f_bench_grad.json"])
+@pytest.mark.parametrize("name", ["r1f_bench_base.json", "r1f_bench_grad.json", "r2f_bench_grad.json"])
 def test_recorded_bench_line_has_the_contract_keys(name):
     d = _last_line(name)
     assert all(k in d for k in REQUIRED), [k for k in REQUIRED if k not in d]
@@ -31,6 +31,14 @@ def test_recorded_bench_line_has_the_contract_keys(name):
     assert c["kind"] == "reference" and c["cores"] >= 1 and c["unit"] == d["unit"] and c["sample"]
     assert d["gpu_launches"] > 0 and d["clocks"]["reasons"] == [] and d["clocks"]["sm_mhz"] <= d["clocks"]["sm_max_mhz"]
     assert d["steps"] >= 1 and d["warmup"] >= 3
+
+
+def test_round2_line_measures_the_target_with_the_same_config_in_both_arms():
+    ours, ref = _last_line("r2f_bench_grad.json"), _last_line("r2f_bench_reference.json")
+    assert ours["config"] == ref["config"] and ours["config"]["variant"] == "grad" and ours["config"]["voxel_size"] == 0.01
+    assert ours["metric"] == ref["metric"] and ref["impl"] == "reference" and ref["gpu_launches"] == 0
+    assert ours["repetitions"]["n"] >= 9 and ours["repetitions"]["value_min"] <= ours["value"] <= ours["repetitions"]["value_max"]
+    assert "host wall clock" in ours["e2e"]["timing"].lower() and ours["roofline"]["traffic"] > 0
 
 
 def test_recorded_reference_arm_line():
