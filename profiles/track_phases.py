@@ -1,5 +1,6 @@
 """Phase timing of the persistent tracker from in-kernel %globaltimer stamps: python profiles/track_phases.py [grad|base]"""
 import ctypes as C
+import os
 import sys
 from pathlib import Path
 
@@ -72,6 +73,8 @@ def anatomy(tag, inflight):
     print("   fusion done    ", f(x[:, 2]))
     print("   exit           ", f(x[:, 3]))
     # per-warp anatomy of the fusion phase (warps that had work)
+    if os.environ.get("GSDF_SAVE_FUSE_STAMPS"):
+        np.save(os.environ["GSDF_SAVE_FUSE_STAMPS"] + "_" + tag.split()[0] + ".npy", fw)
     fw = fw[fw[:, 0] > 0]
     if len(fw):
         units, probes, reds = fw[:, 6] & 0xFFFFFFFF, fw[:, 6] >> 32, fw[:, 7]
