@@ -36,7 +36,7 @@ EXPORTS = [
     "gsdf_llt_solve6", "gsdf_synchronize", "gsdf_stream", "gsdf_launch_count", "gsdf_profile_enable",
     "gsdf_profile_read", "gsdf_track_stats", "gsdf_accumulate_noalloc", "gsdf_scan_set_pose", "gsdf_scan_set_tracker",
     "gsdf_scan_submit", "gsdf_scan_collect", "gsdf_scan_pending", "gsdf_scan_run", "gsdf_upload", "gsdf_host_alloc", "gsdf_host_free", "gsdf_accumulate_local", "gsdf_trace_enable", "gsdf_trace_dump", "gsdf_debug_track_timers", "gsdf_debug_frame_log", "gsdf_p2p_export", "gsdf_p2p_connect", "gsdf_comm_unique_id", "gsdf_comm_init",
-    "gsdf_extract_mesh", "gsdf_vis_enable", "gsdf_vis_download", "gsdf_version",
+    "gsdf_extract_mesh", "gsdf_vis_enable", "gsdf_vis_download", "gsdf_get_voxels", "gsdf_grow", "gsdf_version",
 ]
 
 
@@ -99,6 +99,8 @@ def lib() -> C.CDLL:
     L.gsdf_download.argtypes = [H, C.c_int64, _i32p, _f32p, _f32p, _f32p, C.POINTER(C.c_int64)]
     L.gsdf_extract_mesh.argtypes = [H, C.c_int64, _f32p, C.POINTER(C.c_int64)]
     L.gsdf_vis_enable.argtypes = [H, C.c_int64]
+    L.gsdf_get_voxels.argtypes = [H, C.c_int64, _i32p, _f32p, _f32p, _f32p]
+    L.gsdf_grow.argtypes = [H, C.c_int32]
     L.gsdf_vis_download.argtypes = [H, C.c_int64, _i32p, _i32p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gsdf_pose_matrix.restype = None
     L.gsdf_pose_matrix.argtypes = [_f32p, _f32p, _f32p]
@@ -424,6 +426,19 @@ class Sdf:
             order = np.lexsort((keys[:, 2], keys[:, 1], keys[:, 0]))
             keys, dist, weight, grad = keys[order], dist[order], weight[order], grad[order]
         return keys, dist, weight, grad
+
+    def get_voxels(self, keys):
+        """getSdf(Vec3i) for many voxels: (dist, weight, grad) at the given keys, zeros where there is no voxel."""
+        k = np.ascontiguousarray(keys, np.int32).reshape(-1, 3)
+        n = len(k)
+        d, w, g = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+        if n:
+            self._check(self.L.gsdf_get_voxels(self.h, n, k.ctypes.data_as(_i32p), _fp(d), _fp(w), _fp(g)))
+        return d, w, g
+
+    def grow(self, new_log2_capacity: int):
+        """Rehash the block table into 2^new_log2_capacity slots (gsdf_grow)."""
+        self._check(self.L.gsdf_grow(self.h, new_log2_capacity))
 
     def vis_enable(self, max_entries: int):
         """Start recording vis_ (MapGradPixelSdfOmp.cpp:118-120): which update() calls touched which voxel."""

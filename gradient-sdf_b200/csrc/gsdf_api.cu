@@ -113,6 +113,9 @@ struct gsdf_map {
     int track_threads = kTrackThreadsMax;  // 768 (one CTA per SM) or 384 (two): GSDF_TRACK_THREADS
     Pose* d_pose = nullptr;
     float* d_out29 = nullptr;
+    float* d_query = nullptr;         // staging of gsdf_query / gsdf_get_voxels (8 floats per point), grown on demand
+    int64_t query_cap = 0;
+    bool auto_grow = true;            // GSDF_AUTO_GROW=0: a full hash is an error instead of a reason to grow
     unsigned long long* d_count2 = nullptr;
     // pinned host staging
     float* h_out29 = nullptr;
@@ -479,7 +482,7 @@ void free_all(gsdf_map* h) {
     for (int i = 0; i < kRing; ++i) { cudaFree(h->d_normals[i]); cudaFree(h->d_vlist[i]); }
     cudaFree(h->d_nvalid); cudaFree(h->d_compact_flags); cudaFree(h->d_compact_flags2); cudaFree(h->d_track_rows);
     cudaFree(h->d_dbg); cudaFree(h->d_flog);
-    cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2);
+    cudaFree(h->d_partials); cudaFree(h->d_pose); cudaFree(h->d_out29); cudaFree(h->d_count2); cudaFree(h->d_query);
     cudaFreeHost(h->h_out29); cudaFreeHost(h->h_ctr); cudaFreeHost(h->h_pose); cudaFreeHost(h->h_count2);
     cudaFreeHost(h->h_state);
     for (auto& sl : h->ring) {
@@ -638,6 +641,17 @@ gsdf_status set_state_pose(gsdf_map* h, const float* pose7) {
     return GSDF_OK;
 }
 
+// The reference's map never fills up; this one is rehashed into a table four times as large as soon as it is half full
+// (called where the pipeline is idle).  A frame adds a few per cent of the blocks already there, so a table that starts with
+// room for its first frame never drops a sample; GSDF_AUTO_GROW=0 keeps the capacity fixed (then a full table is an error).
+gsdf_status maybe_grow(gsdf_map* h, int64_t blocks) {
+    if (!h->auto_grow || blocks * 2 <= (int64_t)h->cap) return GSDF_OK;
+    int lg = h->cfg.log2_capacity;
+    while (lg < 26 && blocks * 4 > ((int64_t)1 << lg)) ++lg;
+    if (lg == h->cfg.log2_capacity) return GSDF_OK;
+    return gsdf_grow(h, lg);
+}
+
 gsdf_status pipeline_idle(gsdf_map* h) {
     if (h->seq_submitted != h->seq_collected) {
         h->err = "frames submitted with gsdf_scan_submit are still pending: collect them first";
@@ -680,6 +694,7 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     if (const char* e = std::getenv("GSDF_BATCH_FRAMES")) h->batch_frames = std::min(kMaxBatch, std::max(1, std::atoi(e)));
     if (const char* e = std::getenv("GSDF_SERIAL")) h->serial = e[0] == '1';
     if (const char* e = std::getenv("GSDF_MERGED_SIDE")) h->merged_side = e[0] == '1';
+    if (const char* e = std::getenv("GSDF_AUTO_GROW")) h->auto_grow = e[0] == '1';
     if (const char* e = std::getenv("GSDF_FUSE_IN_TRACK")) h->fuse_in_track = e[0] == '1';
     h->geom.w = c.width; h->geom.h = c.height;
     h->geom.vs = c.voxel_size;
@@ -791,6 +806,7 @@ gsdf_status gsdf_integrate(gsdf_handle h, const float* R9, const float* t3, gsdf
             h->err = "voxel-block hash full: samples dropped; raise gsdf_config.log2_capacity";
             return GSDF_ERR_CAPACITY;
         }
+        return maybe_grow(h, stats->blocks);
     }
     return GSDF_OK;
 }
@@ -868,31 +884,125 @@ gsdf_status gsdf_track(gsdf_handle h, float* pose7, int32_t max_iters, float con
     return GSDF_OK;
 }
 
+namespace {
+// staging buffer of 8 floats per point, kept between calls (Sdf::tsdf / weights / getSdf are called point by point by the
+// reference's callers: no cudaMalloc per call)
+gsdf_status query_staging(gsdf_map* h, int64_t n) {
+    if (n <= h->query_cap) return GSDF_OK;
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    cudaFree(h->d_query);
+    h->d_query = nullptr; h->query_cap = 0;
+    const int64_t cap = std::max<int64_t>(n, 4096);
+    CUDA_TRY(h, cudaMalloc(&h->d_query, sizeof(float) * 8 * cap));
+    h->query_cap = cap;
+    return GSDF_OK;
+}
+}  // namespace
+
 gsdf_status gsdf_query(gsdf_handle h, const float* pts, int64_t n, float* phi, float* grad, float* w) {
     if (!h || n < 0 || (n > 0 && (!pts || !phi || !grad || !w))) return GSDF_ERR_INVALID;
     if (n == 0) return GSDF_OK;
     CUDA_TRY(h, cudaSetDevice(h->cfg.device));
-    float *d_pts = nullptr, *d_out = nullptr;
-    CUDA_TRY(h, cudaMalloc(&d_pts, sizeof(float) * 3 * n));
-    cudaError_t e = cudaMalloc(&d_out, sizeof(float) * 5 * n);
-    if (e != cudaSuccess) { cudaFree(d_pts); h->err = "cudaMalloc(query)"; return GSDF_ERR_CUDA; }
-    gsdf_status s = GSDF_OK;
-    do {
-        if (cudaMemcpyAsync(d_pts, pts, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, h->stream) != cudaSuccess) { s = GSDF_ERR_CUDA; break; }
-        const int blocks = (int)((n + 255) / 256);
-        s = by_variant(h, [&](auto V) {
-            query_kernel<decltype(V)::value><<<blocks, 256, 0, h->stream>>>(h->view, h->geom, d_pts, (long long)n, d_out,
-                                                                            d_out + n, d_out + 4 * n);
-            return check_launch(h, "query_kernel");
-        });
-        if (s != GSDF_OK) break;
-        cudaMemcpyAsync(phi, d_out, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream);
-        cudaMemcpyAsync(grad, d_out + n, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, h->stream);
-        cudaMemcpyAsync(w, d_out + 4 * n, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream);
-        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { h->err = "query: stream sync failed"; s = GSDF_ERR_CUDA; }
-    } while (0);
-    cudaFree(d_pts); cudaFree(d_out);
-    return s;
+    gsdf_status s = query_staging(h, n);
+    if (s != GSDF_OK) return s;
+    float *d_pts = h->d_query, *d_out = h->d_query + 3 * n;
+    CUDA_TRY(h, cudaMemcpyAsync(d_pts, pts, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, h->stream));
+    const int blocks = (int)((n + 255) / 256);
+    s = by_variant(h, [&](auto V) {
+        query_kernel<decltype(V)::value><<<blocks, 256, 0, h->stream>>>(h->view, h->geom, d_pts, (long long)n, d_out, d_out + n, d_out + 4 * n);
+        return check_launch(h, "query_kernel");
+    });
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaMemcpyAsync(phi, d_out, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(grad, d_out + n, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(w, d_out + 4 * n, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return GSDF_OK;
+}
+
+// getSdf(Vec3i) (MapGradPixelSdf.h:127-129, MapPixelSdf.h:123-125), batched: the voxels stored at the given keys
+gsdf_status gsdf_get_voxels(gsdf_handle h, int64_t n, const int32_t* keys, float* dist, float* weight, float* grad) {
+    if (!h || n < 0 || (n > 0 && (!keys || !dist || !weight || !grad))) return GSDF_ERR_INVALID;
+    if (n == 0) return GSDF_OK;
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    s = query_staging(h, n);
+    if (s != GSDF_OK) return s;
+    int* d_keys = reinterpret_cast<int*>(h->d_query);
+    float* d_out = h->d_query + 3 * n;
+    CUDA_TRY(h, cudaMemcpyAsync(d_keys, keys, sizeof(int) * 3 * n, cudaMemcpyHostToDevice, h->stream));
+    s = by_variant(h, [&](auto V) {
+        get_voxels_kernel<decltype(V)::value><<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->view, (long long)n, d_keys, d_out,
+                                                                                              d_out + n, d_out + 2 * n);
+        return check_launch(h, "get_voxels_kernel");
+    });
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaMemcpyAsync(dist, d_out, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(weight, d_out + n, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(grad, d_out + 2 * n, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return GSDF_OK;
+}
+
+// The reference's map grows without bound (tsdf_[vi], MapGradPixelSdfOmp.cpp:114); this one grows by rehashing into a larger
+// table: new arrays, every block re-inserted and copied on the device, the old arrays freed.
+gsdf_status gsdf_grow(gsdf_handle h, int32_t new_log2_capacity) {
+    if (!h) return GSDF_ERR_INVALID;
+    if (new_log2_capacity <= h->cfg.log2_capacity || new_log2_capacity > 26) { h->err = "gsdf_grow: new_log2_capacity must be larger than the current one and at most 26"; return GSDF_ERR_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+    gsdf_status s = pipeline_idle(h);
+    if (s != GSDF_OK) return s;
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream_n));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    const size_t ncap = (size_t)1 << new_log2_capacity;
+    MapView nv = h->view;
+    nv.keys = nullptr; nv.acc4 = nullptr; nv.accW = nullptr; nv.acc2 = nullptr; nv.vis_stamp = nullptr;
+    nv.cap_mask = (uint32_t)(ncap - 1);
+    int* d_slot_map = nullptr;
+    auto fail = [&](const char* what) {
+        cudaFree(nv.keys); cudaFree(nv.acc4); cudaFree(nv.accW); cudaFree(nv.acc2); cudaFree(nv.vis_stamp); cudaFree(d_slot_map);
+        h->err = std::string("gsdf_grow: ") + what;
+        return GSDF_ERR_CUDA;
+    };
+    const bool grad = h->cfg.variant == GSDF_GRAD_SDF;
+    if (cudaMalloc(&nv.keys, sizeof(unsigned long long) * ncap) != cudaSuccess) return fail("out of device memory (keys)");
+    if (grad) {
+        if (cudaMalloc(&nv.acc4, sizeof(float4) * ncap * kBlockVoxels) != cudaSuccess || cudaMalloc(&nv.accW, sizeof(float) * ncap * kBlockVoxels) != cudaSuccess)
+            return fail("out of device memory (voxels)");
+        cudaMemsetAsync(nv.acc4, 0, sizeof(float4) * ncap * kBlockVoxels, h->stream);
+        cudaMemsetAsync(nv.accW, 0, sizeof(float) * ncap * kBlockVoxels, h->stream);
+    } else {
+        if (cudaMalloc(&nv.acc2, sizeof(float2) * ncap * kBlockVoxels) != cudaSuccess) return fail("out of device memory (voxels)");
+        cudaMemsetAsync(nv.acc2, 0, sizeof(float2) * ncap * kBlockVoxels, h->stream);
+    }
+    cudaMemsetAsync(nv.keys, 0xFF, sizeof(unsigned long long) * ncap, h->stream);
+    if (h->view.vis_stamp) {
+        if (cudaMalloc(&nv.vis_stamp, sizeof(unsigned int) * ncap * kBlockVoxels) != cudaSuccess || cudaMalloc(&d_slot_map, sizeof(int) * h->cap) != cudaSuccess)
+            return fail("out of device memory (visibility)");
+        cudaMemsetAsync(nv.vis_stamp, 0, sizeof(unsigned int) * ncap * kBlockVoxels, h->stream);
+    }
+    const int grid = (int)std::min<size_t>(h->cap, (size_t)h->sm_count * 32);
+    s = by_variant(h, [&](auto V) {
+        rehash_kernel<decltype(V)::value><<<grid, 128, 0, h->stream>>>(h->view, nv, h->d_ctr, d_slot_map);
+        return check_launch(h, "rehash_kernel");
+    });
+    if (s == GSDF_OK && h->view.vis_stamp) {
+        if (cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaStreamSynchronize(h->stream) != cudaSuccess) return fail("reading the counters failed");
+        const long long n = (long long)std::min<unsigned long long>(h->h_ctr->vis_cursor, h->view.vis_cap);
+        if (n > 0) {
+            vis_remap_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->view.vis_log, n, d_slot_map);
+            s = check_launch(h, "vis_remap_kernel");
+        }
+    }
+    if (s != GSDF_OK || cudaStreamSynchronize(h->stream) != cudaSuccess) return fail("rehash failed");
+    cudaFree(h->view.keys); cudaFree(h->view.acc4); cudaFree(h->view.accW); cudaFree(h->view.acc2); cudaFree(h->view.vis_stamp);
+    cudaFree(d_slot_map);
+    h->view = nv;
+    h->cap = ncap;
+    h->cfg.log2_capacity = new_log2_capacity;
+    return GSDF_OK;
 }
 
 gsdf_status gsdf_voxel_count(gsdf_handle h, int64_t* n_voxels, int64_t* n_blocks) {
@@ -1274,6 +1384,7 @@ gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out) {
         h->err = "sharded tracker: a peer rank did not reach the NVLink exchange within 0.5 s";
         return GSDF_ERR_NCCL;
     }
+    if (h->seq_collected == h->seq_submitted) return maybe_grow(h, out->blocks);  // pipeline empty: the table may grow now
     return GSDF_OK;
 }
 
@@ -1296,7 +1407,9 @@ gsdf_status gsdf_scan_run(gsdf_handle h, const float* const* frames, int64_t n, 
     int launches = 0;
     gsdf_status s = GSDF_OK;
     while (collected < n) {
-        while (submitted < n) {
+        // half full: submit nothing new, so that the pipeline drains and gsdf_scan_collect grows the table
+        const bool hold = h->auto_grow && collected > 0 && results[collected - 1].blocks * 2 > (int64_t)h->cap && submitted > collected;
+        while (submitted < n && !hold) {
             // batch sizes ramp up 1, 2, 4, ...: the first tracker launch waits for ONE frame-only kernel, not for four
             const int ramp = std::min(h->batch_frames, 1 << std::min(launches, 3));
             const int nb = batches ? (int)std::min<int64_t>(ramp, n - submitted) : 1;

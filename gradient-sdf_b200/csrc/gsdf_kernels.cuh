@@ -441,6 +441,68 @@ vis_decode_kernel(MapView m, long long n, int* __restrict__ keys, int* __restric
     frames[i] = (int)(e & 0xFFFFFFull);
 }
 
+// getSdf(Vec3i) (MapGradPixelSdf.h:127-129, MapPixelSdf.h:123-125): the voxels at the listed keys; absent or empty -> zeros.
+template <int VARIANT>
+__global__ void __launch_bounds__(256)
+get_voxels_kernel(MapView m, long long n, const int* __restrict__ keys, float* __restrict__ dist, float* __restrict__ weight,
+                  float* __restrict__ grad) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int vx = keys[3 * i], vy = keys[3 * i + 1], vz = keys[3 * i + 2];
+    float W = 0.f, S = 0.f, gx = 0.f, gy = 0.f, gz = 0.f;
+    const int slot = map_find(m, block_key_of(vx, vy, vz));
+    if (slot >= 0) {
+        const size_t addr = (size_t)slot * kBlockVoxels + local_index(vx, vy, vz);
+        if (VARIANT == 0) { W = m.accW[addr]; const float4 a = m.acc4[addr]; S = a.x; gx = a.y; gy = a.z; gz = a.w; }
+        else { const float2 a = m.acc2[addr]; W = a.x; S = a.y; }
+    }
+    const bool live = W > 0.f;
+    dist[i] = live ? S / W : 0.f;
+    weight[i] = live ? W : 0.f;
+    grad[3 * i] = live ? gx : 0.f; grad[3 * i + 1] = live ? gy : 0.f; grad[3 * i + 2] = live ? gz : 0.f;
+}
+
+// Growing the table (gsdf_grow): every block of the old table is re-inserted into the new one and its 512 voxels copied.
+// One CTA per old slot; slot_map[old slot] = new slot (for the visibility log, whose entries hold voxel addresses).
+template <int VARIANT>
+__global__ void __launch_bounds__(128)
+rehash_kernel(MapView old_m, MapView new_m, Counters* ctr, int* __restrict__ slot_map) {
+    __shared__ int s_slot;
+    for (unsigned int slot = blockIdx.x; slot <= old_m.cap_mask; slot += gridDim.x) {
+        const unsigned long long key = old_m.keys[slot];
+        if (key == kEmptyKey) continue;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            // (ctr->blocks already counts this block: the insert below must not count it again)
+            uint32_t ns = hash_key(key) & new_m.cap_mask;
+            for (;;) {
+                const unsigned long long k = atomicCAS(new_m.keys + ns, kEmptyKey, key);
+                if (k == kEmptyKey || k == key) break;
+                ns = (ns + 1) & new_m.cap_mask;
+            }
+            s_slot = (int)ns;
+            if (slot_map) slot_map[slot] = (int)ns;
+        }
+        __syncthreads();
+        const size_t src = (size_t)slot * kBlockVoxels, dst = (size_t)s_slot * kBlockVoxels;
+        for (int v = threadIdx.x; v < kBlockVoxels; v += blockDim.x) {
+            if (VARIANT == 0) { new_m.acc4[dst + v] = old_m.acc4[src + v]; new_m.accW[dst + v] = old_m.accW[src + v]; }
+            else new_m.acc2[dst + v] = old_m.acc2[src + v];
+            if (old_m.vis_stamp) new_m.vis_stamp[dst + v] = old_m.vis_stamp[src + v];
+        }
+    }
+    (void)ctr;
+}
+
+__global__ void __launch_bounds__(256)
+vis_remap_kernel(unsigned long long* __restrict__ log, long long n, const int* __restrict__ slot_map) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long e = log[i], vaddr = e >> 24;
+    const unsigned long long nv = ((unsigned long long)slot_map[vaddr >> 9] << 9) | (vaddr & 511);
+    log[i] = (nv << 24) | (e & 0xFFFFFFull);
+}
+
 // Restore voxels from a download (checkpoint / resume; no counterpart in the reference): one thread per listed voxel,
 // the block is found or inserted, the voxel's accumulators are SET to {dist * W, grad, W}.  A sharded map keeps only
 // what its ownership rule assigns to it (including base-sdf halo copies), so every rank may be handed the whole list.

@@ -170,15 +170,11 @@ public:
     void set_zmin(float z_min) { z_min_ = z_min; }
     void set_zmax(float z_max) { z_max_ = z_max; }
 
-    SdfVoxel getSdf(Vec3i idx) const {  // MapGradPixelSdf.h:127-129 (voxel centre query)
+    SdfVoxel getSdf(Vec3i idx) const {  // MapGradPixelSdf.h:127-129: the voxel stored at idx (zeros if there is none)
         SdfVoxel v;
-        HostMap m;
-        if (!download(m)) return v;
-        for (int64_t i = 0; i < m.n; ++i)
-            if (m.keys[3 * i] == idx[0] && m.keys[3 * i + 1] == idx[1] && m.keys[3 * i + 2] == idx[2]) {
-                v.dist = m.dist[i]; v.weight = m.weight[i];
-                v.grad = Vec3f(m.grad[3 * i], m.grad[3 * i + 1], m.grad[3 * i + 2]);
-            }
+        float g[3] = {0.f, 0.f, 0.f};
+        const int32_t key[3] = {idx[0], idx[1], idx[2]};
+        if (gpu_ && gsdf_get_voxels(gpu_, 1, key, &v.dist, &v.weight, g) == GSDF_OK) v.grad = Vec3f(g[0], g[1], g[2]);
         return v;
     }
 

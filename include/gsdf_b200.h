@@ -157,6 +157,19 @@ gsdf_status gsdf_vis_enable(gsdf_handle h, int64_t max_entries);
 gsdf_status gsdf_vis_download(gsdf_handle h, int64_t max_n, int32_t* keys, int32_t* frames, int64_t* n_out,
                               int64_t* frames_fused);
 
+/* getSdf(Vec3i) (MapGradPixelSdf.h:127-129, MapPixelSdf.h:123-125), batched: dist, weight and grad (n*3, zeros for
+ * base-sdf) of the voxels at keys (n*3); zeros where the voxel does not exist. */
+gsdf_status gsdf_get_voxels(gsdf_handle h, int64_t n, const int32_t* keys, float* dist, float* weight, float* grad);
+
+/* The reference's hash map grows without bound (tsdf_[vi], MapGradPixelSdfOmp.cpp:114).  Here the table is rehashed into a
+ * larger one: gsdf_grow moves every block into a table of 2^new_log2_capacity slots on the device (new arrays are allocated,
+ * the old ones freed; both exist for the duration of the call).  It happens by itself — to four times the blocks in use, as
+ * soon as the table is half full, at the points where no frame is in flight (gsdf_integrate with stats, gsdf_scan_collect of
+ * the last pending frame, inside gsdf_scan_run, which stops submitting and drains first) — unless GSDF_AUTO_GROW=0 is set
+ * in the environment at gsdf_create; then, and when growth fails for lack of memory, or when one frame alone overflows the
+ * table, a full table is GSDF_ERR_CAPACITY as before (never a silent drop). */
+gsdf_status gsdf_grow(gsdf_handle h, int32_t new_log2_capacity);
+
 /* Checkpoint / resume, no counterpart in the reference (which can only dump the final map as text, save_sdf): sets the
  * listed voxels to the given state — the arrays are what gsdf_download returns (grad may be NULL for base-sdf); voxels
  * with weight <= 0 are skipped.  Into an empty map (gsdf_reset) this restores a downloaded one: same key set, same

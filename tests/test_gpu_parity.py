@@ -365,7 +365,8 @@ def test_edge_cases(pkg, po, synth):
     sdf.close()
 
 
-def test_capacity_overflow_is_reported(pkg, synth):
+def test_capacity_overflow_is_reported(pkg, synth, monkeypatch):
+    monkeypatch.setenv("GSDF_AUTO_GROW", "0")  # fixed capacity: a full table is an error (with growth see the tests below)
     W, H = 160, 120
     frames, poses, K, _ = synth.make_sequence(50, W, H)
     nest = pkg.NormalEstimator(W, H, K, 11)
@@ -376,7 +377,8 @@ def test_capacity_overflow_is_reported(pkg, synth):
     sdf.close()
 
 
-def test_frame_loop_reports_a_full_hash_and_leaves_the_handle_usable(pkg, synth):
+def test_frame_loop_reports_a_full_hash_and_leaves_the_handle_usable(pkg, synth, monkeypatch):
+    monkeypatch.setenv("GSDF_AUTO_GROW", "0")
     """gsdf_scan_run stops at the first error, drains what is in flight and keeps the error; after gsdf_reset the same
     handle runs again (with room this time nothing is dropped)."""
     W, H = 160, 120
@@ -409,6 +411,51 @@ def test_frame_loop_reports_a_full_hash_and_leaves_the_handle_usable(pkg, synth)
     res2 = big.scan_run([frames[i].ctypes.data for i in range(1, 10)], on_device=False)
     assert [r.iters for r in res2] == [r.iters for r in res]
     big.close()
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_the_block_table_grows_like_the_references_map(pkg, po, synth, variant):
+    """The reference's hash map never fills up (tsdf_[vi], MapGradPixelSdfOmp.cpp:114).  A table that starts with room for
+    little more than its first frame is rehashed on the way (gsdf_grow, by itself when half full): the pose-injected key set
+    still equals the oracle's bit for bit, values in tolerance, getSdf() of single voxels and vis_ survive the moves; and
+    the frame loop (gsdf_scan_run) runs the orbit that overflows a fixed table of the same size."""
+    W, H = 320, 240
+    frames, poses, K, _ = synth.make_sequence(100, W, H)
+    vs, trunc, CAP = np.float32(0.01), np.float32(5), 9
+    nest = pkg.NormalEstimator(W, H, K, 11)
+    cls = pkg.MapGradPixelSdf if variant == 0 else pkg.MapPixelSdf
+    sdf = cls(vs, trunc * vs, nest, log2_capacity=CAP)  # 512 blocks: room for the first frame, not for the orbit
+    orc = po.Oracle(variant, vs, trunc, W, H, K)
+    if variant == 0:
+        sdf.vis_enable(2_000_000)
+    caps = []
+    for i in range(0, 40, 4):
+        sdf.update(frames[i], poses[i])
+        orc.update(frames[i], poses[i])
+        caps.append(sdf.voxel_count()[1])
+    assert caps[0] < (1 << CAP) < caps[-1], caps  # more blocks than the table started with
+    got, want = sdf.download(), orc.download()
+    check_map(got, want, float(trunc * vs), variant)
+    pick = np.random.default_rng(3).integers(0, len(got[0]), 500)
+    d, w, g = sdf.get_voxels(got[0][pick])
+    assert np.array_equal(d, got[1][pick]) and np.array_equal(w, got[2][pick]) and np.array_equal(g, got[3][pick])
+    d0, w0, g0 = sdf.get_voxels(np.array([[100000, 5, 5]], np.int32))
+    assert not d0.any() and not w0.any() and not g0.any()
+    if variant == 0:
+        k, fr, nf = sdf.get_vis()
+        assert nf == 10 and {tuple(x) for x in k} == {tuple(x) for x in got[0]} and set(fr.tolist()) == set(range(10))
+    sdf.grow(12)  # explicit growth keeps everything too
+    again = sdf.download()
+    assert all(np.array_equal(a, b) for a, b in zip(got, again))
+    sdf.close()
+    loop = cls(vs, trunc * vs, nest, log2_capacity=CAP)
+    ident = np.array([0, 0, 0, 0, 0, 0, 1], np.float32)
+    loop.scan_set_pose(ident)
+    loop.scan_submit(depth_host=frames[0], track=False)
+    loop.scan_collect()
+    res = loop.scan_run([frames[i].ctypes.data for i in range(1, 40)], on_device=False)
+    assert len(res) == 39 and res[-1].blocks > (1 << CAP) and sum(r.converged for r in res) >= 35
+    loop.close()
 
 
 def test_full_size_properties(pkg, synth):
