@@ -115,6 +115,7 @@ struct gsdf_map {
     float* d_out29 = nullptr;
     float* d_query = nullptr;         // staging of gsdf_query / gsdf_get_voxels (8 floats per point), grown on demand
     int64_t query_cap = 0;
+    int carveout = 50;                // preferred shared-memory carveout (%) of the two pipeline kernels (GSDF_CARVEOUT)
     bool auto_grow = true;            // GSDF_AUTO_GROW=0: a full hash is an error instead of a reason to grow
     unsigned long long* d_count2 = nullptr;
     // pinned host staging
@@ -556,7 +557,13 @@ gsdf_status create_impl(gsdf_map* h) {
         // Shadow mode needs an SM whose L1/shared split already leaves room for the frame-only kernel's 116 KB when its CTA
         // arrives: the split is chosen when a kernel lands on an EMPTY SM, and the tracker alone would ask for a few KB, after
         // which no frame-only CTA fits beside it until the SM drains (measured: the two kernels then simply alternate).
-        CUDA_TRY(h, cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        // 50 % of the maximum (a 132 KB shared / 124 KB L1 split): room for the tracker CTA and two frame-only CTAs, and an L1
+        // that still holds the voxels a CTA re-reads pass after pass (measured 21.5 k frames/s against 21.1 k with the maximum
+        // carveout; 40 % and 64 % fell back into the alternating state, profiles/r2t_carveout_sweep.txt)
+        int carve = 50;
+        if (const char* e = std::getenv("GSDF_CARVEOUT")) carve = std::min(100, std::max(0, std::atoi(e)));  // % of the maximum
+        CUDA_TRY(h, cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        h->carveout = carve;
         int per_sm = 0;
         CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, h->track_threads, 0));
         if (per_sm < 1) { h->err = "track_kernel does not fit on an SM"; return GSDF_ERR_CUDA; }
@@ -587,8 +594,7 @@ gsdf_status create_impl(gsdf_map* h) {
     if (normals_smem(h, NC_H) > 48 * 1024)
         CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)normals_smem(h, NC_H)));
-    CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                     cudaSharedmemCarveoutMaxShared));
+    CUDA_TRY(h, cudaFuncSetAttribute(normals_compact_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, h->carveout));
     build_normal_cache(c, h->h_planes);
     CUDA_TRY(h, cudaMemcpyAsync(h->d_planes, h->h_planes.data(), sizeof(float) * n * 11, cudaMemcpyHostToDevice, h->stream));
     return clear_map(h);
