@@ -404,6 +404,10 @@ __device__ __forceinline__ void exchange_29(unsigned long long* rows /* [2][grid
 // pointer jumping (v += v[next], next = next[next]): ceil(log2(group size)) rounds of NV + 1 shuffles, where a
 // leader that collects its members one by one needs group size - 1 rounds — and at 1 cm voxels a voxel spans ~12
 // pixels of an 8x4 tile.  After the last round the first member (the leader) holds the group's sum.
+#ifndef GSDF_FUSE_STAMPS
+#define GSDF_FUSE_STAMPS 0  // 1: per-warp stamps of the first fusion unit (make GSDF_FUSE_STAMPS=1; profiles/track_phases.py)
+#endif
+
 template <int NV>
 __device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool narrow, bool has, float* v, bool& leader) {
     const int lane = threadIdx.x & 31;
@@ -453,11 +457,18 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
     const int warps_total = (gridDim.x * blockDim.x) >> 5;
     const int wid = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     const int u1 = (int)(units * (wid + 1) / warps_total);
-    // debug stamps of this warp (lane 0): 0 entry, 1 first pixel data there, 2 first slot known, 3 first merge done, 4 first
-    // reductions issued, 5 all units done, 6 = units | probes << 32, 7 = reductions issued by the warp
+    // debug stamps of this warp (lane 0): 0 entry, 5 all units done, 6 = units | probes << 32; and, only in a build with
+    // -DGSDF_FUSE_STAMPS=1 (they cost ~21 of the ~250 instructions of a unit): 1 first pixel data there, 2 first slot
+    // known, 3 first merge done, 4 first reductions issued, 7 = reductions issued by the warp
     unsigned long long* dbg = (fdbg && lane == 0) ? fdbg + (size_t)wid * 8 : nullptr;
-    unsigned int d_probes = 0, d_reds = 0;
+    unsigned int d_probes = 0;
+#if GSDF_FUSE_STAMPS
+    unsigned int d_reds = 0;
     bool d_first = true;
+#define GSDF_FSTAMP(i) do { if (dbg && d_first) dbg[i] = global_ns(); } while (0)
+#else
+#define GSDF_FSTAMP(i) do { } while (0)
+#endif
     if (dbg) { dbg[0] = global_ns(); dbg[6] = (unsigned long long)(u1 - (int)(units * wid / warps_total)); }
     for (int u = (int)(units * wid / warps_total); u < u1;) {
         const int chunk = u / S, k_first = u - chunk * S;
@@ -488,8 +499,11 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
             }
         }
         n_pts += (valid && k_first == 0) ? 1u : 0u;
-        if (dbg && d_first) dbg[1] = global_ns();
-        unsigned long long last_key = kEmptyKey;
+        GSDF_FSTAMP(1);
+        // block of the previous committed sample of this ray and its slot.  Consecutive samples are one voxel apart and a
+        // segment has at most 2*factor+1 of them, so the low 10 bits of each block coordinate identify the block here:
+        // one 30-bit compare per sample instead of packing and comparing the 63-bit key (which is built only for a probe)
+        unsigned int last_sig = 0xFFFFFFFFu;
         int slot = -1;
         for (int kk = k_first - g.factor; kk < k_end - g.factor; ++kk) {               // :103
             bool has = false;
@@ -501,9 +515,10 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                 const float py = __fadd_rn(__fmul_rn(s, Rxy1), pose.t[1]);
                 const float pz = __fadd_rn(__fmul_rn(s, Rxy2), pose.t[2]);
                 const int vx = float2vox1(g.vs_inv, px), vy = float2vox1(g.vs_inv, py), vz = float2vox1(g.vs_inv, pz);
-                const unsigned long long key = block_key_of(vx, vy, vz);
+                const int bx = vx >> kBlockLog2, by = vy >> kBlockLog2, bz = vz >> kBlockLog2;  // arithmetic shift = floor
+                const unsigned int sig = ((unsigned)bx & 1023u) | (((unsigned)by & 1023u) << 10) | (((unsigned)bz & 1023u) << 20);
                 // sharded map: samples of other ranks' blocks (7 of 8 on 8 GPUs) are dropped before the sdf arithmetic
-                const int keep = m.world > 1 ? shard_keeps<VARIANT>(m.world, m.rank, key, vx, vy, vz) : 3;
+                const int keep = m.world > 1 ? shard_keeps<VARIANT>(m.world, m.rank, pack_block(bx, by, bz), vx, vy, vz) : 3;
                 float sdf = 0.f, wgt = 0.f;
                 if (keep) {
                     const float qx = __fsub_rn(__fmul_rn(g.vs, (float)vx), pose.t[0]);     // :107
@@ -513,9 +528,9 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                     wgt = sdf_weight(sdf, g.T, g.inv_T);
                 }
                 if (wgt > 0.f) {                                                       // :110-111
-                    if (key != last_key) {
-                        last_key = key;
-                        slot = map_find_or_insert(m, key, ctr);
+                    if (sig != last_sig) {
+                        last_sig = sig;
+                        slot = map_find_or_insert(m, pack_block(bx, by, bz), ctr);
                         if (slot < 0) atomicAdd(&ctr->overflow, 1u);
                         ++d_probes;
                     }
@@ -529,7 +544,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                     }
                 }
             }
-            if (dbg && d_first) dbg[2] = global_ns();
+            GSDF_FSTAMP(2);
             if (!__any_sync(0xffffffffu, has)) continue;  // nothing to commit in this unit (outside the band / not ours)
             if (!has) {
 #pragma unroll
@@ -537,8 +552,10 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
             }
             bool leader;
             warp_merge_by_key<(VARIANT == 0 ? 5 : 2)>(vaddr, narrow, has, v, leader);
-            if (dbg && d_first) dbg[3] = global_ns();
+            GSDF_FSTAMP(3);
+#if GSDF_FUSE_STAMPS
             if (fdbg) d_reds += __popc(__ballot_sync(0xffffffffu, leader));
+#endif
             if (leader) {
                 if (VARIANT == 0) {
                     red_add_f4(m.acc4 + vaddr, v[0], v[1], v[2], v[3]);                // :115-117
@@ -562,10 +579,19 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                     }
                 }
             }
+#if GSDF_FUSE_STAMPS
             if (dbg && d_first) { dbg[4] = global_ns(); d_first = false; }
+#endif
         }
     }
-    if (dbg) { dbg[5] = global_ns(); dbg[6] |= (unsigned long long)d_probes << 32; dbg[7] = d_reds; }
+    if (dbg) {
+        dbg[5] = global_ns();
+        dbg[6] |= (unsigned long long)d_probes << 32;
+#if GSDF_FUSE_STAMPS
+        dbg[7] = d_reds;
+#endif
+    }
+#undef GSDF_FSTAMP
 }
 
 // statistics: warp -> CTA (shared-memory atomics) -> one slot per CTA; never thousands of warps on one word
