@@ -362,6 +362,18 @@ gsdf_status launch_fuse(gsdf_map* h, const Pose& pose, int pose_src, int nbuf, c
 // bufs[i] and leaves its result in snaps[i]); pose, converged flag and iteration count of the last frame stay in
 // d_state.  fuse_mode 0/1/2 (never / always / iff converged) integrates each frame in the same launch.  Sharded maps
 // without a peer connection take the per-iteration NCCL path below (nb = 1 only).
+// The persistent tracker as a launchable function: grad-/base-sdf, 768 or 2 x 384 threads per SM, with or without the debug
+// stamps (the stamped twin runs only while gsdf_debug_track_timers is armed: its stamp tests cost instructions in every unit).
+const void* track_fn(int variant, int threads, bool stamps) {
+    const bool two = threads == 384;
+    if (variant == 0) {
+        if (stamps) return two ? (const void*)track_kernel<0, 384, true> : (const void*)track_kernel<0, 768, true>;
+        return two ? (const void*)track_kernel<0, 384, false> : (const void*)track_kernel<0, 768, false>;
+    }
+    if (stamps) return two ? (const void*)track_kernel<1, 384, true> : (const void*)track_kernel<1, 768, true>;
+    return two ? (const void*)track_kernel<1, 384, false> : (const void*)track_kernel<1, 768, false>;
+}
+
 gsdf_status launch_track_batch(gsdf_map* h, const TrackParams& tp, const int* bufs, int nb, cudaStream_t stream, int fuse_mode,
                                ResultSnapshot* const* snaps, int64_t seq0);
 
@@ -405,8 +417,7 @@ gsdf_status launch_track_batch(gsdf_map* h, const TrackParams& tp, const int* bu
             void* args[] = {&view, &geom, &ti_, &st, &rows, &tag0, &tp_, &planes, &ctr, &fb, &px};
             // cooperative launch: the driver guarantees that all CTAs are resident together (the exchange and grid_barrier
             // rely on it)
-            const void* fn = h->track_threads == 384 ? (const void*)track_kernel<decltype(V)::value, 384>
-                                                     : (const void*)track_kernel<decltype(V)::value, 768>;
+            const void* fn = track_fn(decltype(V)::value, h->track_threads, fb.dbg != nullptr);
             cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(h->track_blocks), dim3(h->track_threads), args, 0, stream);
             if (e != cudaSuccess) { h->err = std::string("launch of track_kernel: ") + cudaGetErrorString(e); return GSDF_ERR_CUDA; }
             return check_launch(h, "track_kernel");
@@ -552,8 +563,8 @@ gsdf_status create_impl(gsdf_map* h) {
     if (const char* e = std::getenv("GSDF_TRACK_THREADS")) h->track_threads = std::atoi(e) == 384 ? 384 : 768;
     {
         const bool two = h->track_threads == 384;
-        const void* fn = c.variant == GSDF_GRAD_SDF ? (two ? (const void*)track_kernel<0, 384> : (const void*)track_kernel<0, 768>)
-                                                    : (two ? (const void*)track_kernel<1, 384> : (const void*)track_kernel<1, 768>);
+        const int v = c.variant == GSDF_GRAD_SDF ? 0 : 1;
+        const void* fn = track_fn(v, h->track_threads, false);
         // Shadow mode needs an SM whose L1/shared split already leaves room for the frame-only kernel's 116 KB when its CTA
         // arrives: the split is chosen when a kernel lands on an EMPTY SM, and the tracker alone would ask for a few KB, after
         // which no frame-only CTA fits beside it until the SM drains (measured: the two kernels then simply alternate).
@@ -563,6 +574,7 @@ gsdf_status create_impl(gsdf_map* h) {
         int carve = 50;
         if (const char* e = std::getenv("GSDF_CARVEOUT")) carve = std::min(100, std::max(0, std::atoi(e)));  // % of the maximum
         CUDA_TRY(h, cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        CUDA_TRY(h, cudaFuncSetAttribute(track_fn(v, h->track_threads, true), cudaFuncAttributePreferredSharedMemoryCarveout, carve));
         h->carveout = carve;
         int per_sm = 0;
         CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, h->track_threads, 0));
@@ -709,6 +721,12 @@ gsdf_status gsdf_create(const gsdf_config* cfg, gsdf_handle* out) {
     h->geom.inv_T = (float)(1. / (double)c.truncation);   // Sdf.h:105
     h->geom.z_min = c.z_min; h->geom.z_max = c.z_max;
     h->geom.factor = (int)std::floor(c.truncation / c.voxel_size);  // MapGradPixelSdfOmp.cpp:78
+    // fusion counts its work units (32-pixel chunk x ray sample) in 32 bits
+    if (((double)c.width * c.height / 32. + 1.) * (2. * h->geom.factor + 1.) >= 2147483648.) {
+        g_create_error = "width * height * (2 * truncation / voxel_size + 1) is too large";
+        free_all(h);
+        return GSDF_ERR_INVALID;
+    }
     gsdf_status s = create_impl(h);
     if (s != GSDF_OK) { g_create_error = h->err; free_all(h); return s; }
     *out = h;

@@ -404,10 +404,6 @@ __device__ __forceinline__ void exchange_29(unsigned long long* rows /* [2][grid
 // pointer jumping (v += v[next], next = next[next]): ceil(log2(group size)) rounds of NV + 1 shuffles, where a
 // leader that collects its members one by one needs group size - 1 rounds — and at 1 cm voxels a voxel spans ~12
 // pixels of an 8x4 tile.  After the last round the first member (the leader) holds the group's sum.
-#ifndef GSDF_FUSE_STAMPS
-#define GSDF_FUSE_STAMPS 0  // 1: per-warp stamps of the first fusion unit (make GSDF_FUSE_STAMPS=1; profiles/track_phases.py)
-#endif
-
 template <int NV>
 __device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool narrow, bool has, float* v, bool& leader) {
     const int lane = threadIdx.x & 31;
@@ -434,7 +430,9 @@ __device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool n
 // gets the same number of units (+-1).  Called by fuse_list_kernel and by the tail of track_kernel (fused launch).
 // COHERENT: the list and the normals were produced earlier in the SAME launch (frame kernel) -> L2 loads, not the
 // non-coherent read-only path.
-template <int VARIANT, bool COHERENT>
+// STAMPS: debug stamps per warp (track_kernel<.., true>, launched only while gsdf_debug_track_timers is armed: the stamp
+// tests alone are ~21 of the ~250 instructions of a unit).
+template <int VARIANT, bool COHERENT, bool STAMPS = false>
 __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, const Pose& pose,
                                           const int2* __restrict__ vlist, int n_valid, const float* __restrict__ nx,
                                           const float* __restrict__ ny, const float* __restrict__ nz,
@@ -453,24 +451,20 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
     // loads the pixel data of only one or two chunks.  Warp ranges are interleaved over the CTAs (warp-major).
     const bool narrow = m.cap_mask < (1u << 23) - 32u;  // voxel addresses (slot * 512 + local) below 2^32 - 2^14
     const int nchunks = (n_valid + 31) >> 5;
-    const long long units = (long long)nchunks * S;
+    const int units = nchunks * S;  // < 2^31: a frame has at most 2^26 pixels (gsdf_create), S is at most a few hundred
     const int warps_total = (gridDim.x * blockDim.x) >> 5;
     const int wid = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
-    const int u1 = (int)(units * (wid + 1) / warps_total);
-    // debug stamps of this warp (lane 0): 0 entry, 5 all units done, 6 = units | probes << 32; and, only in a build with
-    // -DGSDF_FUSE_STAMPS=1 (they cost ~21 of the ~250 instructions of a unit): 1 first pixel data there, 2 first slot
-    // known, 3 first merge done, 4 first reductions issued, 7 = reductions issued by the warp
-    unsigned long long* dbg = (fdbg && lane == 0) ? fdbg + (size_t)wid * 8 : nullptr;
-    unsigned int d_probes = 0;
-#if GSDF_FUSE_STAMPS
-    unsigned int d_reds = 0;
+    // warp w takes units [w*q + min(w, r), ...): q or q + 1 of them (one division, the same for every warp)
+    const int q = units / warps_total, r = units - q * warps_total;
+    const int u0 = wid * q + min(wid, r), u1 = u0 + q + (wid < r ? 1 : 0);
+    // debug stamps of this warp (lane 0): 0 entry, 1 first pixel data there, 2 first slot known, 3 first merge done, 4 first
+    // reductions issued, 5 all units done, 6 = units | probes << 32, 7 = reductions issued by the warp
+    unsigned long long* dbg = (STAMPS && fdbg && lane == 0) ? fdbg + (size_t)wid * 8 : nullptr;
+    unsigned int d_probes = 0, d_reds = 0;
     bool d_first = true;
-#define GSDF_FSTAMP(i) do { if (dbg && d_first) dbg[i] = global_ns(); } while (0)
-#else
-#define GSDF_FSTAMP(i) do { } while (0)
-#endif
-    if (dbg) { dbg[0] = global_ns(); dbg[6] = (unsigned long long)(u1 - (int)(units * wid / warps_total)); }
-    for (int u = (int)(units * wid / warps_total); u < u1;) {
+#define GSDF_FSTAMP(i) do { if (STAMPS && dbg && d_first) dbg[i] = global_ns(); } while (0)
+    if (dbg) { dbg[0] = global_ns(); dbg[6] = (unsigned long long)(u1 - u0); }
+    for (int u = u0; u < u1;) {
         const int chunk = u / S, k_first = u - chunk * S;
         const int k_end = min(S, k_first + (u1 - u));  // exclusive
         u += k_end - k_first;
@@ -509,6 +503,7 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
             bool has = false;
             unsigned long long vaddr = 0;
             float v[VARIANT == 0 ? 5 : 2];
+            float wq = 0.f, sq = 0.f;  // this lane's weight and sdf
             if (valid) {
                 const float s = __fadd_rn(z, __fmul_rn((float)kk, g.vs));
                 const float px = __fadd_rn(__fmul_rn(s, Rxy0), pose.t[0]);             // :105
@@ -532,30 +527,28 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                         last_sig = sig;
                         slot = map_find_or_insert(m, pack_block(bx, by, bz), ctr);
                         if (slot < 0) atomicAdd(&ctr->overflow, 1u);
-                        ++d_probes;
+                        if (STAMPS) ++d_probes;
                     }
                     if (slot >= 0) {
                         has = true;
                         vaddr = (unsigned long long)slot * kBlockVoxels + local_index(vx, vy, vz);
-                        const float ws = wgt * sdf_truncate(sdf, g.T);
-                        if (VARIANT == 0) { v[0] = ws; v[1] = wgt * Rn0; v[2] = wgt * Rn1; v[3] = wgt * Rn2; v[4] = wgt; }
-                        else { v[0] = wgt; v[1] = ws; }
                         n_upd += keep >> 1;  // halo copies are not counted twice
                     }
                 }
+                wq = wgt; sq = sdf;
             }
             GSDF_FSTAMP(2);
             if (!__any_sync(0xffffffffu, has)) continue;  // nothing to commit in this unit (outside the band / not ours)
-            if (!has) {
-#pragma unroll
-                for (int i = 0; i < (VARIANT == 0 ? 5 : 2); ++i) v[i] = 0.f;
+            // the summands, computed by every lane (lanes without a sample are in no one's group: theirs are never read)
+            {
+                const float ws = wq * sdf_truncate(sq, g.T);
+                if (VARIANT == 0) { v[0] = ws; v[1] = wq * Rn0; v[2] = wq * Rn1; v[3] = wq * Rn2; v[4] = wq; }
+                else { v[0] = wq; v[1] = ws; }
             }
             bool leader;
             warp_merge_by_key<(VARIANT == 0 ? 5 : 2)>(vaddr, narrow, has, v, leader);
             GSDF_FSTAMP(3);
-#if GSDF_FUSE_STAMPS
-            if (fdbg) d_reds += __popc(__ballot_sync(0xffffffffu, leader));
-#endif
+            if (STAMPS && fdbg) d_reds += __popc(__ballot_sync(0xffffffffu, leader));
             if (leader) {
                 if (VARIANT == 0) {
                     red_add_f4(m.acc4 + vaddr, v[0], v[1], v[2], v[3]);                // :115-117
@@ -579,18 +572,10 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
                     }
                 }
             }
-#if GSDF_FUSE_STAMPS
-            if (dbg && d_first) { dbg[4] = global_ns(); d_first = false; }
-#endif
+            if (STAMPS && dbg && d_first) { dbg[4] = global_ns(); d_first = false; }
         }
     }
-    if (dbg) {
-        dbg[5] = global_ns();
-        dbg[6] |= (unsigned long long)d_probes << 32;
-#if GSDF_FUSE_STAMPS
-        dbg[7] = d_reds;
-#endif
-    }
+    if (dbg) { dbg[5] = global_ns(); dbg[6] |= (unsigned long long)d_probes << 32; dbg[7] = d_reds; }
 #undef GSDF_FSTAMP
 }
 
@@ -785,9 +770,9 @@ __device__ __forceinline__ T pick(T const (&a)[kMaxBatch], int f) {
     return r;
 }
 
-#define GSDF_STAMP(i) do { if (fb.dbg && threadIdx.x == 0 && k < 4) fb.dbg[((size_t)blockIdx.x * 4 + k) * 6 + (i)] = global_ns(); } while (0)
+#define GSDF_STAMP(i) do { if (STAMPS && fb.dbg && threadIdx.x == 0 && k < 4) fb.dbg[((size_t)blockIdx.x * 4 + k) * 6 + (i)] = global_ns(); } while (0)
 // whole-launch stamps, after the per-pass ones: [gridDim.x][4] = entry, Gauss-Newton loop left, fusion done, exit
-#define GSDF_STAMPX(i) do { if (fb.dbg && threadIdx.x == 0) fb.dbg[(size_t)gridDim.x * 24 + (size_t)blockIdx.x * 4 + (i)] = global_ns(); } while (0)
+#define GSDF_STAMPX(i) do { if (STAMPS && fb.dbg && threadIdx.x == 0) fb.dbg[(size_t)gridDim.x * 24 + (size_t)blockIdx.x * 4 + (i)] = global_ns(); } while (0)
 
 // Frame-only work of the pipeline in ONE launch: each CTA compacts the z-valid pixels of its 32 x 8 tile (8 warps <-> its
 // eight 8x4 sub-tiles) and then computes the tile's normals.  List order: 32x8 tiles row-major, 8x4 sub-tiles row-major
@@ -933,7 +918,7 @@ __device__ __forceinline__ void peer_allreduce_29(const PeerExchange& px, int k,
     __syncthreads();
 }
 
-template <int VARIANT, int NT>
+template <int VARIANT, int NT, bool STAMPS = false /* phase stamps into fb.dbg (gsdf_debug_track_timers armed) */>
 __global__ void __launch_bounds__(NT == 384 ? 512 : 1024, NT == 384 ? 2 : 1)  // 64 registers per thread (see kTrackThreadsMax)
 track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
              unsigned long long* __restrict__ rows /* [2][gridDim.x][kAccStride] tagged words */, unsigned int tag0,
@@ -1046,9 +1031,9 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
         if (fused_prev) {
             const size_t np = (size_t)g.w * g.h;
             unsigned int n_upd = 0, n_pts = 0;
-            fuse_work<VARIANT, true>(m, g, s_pose, vlist, n_valid, fuse_normals, fuse_normals + np, fuse_normals + 2 * np,
-                                     planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd,
-                                     fb.dbg ? fb.dbg + (size_t)gridDim.x * 28 : nullptr);
+            fuse_work<VARIANT, true, STAMPS>(m, g, s_pose, vlist, n_valid, fuse_normals, fuse_normals + np, fuse_normals + 2 * np,
+                                             planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd,
+                                             (STAMPS && fb.dbg) ? fb.dbg + (size_t)gridDim.x * 28 : nullptr);
             fuse_stats_flush(ctr, n_pts, n_upd);
         }
         GSDF_STAMPX(2);

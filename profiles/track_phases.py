@@ -83,14 +83,15 @@ def anatomy(tag, inflight):
         print(f"   fusion per warp: {len(busy)} of {len(fw)} warps had units; units/warp {units.mean():.2f} (max {units.max()}), "
               f"probes/warp {probes.mean():.2f}, reductions/warp {reds.mean():.1f}")
         print(f"      warp total        mean {d(0, 5).mean():6.2f}  max {d(0, 5).max():6.2f} us")
-        if busy[:, 1].any():  # library built with GSDF_FUSE_STAMPS=1 (make -C gradient-sdf_b200 GSDF_FUSE_STAMPS=1)
+        busy = busy[busy[:, 4] > 0]  # warps that committed something (a chunk of invalid normals commits nothing)
+        if len(busy):
             print(f"      pixel data        mean {d(0, 1).mean():6.2f}  max {d(0, 1).max():6.2f} us")
             print(f"      first slot known  mean {d(1, 2).mean():6.2f}  max {d(1, 2).max():6.2f} us")
             print(f"      first merge       mean {d(2, 3).mean():6.2f}  max {d(2, 3).max():6.2f} us")
             print(f"      first reds issued mean {d(3, 4).mean():6.2f}  max {d(3, 4).max():6.2f} us")
             print(f"      remaining units   mean {d(4, 5).mean():6.2f}  max {d(4, 5).max():6.2f} us")
         else:
-            print("      (first-unit stamps and the reduction count need a build with GSDF_FUSE_STAMPS=1)")
+            print("      (no first-unit stamps in this launch)")
         print(f"      entry spread {(fw[:, 0].max() - fw[:, 0].min()) / 1e3:.2f} us, end spread {(fw[:, 5].max() - fw[:, 5].min()) / 1e3:.2f} us")
 
 
