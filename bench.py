@@ -655,7 +655,7 @@ def run_ours(args):
         # duration in the pipeline is taken from the in-kernel span log of an identical, separately run pass (events
         # cannot bracket it without putting operations between the frames); the per-kernel event brackets of the
         # unfused profile pass are kept in per_kernel_GBps.
-        # gsdf_scan_run gives the tracker up to 4 frames per launch: launches in the timed region = one frame-only
+        # gsdf_scan_run gives the tracker up to 8 frames per launch: launches in the timed region = one frame-only
         # kernel per frame + the tracker launches
         fpl = args.steps / max(1, main["launches"] - args.steps)
         kname = (f"track_kernel<{v}> (fused launch over {fpl:.2f} frames: per frame the Gauss-Newton loop, "
@@ -701,10 +701,10 @@ def run_ours(args):
                         "once per pass (L2 = 126 MB); the map is state carried from frame to frame by design; "
                         "value_l2_flushed_unpipelined = one frame in flight, 256 MiB L2 flush before each",
                   "timing": f"median of {args.reps} passes; value = K / device-timeline span (CUDA events on the library's "
-                            "stream) from the first timed submit to the last result, up to 12 frames in flight, no untimed "
+                            "stream) from the first timed submit to the last result, up to 24 frames in flight, no untimed "
                             "gaps, max over ranks; every pass = reset map, frame 0 fused, W warm-up frames, K timed frames; "
                             "one whole pass is run and discarded before the first timed one",
-                  "api": "gsdf_scan_run (the frame loop in C: up to 4 frames per tracker launch, uploads and frame-only "
+                  "api": "gsdf_scan_run (the frame loop in C: up to 8 frames per tracker launch, uploads and frame-only "
                          "kernels ahead of it)"},
         "voxel_updates_per_s": main["voxel_updates_per_s"], "updates_per_frame": main["updates_per_frame"],
         "converged_steps": main["converged_steps"], "gn_iterations_per_step": iters_per_step,

@@ -55,7 +55,7 @@ NcclApi g_nccl;
 constexpr int kNcclFloat = 7, kNcclSum = 0;  // ncclFloat32, ncclSum (nccl.h)
 std::string g_create_error;
 constexpr int kFlogFrames = 256;
-constexpr int kRing = 12;       // frame slots: gsdf_scan_run keeps up to three batches of kMaxBatch frames in flight
+constexpr int kRing = 24;       // frame slots: gsdf_scan_run keeps up to three batches of kMaxBatch frames in flight
 constexpr int kMaxPending = 4;  // frames in flight through gsdf_scan_submit (the documented limit)
 }  // namespace
 
@@ -143,7 +143,7 @@ struct gsdf_map {
     bool fuse_in_track = true;  // GSDF_FUSE_IN_TRACK=0: separate fusion launch instead of the tracker launch's tail
     bool merged_side = true;    // GSDF_MERGED_SIDE=0: compaction and normals as two launches
     bool serial = false;        // GSDF_SERIAL=1: frame-only kernels on the main stream instead of the side stream
-    int batch_frames = kMaxBatch;  // GSDF_BATCH_FRAMES=1..4: frames per tracker launch in gsdf_scan_run
+    int batch_frames = kMaxBatch;  // GSDF_BATCH_FRAMES=1..8: frames per tracker launch in gsdf_scan_run
     unsigned long long* d_dbg = nullptr;  // tracker phase stamps (gsdf_debug_track_timers)
     int64_t dbg_only_seq = -1;            // >= 0: only the launch that holds this frame writes stamps (GSDF_DBG_SKIP)
     unsigned long long* d_flog = nullptr; // [kFlogFrames][8] kernel spans per pipeline frame (gsdf_debug_frame_log)
@@ -413,7 +413,7 @@ gsdf_status launch_track_batch(gsdf_map* h, const TrackParams& tp, const int* bu
             }
             PeerExchange px = h->px;  // world <= 1 unless gsdf_p2p_connect succeeded
             if (px.world > 1 && tp.max_iters > 63) { h->err = "sharded tracking over NVLink supports at most 63 iterations"; return GSDF_ERR_INVALID; }
-            if (px.world > 1) { px.launch = ++h->p2p_launches; px.epoch0 = px.launch * 256u; }  // <= kMaxBatch * 63 passes per launch
+            if (px.world > 1) { px.launch = ++h->p2p_launches; px.epoch0 = px.launch * 512u; }  // <= kMaxBatch * 63 passes per launch
             void* args[] = {&view, &geom, &ti_, &st, &rows, &tag0, &tp_, &planes, &ctr, &fb, &px};
             // cooperative launch: the driver guarantees that all CTAs are resident together (the exchange and grid_barrier
             // rely on it)

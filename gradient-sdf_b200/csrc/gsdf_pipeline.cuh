@@ -195,6 +195,22 @@ __device__ __forceinline__ void track_pixel(const MapView& m, const FrameGeom& g
     }
 }
 
+// Key of the block a pixel's lookup probes first (Lookup<V>::eval: the voxel's block / the block of the cell's floor corner),
+// computed exactly as track_pixel_terms + eval compute it.
+template <int VARIANT>
+__device__ __forceinline__ unsigned long long first_block_key(const MapView& m, const FrameGeom& g, const TrackIntr& ti,
+                                                              const float* R, const float* t, int yx, float z) {
+    const int y = yx >> 16, x = yx & 0xFFFF;
+    const float x0 = ((float)x - ti.cx) * ti.fx_inv, y0 = ((float)y - ti.cy) * ti.fy_inv;
+    const float cx_ = x0 * z, cy_ = y0 * z;
+    const float px = dot3_rn(R[0], R[1], R[2], cx_, cy_, z) + t[0];
+    const float py = dot3_rn(R[3], R[4], R[5], cx_, cy_, z) + t[1];
+    const float pz = dot3_rn(R[6], R[7], R[8], cx_, cy_, z) + t[2];
+    if (VARIANT == 0) return block_key_of(float2vox1(g.vs_inv, px), float2vox1(g.vs_inv, py), float2vox1(g.vs_inv, pz));
+    return block_key_of((int)floorf(__fmul_rn(g.vs_inv, px)), (int)floorf(__fmul_rn(g.vs_inv, py)),
+                        (int)floorf(__fmul_rn(g.vs_inv, pz)));
+}
+
 // Same terms for the persistent tracker, which reduces every pixel's 29 products across the warp at once (the reduce-scatter
 // butterfly below) instead of carrying 29 accumulators per thread from pixel to pixel: v[0..31] = this pixel's products
 // (zeros if it does not contribute).
@@ -750,7 +766,7 @@ normals_tile_kernel(const float* __restrict__ depth, const float* __restrict__ x
 // lists and normals the side stream has prepared; every other caller passes one).  Entering, leaving and relaunching
 // the kernel costs 7.6 us per launch at 640x480 (entry 1.2, result + exit 2.4, kernel-to-kernel gap 4); between two
 // frames of a batch there is one grid barrier instead.
-constexpr int kMaxBatch = 4;
+constexpr int kMaxBatch = 8;
 struct FrameBatch {
     int n;                                  // frames in this launch
     int fuse_mode;                          // 0 = never, 1 = always (setup / ground-truth pose), 2 = iff the optimisation converged
@@ -850,11 +866,16 @@ normals_compact_kernel(const float* __restrict__ depth, const float* __restrict_
 // instead of cooperative_groups' grid.sync(): barrier number b is passed once the counter reaches (b + 1) * gridDim.x,
 // the last CTA to leave the kernel resets it, and a wait that exceeds 2 s sets barrier_timeout (reported by
 // gsdf_scan_collect as an error) instead of hanging the device.
-__device__ __forceinline__ void grid_barrier(Counters* ctr, unsigned int target) {
+// The barrier in two halves, so that work which does not depend on the other CTAs can be done between arriving and waiting.
+__device__ __forceinline__ void grid_arrive(Counters* ctr) {
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(&ctr->barrier, 1u);
+    }
+}
+__device__ __forceinline__ void grid_wait(Counters* ctr, unsigned int target) {
+    if (threadIdx.x == 0) {
         unsigned int seen, spins = 0;
         unsigned long long t0 = 0;
         for (;;) {
@@ -954,9 +975,23 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
         const int n_valid = __ldcg(pick(fb.n_valid, f));
         int2 e0 = make_int2(0, 0);
         if (gtid < g.w * g.h) e0 = __ldcg(vlist + gtid);
+        unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
+        int cs = -1;
         if (f > 0) {
-            // every CTA's fusion of the previous frame (and its statistics) is complete before anyone reads the map again
-            grid_barrier(ctr, ++barriers * gridDim.x);
+            // every CTA's fusion of the previous frame (and its statistics) is complete before anyone reads the map again.
+            // Between arriving and waiting: the block of this thread's pixel at the pose the frame starts from (the one the
+            // previous frame ended with, still in shared memory) is looked up in the key table, so that the first pass
+            // finds its slot cached like the later ones do.  Other CTAs may still be inserting: a block that is found stays
+            // where it is, one that is not found is looked up again by the pass itself.
+            grid_arrive(ctr);
+            if (gtid < n_valid) {
+                const unsigned long long key = first_block_key<VARIANT>(m, g, ti, s_pose.R, s_pose.t, e0.x, __int_as_float(e0.y));
+                if (m.world <= 1 || block_owner(key, m.world) == m.rank) {
+                    const int slot = map_find(m, key);
+                    if (slot >= 0) { ck = key; cs = slot; }
+                }
+            }
+            grid_wait(ctr, ++barriers * gridDim.x);
             // CTA 0 publishes the previous frame; it does so before it publishes its sums of this frame's first pass, which
             // every CTA waits for before it can reach this frame's fusion, so no statistics of this frame are in yet
             ResultSnapshot* prev = pick(fb.snap, f - 1);
@@ -965,8 +1000,6 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
         }
         if (threadIdx.x == 0 && flog) flog_enter(flog + 2);
         int converged = 0, k = 0;
-        unsigned long long ck = kEmptyKey;  // block probed for this thread's pixel in the previous pass
-        int cs = -1;
         __syncthreads();
         if (threadIdx.x == 0) {
             quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59

@@ -219,7 +219,7 @@ gsdf_status gsdf_scan_collect(gsdf_handle h, gsdf_frame_result* out);
 int32_t gsdf_scan_pending(gsdf_handle h);
 /* The Scan3D frame loop (main_scan_3d.cpp:208-266) for n frames in one call; results[i] is filled in frame order
  * (the pipeline must be empty on entry and is empty on return).  Knowing the frames ahead, the loop gives the tracker
- * up to 4 frames per launch and keeps up to 12 frames in flight (uploads and frame-only kernels run ahead); the result
+ * up to 8 frames per launch and keeps up to 24 frames in flight (uploads and frame-only kernels run ahead); the result
  * of every frame is the same as through gsdf_scan_submit / gsdf_scan_collect.  frames[i] are host pointers
  * (on_device = 0, pinned memory recommended) or 16-byte aligned device pointers (on_device = 1), all valid until the
  * call returns; mode as gsdf_scan_submit.  Stops at the first error (results of the frames collected so far are
