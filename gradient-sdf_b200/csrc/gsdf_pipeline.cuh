@@ -356,15 +356,20 @@ __device__ __forceinline__ float block_sum_29(float mine, float (*sm)[kAccStride
     return s;
 }
 
-template <int NWARPS>
+struct NoWork { __device__ __forceinline__ void operator()() const {} };
+
+// `between`: work that does not depend on the exchange, run after this CTA has published its sums and before it starts to
+// poll (the words of the slowest CTA are at least one L2 round trip away).
+template <int NWARPS, typename Between = NoWork>
 __device__ __forceinline__ void exchange_29(unsigned long long* rows /* [2][gridDim.x][32] */, unsigned int tag, float mine,
                                             float (*sm)[kAccStride] /* not the CTA stage's array */, float* tot,
-                                            Counters* ctr, unsigned int poll_ns) {
+                                            Counters* ctr, unsigned int poll_ns, Between between = Between()) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nrows = gridDim.x;
     unsigned long long* buf = rows + (size_t)(tag & 1u) * nrows * kAccStride;
     const unsigned long long tg = (unsigned long long)tag << 32;
     if (threadIdx.x < kAccTerms) st_word(buf + (size_t)blockIdx.x * kAccStride + threadIdx.x, tg | __float_as_uint(mine));
+    between();
     // warp w polls rows w, w + NWARPS, ...; lane = term.  All loads of a round are in flight together.
     constexpr int kJ = 8;
     float s = 0.f;
@@ -448,13 +453,45 @@ __device__ __forceinline__ void warp_merge_by_key(unsigned long long key, bool n
 // non-coherent read-only path.
 // STAMPS: debug stamps per warp (track_kernel<.., true>, launched only while gsdf_debug_track_timers is armed: the stamp
 // tests alone are ~21 of the ~250 instructions of a unit).
+// The calling warp's share [u0, u1) of the frame's units (unit = 32-pixel chunk of the list x one ray sample, chunk-major).
+__device__ __forceinline__ void fuse_range(int n_valid, int S, int& u0, int& u1) {
+    const int units = ((n_valid + 31) >> 5) * S;  // < 2^31: checked by gsdf_create
+    const int warps_total = (gridDim.x * blockDim.x) >> 5;
+    const int wid = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;  // warp ranges are interleaved over the CTAs
+    // warp w takes units [w*q + min(w, r), ...): q or q + 1 of them (one division, the same for every warp)
+    const int q = units / warps_total, r = units - q * warps_total;
+    u0 = wid * q + min(wid, r);
+    u1 = u0 + q + (wid < r ? 1 : 0);
+}
+
+// The pose-independent pixel data of one list entry, as fusion needs it.  track_kernel fetches the data of each warp's
+// FIRST unit while the sums of the frame's first two passes travel (the list entry in the first, the planes it indexes in the
+// second: one L2 round trip each, less than the exchange takes anyway) and parks it in shared memory (kPfWords words per
+// thread), so that the fusion phase does not open with two dependent L2 round trips that nothing overlaps.
+constexpr int kPfWords = 7;  // z, x0, y0, normal (3), hom_inv
+template <bool COHERENT>
+__device__ __forceinline__ void fuse_pixel_planes(const FrameGeom& g, int2 e, const float* __restrict__ nx,
+                                                  const float* __restrict__ ny, const float* __restrict__ nz,
+                                                  const float* __restrict__ x0, const float* __restrict__ y0,
+                                                  const float* __restrict__ hom_inv, float* o) {
+    const int idx = (e.x >> 16) * g.w + (e.x & 0xFFFF);
+    o[0] = __int_as_float(e.y);
+    o[1] = x0[idx]; o[2] = y0[idx];
+    o[3] = COHERENT ? __ldcg(nx + idx) : nx[idx];
+    o[4] = COHERENT ? __ldcg(ny + idx) : ny[idx];
+    o[5] = COHERENT ? __ldcg(nz + idx) : nz[idx];
+    o[6] = hom_inv[idx];
+}
+
 template <int VARIANT, bool COHERENT, bool STAMPS = false>
 __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, const Pose& pose,
                                           const int2* __restrict__ vlist, int n_valid, const float* __restrict__ nx,
                                           const float* __restrict__ ny, const float* __restrict__ nz,
                                           const float* __restrict__ x0, const float* __restrict__ y0,
                                           const float* __restrict__ hom_inv, Counters* ctr, unsigned int& n_pts,
-                                          unsigned int& n_upd, unsigned long long* fdbg = nullptr /* debug: [warp][8] stamps */) {
+                                          unsigned int& n_upd, unsigned long long* fdbg = nullptr /* debug: [warp][8] stamps */,
+                                          const float* pf = nullptr /* shared: [kPfWords][blockDim.x], this thread's pixel of
+                                                                       the warp's first unit (fuse_pixel_planes) */) {
     const float* R = pose.R;
     const int lane = threadIdx.x & 31;
     const int S = 2 * g.factor + 1;
@@ -466,13 +503,9 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
     // dealt round-robin and a warp had 3 or 4 of them: the 4-item CTAs finished 6 us after the others), so a warp
     // loads the pixel data of only one or two chunks.  Warp ranges are interleaved over the CTAs (warp-major).
     const bool narrow = m.cap_mask < (1u << 23) - 32u;  // voxel addresses (slot * 512 + local) below 2^32 - 2^14
-    const int nchunks = (n_valid + 31) >> 5;
-    const int units = nchunks * S;  // < 2^31: a frame has at most 2^26 pixels (gsdf_create), S is at most a few hundred
-    const int warps_total = (gridDim.x * blockDim.x) >> 5;
     const int wid = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
-    // warp w takes units [w*q + min(w, r), ...): q or q + 1 of them (one division, the same for every warp)
-    const int q = units / warps_total, r = units - q * warps_total;
-    const int u0 = wid * q + min(wid, r), u1 = u0 + q + (wid < r ? 1 : 0);
+    int u0, u1;
+    fuse_range(n_valid, S, u0, u1);
     // debug stamps of this warp (lane 0): 0 entry, 1 first pixel data there, 2 first slot known, 3 first merge done, 4 first
     // reductions issued, 5 all units done, 6 = units | probes << 32, 7 = reductions issued by the warp
     unsigned long long* dbg = (STAMPS && fdbg && lane == 0) ? fdbg + (size_t)wid * 8 : nullptr;
@@ -488,13 +521,16 @@ __device__ __forceinline__ void fuse_work(const MapView& m, const FrameGeom& g, 
         bool valid = j < n_valid;
         float z = 0.f, Rxy0 = 0.f, Rxy1 = 0.f, Rxy2 = 0.f, Rn0 = 0.f, Rn1 = 0.f, Rn2 = 0.f;
         if (valid) {
-            const int2 e = COHERENT ? __ldcg(vlist + j) : __ldg(vlist + j);
-            const int idx = (e.x >> 16) * g.w + (e.x & 0xFFFF);
-            z = __int_as_float(e.y);
-            const float hx = x0[idx], hy = y0[idx];
-            const float a = COHERENT ? __ldcg(nx + idx) : nx[idx], b = COHERENT ? __ldcg(ny + idx) : ny[idx],
-                        c = COHERENT ? __ldcg(nz + idx) : nz[idx];
-            const float hi = hom_inv[idx];
+            float d7[kPfWords];
+            if (pf != nullptr && u - (k_end - k_first) == u0) {  // the warp's first unit: fetched during the first passes
+#pragma unroll
+                for (int i = 0; i < kPfWords; ++i) d7[i] = pf[i * blockDim.x + threadIdx.x];
+            } else {
+                const int2 e = COHERENT ? __ldcg(vlist + j) : __ldg(vlist + j);
+                fuse_pixel_planes<COHERENT>(g, e, nx, ny, nz, x0, y0, hom_inv, d7);
+            }
+            z = d7[0];
+            const float hx = d7[1], hy = d7[2], a = d7[3], b = d7[4], c = d7[5], hi = d7[6];
             const float nsq = dot3_rn(a, b, c, a, b, c);
             const float d = dot3_rn(a, b, c, hx, hy, 1.f);
             if ((double)nsq < .1) valid = false;                                       // MapGradPixelSdfOmp.cpp:97
@@ -956,6 +992,7 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
     __shared__ float s_part[NW][kAccStride];   // grid stage
     __shared__ int s_conv;
     __shared__ float s_valid_sum;  // contributing pixels summed over the frame's passes (thread 0)
+    __shared__ float s_pf[kPfWords * NT];  // pixel data of each warp's first fusion unit (fuse_pixel_planes)
     GSDF_STAMPX(0);
     // pixel j of the list -> warp-sized chunk j/32 -> CTA (chunk % grid), warp (chunk / grid): a frame with fewer valid
     // pixels than resident threads (the usual case: ~90 k of 114 k) is spread over ALL SMs instead of filling the
@@ -1023,7 +1060,29 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
             GSDF_STAMP(1);
             const float mine = block_sum_29<NW>(wsum, s_warp);
             GSDF_STAMP(2);
-            exchange_29<NW>(rows, tag0 + (unsigned)pass_id + 1u, mine, s_part, s_tot, ctr, tp.poll_ns);
+            // while the sums travel: the pixel this thread's fusion starts with (depends on neither the pose nor the map)
+            exchange_29<NW>(rows, tag0 + (unsigned)pass_id + 1u, mine, s_part, s_tot, ctr, tp.poll_ns, [&]() {
+                if (k > 1 || fuse_normals == nullptr) return;
+                if (k == 0) {  // its list entry
+                    int u0, u1;
+                    fuse_range(n_valid, 2 * g.factor + 1, u0, u1);
+                    const int j = (u0 / (2 * g.factor + 1)) * 32 + (int)(threadIdx.x & 31);
+                    int2 e = make_int2(-1, 0);
+                    if (u0 < u1 && j < n_valid) e = __ldcg(vlist + j);
+                    s_pf[threadIdx.x] = __int_as_float(e.x);
+                    s_pf[NT + threadIdx.x] = __int_as_float(e.y);
+                } else {       // the planes the entry indexes
+                    const int2 e = make_int2(__float_as_int(s_pf[threadIdx.x]), __float_as_int(s_pf[NT + threadIdx.x]));
+                    if (e.x >= 0) {
+                        const size_t np = (size_t)g.w * g.h;
+                        float d7[kPfWords];
+                        fuse_pixel_planes<true>(g, e, fuse_normals, fuse_normals + np, fuse_normals + 2 * np, planes, planes + np,
+                                                planes + 4 * np, d7);
+#pragma unroll
+                        for (int i = 0; i < kPfWords; ++i) s_pf[i * NT + threadIdx.x] = d7[i];
+                    }
+                }
+            });
             GSDF_STAMP(3);
             if (px.world > 1) peer_allreduce_29(px, pass_id, s_tot);
             GSDF_STAMP(4);
@@ -1066,7 +1125,8 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
             unsigned int n_upd = 0, n_pts = 0;
             fuse_work<VARIANT, true, STAMPS>(m, g, s_pose, vlist, n_valid, fuse_normals, fuse_normals + np, fuse_normals + 2 * np,
                                              planes, planes + np, planes + 4 * np, ctr, n_pts, n_upd,
-                                             (STAMPS && fb.dbg) ? fb.dbg + (size_t)gridDim.x * 28 : nullptr);
+                                             (STAMPS && fb.dbg) ? fb.dbg + (size_t)gridDim.x * 28 : nullptr,
+                                             (converged ? k + 1 : k) >= 2 ? s_pf : nullptr);  // two passes have run
             fuse_stats_flush(ctr, n_pts, n_upd);
         }
         GSDF_STAMPX(2);
