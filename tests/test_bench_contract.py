@@ -16,7 +16,7 @@ def _last_line(name):
     return json.loads((ROOT / "profiles" / name).read_text().strip().splitlines()[-1])
 
 
-@pytest.mark.parametrize("name", ["r1f_bench_base.json", "r1f_bench_grad.json", "r2f_bench_grad.json", "r2z_bench_grad.json"])
+@pytest.mark.parametrize("name", ["r1f_bench_base.json", "r1f_bench_grad.json", "r2f_bench_grad.json", "r2z_bench_grad.json", "r2final_bench_grad.json"])
 def test_recorded_bench_line_has_the_contract_keys(name):
     d = _last_line(name)
     assert all(k in d for k in REQUIRED), [k for k in REQUIRED if k not in d]
@@ -34,7 +34,7 @@ def test_recorded_bench_line_has_the_contract_keys(name):
 
 
 def test_round2_line_measures_the_target_with_the_same_config_in_both_arms():
-    ours, ref = _last_line("r2z_bench_grad.json"), _last_line("r2z_bench_reference.json")
+    ours, ref = _last_line("r2final_bench_grad.json"), _last_line("r2final_bench_reference.json")
     assert ours["config"] == ref["config"] and ours["config"]["variant"] == "grad" and ours["config"]["voxel_size"] == 0.01
     assert ours["metric"] == ref["metric"] and ref["impl"] == "reference" and ref["gpu_launches"] == 0
     assert ours["repetitions"]["n"] >= 9 and ours["repetitions"]["value_min"] <= ours["value"] <= ours["repetitions"]["value_max"]
@@ -61,8 +61,9 @@ def test_bench_refuses_to_run_without_a_gpu_instead_of_falling_back():
 
 def test_scaling_lines_never_get_slower_with_more_gpus():
     """bench.py --gpus N reports the better of "sharded over N" and "one GPU of the N" as value (shards_used says which)."""
-    vals = [_last_line("r2z_bench_grad.json")["value"]] + [_last_line(f"r2z_bench_n{n}.json")["value"] for n in (2, 4, 8)]
-    assert all(v >= 0.97 * vals[0] for v in vals[1:]), vals
-    for n in (2, 4, 8):
-        d = _last_line(f"r2z_bench_n{n}.json")
-        assert d["n_gpus"] == n and d["shards_used"] in (1, n) and d["sharded"]["n_shards"] == n and d["room_scale"]["n_gpus"] == n
+    for tag in ("r2z", "r2final"):
+        vals = [_last_line(f"{tag}_bench_grad.json")["value"]] + [_last_line(f"{tag}_bench_n{n}.json")["value"] for n in (2, 4, 8)]
+        assert all(v >= 0.97 * vals[0] for v in vals[1:]), vals
+        for n in (2, 4, 8):
+            d = _last_line(f"{tag}_bench_n{n}.json")
+            assert d["n_gpus"] == n and d["shards_used"] in (1, n) and d["sharded"]["n_shards"] == n and d["room_scale"]["n_gpus"] == n
