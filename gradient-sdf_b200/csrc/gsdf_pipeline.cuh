@@ -251,6 +251,7 @@ __device__ __forceinline__ bool track_pixel_terms(const MapView& m, const FrameG
 // halves the rows of the grid-level exchange below).  64 registers per thread either way, so that one 512-thread,
 // 32-register CTA of the frame-only kernel fits beside it (shadow mode).
 constexpr int kTrackThreadsMax = 768;
+constexpr int kMorePixels = 2;  // pixels per thread beyond the first whose probed block is remembered between passes
 
 struct TrackParams {
     int max_iters;
@@ -993,6 +994,8 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
     __shared__ int s_conv;
     __shared__ float s_valid_sum;  // contributing pixels summed over the frame's passes (thread 0)
     __shared__ float s_pf[kPfWords * NT];  // pixel data of each warp's first fusion unit (fuse_pixel_planes)
+    __shared__ unsigned long long s_ck[kMorePixels * NT];  // block probed for the thread's 2nd, 3rd pixel in the previous pass
+    __shared__ int s_cs[kMorePixels * NT];                 // ... and its slot
     GSDF_STAMPX(0);
     // pixel j of the list -> warp-sized chunk j/32 -> CTA (chunk % grid), warp (chunk / grid): a frame with fewer valid
     // pixels than resident threads (the usual case: ~90 k of 114 k) is spread over ALL SMs instead of filling the
@@ -1037,6 +1040,10 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
         }
         if (threadIdx.x == 0 && flog) flog_enter(flog + 2);
         int converged = 0, k = 0;
+        if (VARIANT == 0) {
+#pragma unroll
+            for (int i = 0; i < kMorePixels; ++i) s_ck[i * NT + threadIdx.x] = kEmptyKey;
+        }
         __syncthreads();
         if (threadIdx.x == 0) {
             quat_to_R(s_pose7 + 3, s_pose.R);  // pose_.rotationMatrix(), RigidPointOptimizerOmp.cpp:59
@@ -1049,13 +1056,42 @@ track_kernel(MapView m, FrameGeom g, TrackIntr ti, FrameState* st,
             // every pixel's 29 products are reduced across the warp at once: lane L keeps the warp's running sum of term L
             // (the loop bound is the chunk's first entry, so whole warps run it together)
             float wsum = 0.f;
+            // A frame with more valid pixels than resident threads (room scale: 2.7 per thread) gives a thread several pixels:
+            // (grad-sdf) the NEXT pixel's list entry is fetched while this one is looked up, and the probed block of the
+            // thread's second and third pixel is remembered in shared memory like the first one's is in registers — otherwise
+            // every further pixel costs three dependent L2 round trips (entry, key, voxel) in every pass.
+            if (VARIANT == 1) {
+                // base-sdf keeps the plain loop: a second inlined copy of its 8-corner lookup (or the state to share one copy)
+                // costs the usual one-pixel-per-thread frame 3 % (measured), more than it gains on large frames
 #pragma unroll 1
-            for (int j = gtid; (j & ~31) < n_valid; j += nthreads) {
-                const bool has = j < n_valid;
-                const int2 e = j == gtid ? e0 : (has ? __ldcg(vlist + j) : make_int2(0, 0));
-                float v[32];
-                track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ck, cs);
-                wsum += warp_reduce_scatter_32(v);
+                for (int j = gtid; (j & ~31) < n_valid; j += nthreads) {
+                    const bool has = j < n_valid;
+                    const int2 e = j == gtid ? e0 : (has ? __ldcg(vlist + j) : make_int2(0, 0));
+                    float v[32];
+                    track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ck, cs);
+                    wsum += warp_reduce_scatter_32(v);
+                }
+            } else {
+                int2 e = e0;
+                int it = 0;
+#pragma unroll 1
+                for (int j = gtid; (j & ~31) < n_valid; j += nthreads, ++it) {
+                    const bool has = j < n_valid;
+                    int2 en = make_int2(0, 0);
+                    if (j + nthreads < n_valid) en = __ldcg(vlist + j + nthreads);
+                    float v[32];
+                    if (it == 0) {
+                        track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ck, cs);
+                    } else {
+                        const bool slot = it <= kMorePixels;
+                        unsigned long long ckx = slot ? s_ck[(it - 1) * NT + threadIdx.x] : kEmptyKey;
+                        int csx = slot ? s_cs[(it - 1) * NT + threadIdx.x] : -1;
+                        track_pixel_terms<VARIANT>(m, g, ti, s_pose.R, s_pose.t, has, e.x, __int_as_float(e.y), v, ckx, csx);
+                        if (slot) { s_ck[(it - 1) * NT + threadIdx.x] = ckx; s_cs[(it - 1) * NT + threadIdx.x] = csx; }
+                    }
+                    wsum += warp_reduce_scatter_32(v);
+                    e = en;
+                }
             }
             GSDF_STAMP(1);
             const float mine = block_sum_29<NW>(wsum, s_warp);
