@@ -4,7 +4,8 @@
 //                                             single-pass compaction of the z-valid pixels into vlist = {(y<<16)|x, z}
 //                                             in tile order (so that every lane of every warp downstream has work and a
 //                                             warp's pixels are neighbours) + FALS normals of the tiles that hold any;
-//   track_kernel<V>                           main stream, persistent cooperative launch over up to kMaxBatch frames;
+//   track_kernel<V, NT, STAMPS>               main stream, persistent cooperative launch over up to kMaxBatch frames
+//                                             (NT threads per CTA; STAMPS = the twin with debug stamps compiled in);
 //                                             per frame the WHOLE Gauss-Newton loop of
 //                                             RigidPointOptimizer::optimize_sampled (RigidPointOptimizerOmp.cpp:44-106):
 //                                             per-pixel lookup + Jacobian, warp -> CTA -> grid reduction of the 29 sums
