@@ -255,7 +255,9 @@ gsdf_status gsdf_profile_read(gsdf_handle h, int32_t kind, int64_t* launches, do
  * "label microseconds" lines (time since the first mark) into buf, returning the size needed. */
 gsdf_status gsdf_trace_enable(gsdf_handle h, int32_t on);
 int64_t gsdf_trace_dump(gsdf_handle h, char* buf, int64_t size);
-/* Debug aid: per-CTA %globaltimer stamps of the tracker's phases (see gsdf_api.cu); not for production use. */
+/* Debug aid, no reference counterpart: per-CTA %globaltimer stamps of the tracker's phases and per-warp stamps of its fusion
+ * (layout in gsdf_api.cu).  out == NULL arms it; while armed the tracker runs its stamped twin (track_kernel<V, NT, true>:
+ * the stamp tests cost ~2 % of the frame rate, which is why the regular kernel does not carry them). */
 gsdf_status gsdf_debug_track_timers(gsdf_handle h, unsigned long long* out, int32_t* n_ctas);
 /* Debug aid, no reference counterpart: device-clock spans of the pipeline's two kernels per submitted frame.
  * out == NULL arms the log; otherwise out receives 256 x 8 words per frame (frame seq modulo 256): {frame-only kernel first
