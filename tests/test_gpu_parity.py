@@ -208,6 +208,19 @@ def test_fusion_and_tracker_sums_vs_oracle_at_baseline_sizes(pkg, po, synth, con
     ref = orc.accumulate(frames[3], R, pn[:3])
     assert got[28] == ref[28] and got[28] > 10000
     assert np.abs(got[:27] - ref[:27]).max() <= 1e-4 * np.abs(ref[:27]).max()
+    # ... and two Gauss-Newton steps of the PERSISTENT tracker (track_kernel: at C4 a thread looks up 2.7 pixels per pass, at
+    # 1280x720 up to 8 — the loop that fetches the next list entry ahead and keeps the blocks of a thread's 2nd and 3rd
+    # pixel between passes) from the previous frame's pose, against the oracle's two steps from the same pose
+    opt = pkg.RigidPointOptimizer(sdf, num_iterations=2)
+    opt.set_pose(poses[2])
+    orc.set_pose(poses[2])
+    orc.set_opt(2, 1e-3, 1.0)
+    conv = opt.optimize(frames[3])
+    conv_o, _ = orc.optimize(frames[3])
+    assert conv == conv_o
+    dp = np.abs(opt.pose() - orc.get_pose())
+    assert dp.max() < 1e-4, dp
+    assert np.abs(opt.pose() - poses[2]).max() > 1e-4  # the steps moved the pose: the comparison is not vacuous
     sdf.close()
 
 
